@@ -1,0 +1,102 @@
+"""CPU: the oracle (oracle/*.c) against golden vectors produced by the REFERENCE ITSELF
+(oracle/make_golden.py: reference .cu/.cpp compiled as host code, dpvo/ba.py imported unchanged)."""
+import numpy as np
+import pytest
+
+import oracle
+
+
+@pytest.mark.parametrize("name,radius,mode,tol", [
+    ("f32_r3", 3, oracle.F32, 0.0), ("f32_r1", 1, oracle.F32, 0.0),
+    ("f16_r3", 3, oracle.F16EMU, 0.0), ("f16_r0", 0, oracle.F16EMU, 0.0),
+    ("f32_r3", 3, oracle.F64, 2e-6), ("f16_r3", 3, oracle.F64, 2e-2)])
+def test_corr_forward_matches_reference(golden, name, radius, mode, tol):
+    g = golden["corr_ref"]
+    out = oracle.corr_forward(g[name + "_fmap1"], g[name + "_fmap2"], g[name + "_coords"], g[name + "_ii"],
+                              g[name + "_jj"], radius, mode=mode)
+    ref = g[name + "_out"]
+    assert out.shape == ref.shape
+    # F32 / F16EMU restate the reference's evaluation order: bit-exact.  F64 = truth: bounded by ref's rounding.
+    assert np.abs(out - ref).max() <= tol * max(1.0, np.abs(ref).max())
+
+
+@pytest.mark.parametrize("name,radius", [("f32_r3", 3), ("f32_r1", 1), ("f16_r3", 3)])
+def test_corr_backward_matches_reference(golden, name, radius):
+    g = golden["corr_ref"]
+    g1, g2 = oracle.corr_backward(g[name + "_fmap1"], g[name + "_fmap2"], g[name + "_coords"], g[name + "_ii"],
+                                  g[name + "_jj"], g[name + "_grad"], radius)
+    for mine, ref in ((g1, g[name + "_g1"]), (g2, g[name + "_g2"])):
+        assert np.abs(mine - ref).max() <= 2e-5 * max(1.0, np.abs(ref).max())
+
+
+@pytest.mark.parametrize("r", [0, 1, 3])
+def test_patchify_matches_reference(golden, r):
+    g = golden["corr_ref"]
+    out = oracle.patchify_forward(g["patchify_net"], g["patchify_coords"], r)
+    assert np.array_equal(out, g[f"patchify_r{r}_out"])
+    ng = oracle.patchify_backward(g["patchify_net"].shape, g["patchify_coords"], g[f"patchify_r{r}_grad"], r)
+    assert np.abs(ng - g[f"patchify_r{r}_netgrad"]).max() < 1e-5
+
+
+def _ba_inputs(g, name):
+    return {k: g[f"{name}_in_{k}"] for k in ("poses", "patches", "intrinsics", "target", "weight", "lmbda", "ii", "jj", "kk")}
+
+
+@pytest.mark.parametrize("name", ["win", "trk", "off"])
+@pytest.mark.parametrize("tag", ["full", "late", "struct"])
+@pytest.mark.parametrize("mode", [oracle.F32, oracle.F64])
+def test_ba_matches_reference(golden, name, tag, mode):
+    g = golden["ba_ref"]
+    t0, t1, iters = (int(v) for v in g[f"{name}_{tag}_args"])
+    o = oracle.ba_forward(**_ba_inputs(g, name), t0=t0, t1=t1, iterations=iters, mode=mode)
+    assert o["status"] == 0
+    # fp32 reference (sequential atomics, LAPACK Cholesky) vs restatement: rounding-level agreement
+    assert np.abs(o["poses"] - g[f"{name}_{tag}_poses"]).max() < 2e-4
+    ref_d = g[f"{name}_{tag}_patches"][:, 2, 0, 0]
+    assert np.abs(o["patches"][:, 2, 0, 0] - ref_d).max() < 2e-3 * max(1.0, np.abs(ref_d).max())
+    assert np.array_equal(o["patches"][:, :2], g[f"{name}_{tag}_patches"][:, :2])
+
+
+@pytest.mark.parametrize("name", ["win", "trk", "off"])
+def test_reproject_and_neighbors_match_reference(golden, name):
+    g = golden["ba_ref"]
+    i = _ba_inputs(g, name)
+    rp = oracle.reproject(i["poses"], i["patches"], i["intrinsics"], i["ii"], i["jj"], i["kk"], mode=oracle.F32)
+    assert np.abs(rp - g[f"{name}_reproject"]).max() < 1e-3
+    ix, jx = oracle.neighbors(i["kk"], i["jj"])
+    assert np.array_equal(ix, g[f"{name}_nb_ix"]) and np.array_equal(jx, g[f"{name}_nb_jx"])
+
+
+def test_neighbors_random_bit_exact(golden):
+    g = golden["ba_ref"]
+    ix, jx = oracle.neighbors(g["nb_rand_ii"], g["nb_rand_jj"])
+    assert np.array_equal(ix, g["nb_rand_ix"]) and np.array_equal(jx, g["nb_rand_jx"])
+
+
+@pytest.mark.parametrize("tag,freen", [("full", -1), ("free4", 4)])
+def test_solve_system_matches_reference(golden, tag, freen):
+    g = golden["ba_ref"]
+    d, rc = oracle.solve_system(g["pgo_Ji"], g["pgo_Jj"], g["pgo_ii"], g["pgo_jj"], g["pgo_res"], 1e-4, 1e-4, freen)
+    assert rc == 0
+    assert np.abs(d - g[f"pgo_{tag}_delta"]).max() < 1e-4 * max(1.0, np.abs(g[f"pgo_{tag}_delta"]).max())
+
+
+@pytest.mark.parametrize("name", ["win", "trk"])
+@pytest.mark.parametrize("tag", ["prior", "noprior"])
+def test_prior_term_matches_python_ba(golden, syn, name, tag):
+    """dpvo/ba.py (ep=1, one iteration, CUDA-kernel bounds) == CUDA-BA algorithm + prior term"""
+    kw = {"win": dict(seed=0, n=6, M=8, edges="all"), "trk": dict(seed=3, n=12, M=6, edges="tracker", lifetime=5, removal=8)}[name]
+    s = syn.make_ba_scene(**kw)
+    est = s["patches_est"] if tag == "prior" else None
+    o = oracle.ba_forward(s["poses"], s["patches"], s["intrinsics"], s["target"], s["weight"], s["lmbda"], s["ii"],
+                          s["jj"], s["kk"], s["t0"], s["t1"], 1, patches_est=est, mu=2.0, mode=oracle.F64)
+    g = golden["pyba_ref"]
+    rp, rd = g[f"{name}_{tag}_poses"], g[f"{name}_{tag}_patches"][:, 2, 1, 1]
+    assert np.abs(o["poses"][:, :3] - rp[:, :3]).max() < 2e-4
+    qdot = np.abs((o["poses"][:, 3:] * rp[:, 3:]).sum(-1))
+    assert (1 - qdot).max() < 1e-6
+    d = o["patches"][:, 2, 1, 1]
+    # ba.py clamps depths to [1e-3, 10]; the CUDA rule is (>20 -> 1, >= 1e-4): compare where both are inactive
+    ok = (rd > 1.1e-3) & (rd < 9.9) & (d > 1.1e-3) & (d < 9.9)
+    assert ok.mean() > 0.9
+    assert np.abs(d[ok] - rd[ok]).max() < 2e-3
