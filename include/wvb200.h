@@ -1,0 +1,152 @@
+/* wvb200.h -- C ABI of the B200-native (sm_100a) altcorr + fastba hot path.
+ *
+ * Drop-in boundary for ljjTYJR/Wild-video-3d-reconstruction's DPVO tracker: these entry points are what
+ * the reference's two extension modules bind (citations are paths under the reference tree):
+ *
+ *   cuda_corr.forward / backward / patchify_forward / patchify_backward   dpvo/altcorr/correlation.cpp:57-63
+ *   cuda_ba.forward / neighbors / reproject / solve_system                dpvo/fastba/ba.cpp:236-241
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no torch types.  Unless a function says "host", every pointer is a
+ *     DEVICE pointer on the current CUDA device and work is enqueued on `stream` without host
+ *     synchronisation (capture-safe).  The caller owns all buffers.
+ *   - return value: WV_OK (0) or a negative WV_E* code; wv_strerror() names it.  No exceptions cross
+ *     the ABI.  Data-dependent failures that only the device can see (an edge index out of range,
+ *     a reduced camera system that is not positive definite) are reported through a caller-supplied
+ *     device word `status` (see WV_STATUS_*), which the caller reads back when it wants the
+ *     reference's "raise in the same call" behaviour.
+ *   - dtype of feature maps: WV_F16 or WV_F32 (the tracker runs fp16, training fp32).  Geometry is fp32,
+ *     indices are int64 -- exactly the accessor types of the reference kernels.
+ */
+#ifndef WVB200_H_
+#define WVB200_H_
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct CUstream_st* wv_stream_t; /* == cudaStream_t */
+
+enum { WV_F16 = 0, WV_F32 = 1 };
+
+enum {
+  WV_OK = 0,
+  WV_EINVAL = -1,      /* bad argument (null pointer, negative size, unsupported dtype/shape) */
+  WV_ECUDA = -2,       /* a CUDA runtime/driver call failed; wv_last_cuda_error() has the code */
+  WV_EWORKSPACE = -3,  /* workspace too small */
+  WV_EUNSUPPORTED = -4 /* shape outside what this build supports */
+};
+
+/* bits of the device status word */
+enum {
+  WV_STATUS_BAD_INDEX = 1, /* an ii/jj/kk entry was outside its tensor; that edge was skipped */
+  WV_STATUS_NOT_SPD = 2    /* Cholesky met a non-positive pivot (reference: torch::linalg::cholesky throws, ba_cuda.cu:521) */
+};
+
+const char* wv_strerror(int code);
+int wv_last_cuda_error(void);
+/* 1 when a device of compute capability 10.x is current, else 0 (the library has sm_100a code only) */
+int wv_device_supported(void);
+
+/* ---------------------------------------------------------------------------------------------
+ * altcorr
+ * ------------------------------------------------------------------------------------------- */
+
+/* scratch bytes wv_corr_forward wants for its channels-last staging of the referenced fmap2 slots
+ * (0 when the generic path will be taken).  Reference: none (it gathers NCHW directly). */
+size_t wv_corr_workspace_bytes(int dtype, int B, int E, int C, int PH, int PW, int n1, int n2, int H2, int W2, int radius);
+
+/* cuda_corr.forward -- replaces corr_cuda_forward + corr_forward_kernel + the ATen bilinear blend
+ * (dpvo/altcorr/correlation_kernel.cu:82-136, 193-233).
+ *   fmap1 [B][n1][C][PH][PW], fmap2 [B][n2][C][H2][W2] (dtype), coords [B][E][2][PH][PW] fp32,
+ *   ii [E] in [0,n1), jj [E] in [0,n2)  ->  out [B][E][2r+1][2r+1][PH][PW] (dtype), contiguous in the
+ *   reference's *permuted* order (dim2 = x-tap, dim3 = y-tap; correlation_kernel.cu:232).
+ *   Products are accumulated in fp32 for both dtypes (the reference accumulates in scalar_t).
+ *   workspace may be NULL (generic path).  status may be NULL. */
+int wv_corr_forward(const void* fmap1, const void* fmap2, const float* coords, const int64_t* ii,
+                    const int64_t* jj, void* out, int dtype, int B, int E, int C, int PH, int PW,
+                    int n1, int n2, int H2, int W2, int radius, void* workspace, size_t workspace_bytes,
+                    int* status, wv_stream_t stream);
+
+/* cuda_corr.backward -- replaces corr_cuda_backward + corr_backward_kernel (correlation_kernel.cu:139-190, 236-286).
+ *   grad [B][E][2r+1][2r+1][PH][PW] fp32 (same permuted order as `out`), fmap1_grad / fmap2_grad fp32
+ *   accumulators shaped like fmap1 / fmap2, ZEROED BY THE CALLER; the binding casts them to dtype. */
+int wv_corr_backward(const void* fmap1, const void* fmap2, const float* coords, const int64_t* ii,
+                     const int64_t* jj, const float* grad, float* fmap1_grad, float* fmap2_grad,
+                     int dtype, int B, int E, int C, int PH, int PW, int n1, int n2, int H2, int W2,
+                     int radius, int* status, wv_stream_t stream);
+
+/* cuda_corr.patchify_forward (correlation_kernel.cu:16-47, 288-310): net [B][C][H][W], coords [B][M][2]
+ * -> patches [B][M][C][D][D], D = 2r+2, zero where the tap is outside the map (written by this call). */
+int wv_patchify_forward(const void* net, const float* coords, void* patches, int dtype, int B, int M,
+                        int C, int H, int W, int radius, wv_stream_t stream);
+
+/* cuda_corr.patchify_backward (correlation_kernel.cu:49-80, 313-333): gradient [B][M][C][D][D] (dtype)
+ * -> net_grad [B][C][H][W] fp32 accumulator ZEROED BY THE CALLER. */
+int wv_patchify_backward(const void* gradient, const float* coords, float* net_grad, int dtype, int B,
+                         int M, int C, int H, int W, int radius, wv_stream_t stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * fastba
+ * ------------------------------------------------------------------------------------------- */
+
+/* workspace for wv_ba_forward / wv_neighbors on E edges over a patch buffer of n_patches rows */
+size_t wv_ba_workspace_bytes(int64_t E, int64_t n_patches, int n_free_poses);
+
+/* cuda_ba.forward -- replaces cuda_ba() (dpvo/fastba/ba_cuda.cu:422-540): torch::_unique(kk), the edge
+ * kernel reprojection_residuals_and_hessian (:214-365), the ATen Schur/Cholesky sequence (:492-526) and
+ * both retraction kernels (:160-211), for `iterations` Gauss-Newton steps, IN PLACE on poses / patches.
+ *   poses [n_poses][7] (tx,ty,tz,qx,qy,qz,qw; world->camera), patches [n_patches][3][P][P],
+ *   intrinsics [n_poses][4] (row 0 is used, ba_cuda.cu:232-238), target / weight [E][2], lmbda [1],
+ *   ii / jj in [0,n_poses), kk in [0,n_patches); poses t0..t1-1 are free, t1 == t0 is structure-only.
+ *   patches_est (nullable) [n_patches][3][P][P] + mu: the depth-prior term of dpvo/ba.py:151-159
+ *   (C_k += mu*L_k, u_k -= mu*L_k*(d_k - dhat_k), L_k = dhat_k > 0); NULL reproduces the 12-argument call.
+ *   status: device word, OR-ed with WV_STATUS_*; on WV_STATUS_NOT_SPD the failing iteration and all later
+ *   ones apply no update (the reference throws before its retraction kernels). */
+int wv_ba_forward(float* poses, float* patches, const float* intrinsics, const float* target,
+                  const float* weight, const float* lmbda, const int64_t* ii, const int64_t* jj,
+                  const int64_t* kk, int64_t E, int64_t n_poses, int64_t n_patches, int P, int t0, int t1,
+                  int iterations, const float* patches_est, float mu, void* workspace,
+                  size_t workspace_bytes, int* status, wv_stream_t stream);
+
+/* cuda_ba.reproject (ba_cuda.cu:368-418, 543-575): coords [E][2][P][P], no depth clamp. */
+int wv_ba_reproject(const float* poses, const float* patches, const float* intrinsics, const int64_t* ii,
+                    const int64_t* jj, const int64_t* kk, int64_t E, int64_t n_poses, int64_t n_patches,
+                    int P, float* coords, int* status, wv_stream_t stream);
+
+/* cuda_ba.neighbors (dpvo/fastba/ba.cpp:106-151), on the device and without host synchronisation:
+ * for every edge the index of the previous / next edge of the same group `ii` in (jj, original index)
+ * order, -1 at the ends.  ii values must lie in [0, n_groups). */
+int wv_neighbors(const int64_t* ii, const int64_t* jj, int64_t E, int64_t n_groups, int64_t* ix,
+                 int64_t* jx, void* workspace, size_t workspace_bytes, int* status, wv_stream_t stream);
+
+/* cuda_ba.solve_system (dpvo/fastba/ba.cpp:156-234) -- HOST pointers, synchronous, fp64 like the
+ * reference's Eigen::SimplicialCholesky<double>.  J_i / J_j [r][7][7], res [r][7] -> delta [n][7] with
+ * n = max(ii, jj) + 1 (written to *n_out; pass delta == NULL to query n).  freen < 0 solves everything,
+ * otherwise only the leading freen poses.  returns WV_OK, WV_EINVAL (i == j: the reference calls exit(1)),
+ * or 1 when the damped normal matrix is not positive definite. */
+int wv_solve_system_host(const float* J_i, const float* J_j, const int64_t* ii, const int64_t* jj,
+                         const float* res, int64_t r, float ep, float lm, int freen, float* delta,
+                         int64_t* n_out);
+
+/* ---------------------------------------------------------------------------------------------
+ * host-buffer entry points (pinned or pageable HOST memory in, HOST memory out): the call a
+ * non-torch embedder makes; copies are enqueued on `stream` around the same kernels and the call
+ * returns after the stream has drained.  Used by bench.py's end-to-end leg.
+ * ------------------------------------------------------------------------------------------- */
+int wv_corr_forward_host(const void* fmap1, const void* fmap2, const float* coords, const int64_t* ii,
+                         const int64_t* jj, void* out, int dtype, int B, int E, int C, int PH, int PW,
+                         int n1, int n2, int H2, int W2, int radius, wv_stream_t stream);
+
+int wv_ba_forward_host(float* poses, float* patches, const float* intrinsics, const float* target,
+                       const float* weight, const float* lmbda, const int64_t* ii, const int64_t* jj,
+                       const int64_t* kk, int64_t E, int64_t n_poses, int64_t n_patches, int P, int t0,
+                       int t1, int iterations, const float* patches_est, float mu, int* status_out,
+                       wv_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* WVB200_H_ */

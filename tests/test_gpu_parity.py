@@ -1,0 +1,271 @@
+"""GPU (B200) parity tests: the CUDA path, called through the reference-named torch extensions (which go
+through the C ABI of include/wvb200.h), against (1) golden outputs of the reference itself and (2) the CPU oracle."""
+import ctypes
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from helpers import dev, pkg, quat_angle, run_ba, run_corr, vp
+
+pytestmark = pytest.mark.gpu
+
+
+# ------------------------------------------------------------------------------------------------- corr
+@pytest.mark.parametrize("name,radius", [("f32_r3", 3), ("f32_r1", 1)])
+def test_corr_fp32_matches_reference(golden, name, radius):
+    g = golden["corr_ref"]
+    out = run_corr(g[name + "_fmap1"], g[name + "_fmap2"], g[name + "_coords"], g[name + "_ii"], g[name + "_jj"], radius, torch.float32)
+    ref = g[name + "_out"]
+    # tolerance (stated): fp32 maps, rtol 1e-5 / atol 1e-5 (FMA contraction and summation order only)
+    np.testing.assert_allclose(out, ref, rtol=1e-5, atol=1e-5)
+
+
+@pytest.mark.parametrize("name,radius", [("f16_r3", 3), ("f16_r0", 0)])
+def test_corr_fp16_matches_reference(golden, name, radius):
+    g = golden["corr_ref"]
+    args = (g[name + "_fmap1"], g[name + "_fmap2"], g[name + "_coords"], g[name + "_ii"], g[name + "_jj"], radius)
+    out = run_corr(*args, torch.float16)
+    ref = g[name + "_out"]
+    truth = oracle.corr_forward(*args, mode=oracle.F64)
+    # tolerance (stated): |new - ref| <= 2e-2 * max(1, |ref|): the reference accumulates 128 products in fp16
+    assert np.abs(out - ref).max() <= 2e-2 * max(1.0, np.abs(ref).max())
+    # and the new path (fp32 accumulate, one final rounding) must be at least as close to the fp64 truth as the reference
+    assert np.abs(out - truth).max() <= max(np.abs(ref - truth).max(), 1e-3 * max(1.0, np.abs(truth).max()))
+    # one fp16 rounding of the truth: half an ulp of the result
+    assert np.abs(out - truth).max() <= 2.0 ** -10 * max(1.0, np.abs(truth).max())
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 2e-6), (torch.float16, 2.0 ** -10)])
+def test_corr_tracker_workload_vs_oracle(syn, dtype, tol):
+    w = syn.make_corr_workload(seed=1, M=8, pmem=12, n_frames=14, ht=24, wd=32, C=128, lifetime=6, removal=9, oob_frac=0.1)
+    for lvl, (fm, div) in enumerate(((w["fmap0"], 1.0), (w["fmap1"], 4.0))):
+        g = torch.from_numpy(w["gmap"]).to(dtype).float().numpy()
+        f = torch.from_numpy(fm).to(dtype).float().numpy()
+        co = (w["coords"] / div).astype(np.float32)
+        out = run_corr(g, f, co, w["ii1"], w["jj1"], 3, dtype)
+        truth = oracle.corr_forward(g, f, co, w["ii1"], w["jj1"], 3, mode=oracle.F64)
+        assert np.abs(out - truth).max() <= tol * max(1.0, np.abs(truth).max()), f"level {lvl}"
+
+
+def test_corr_empty_and_bad_index(golden):
+    cc, _ = pkg().native_modules()
+    g = golden["corr_ref"]
+    f1, f2 = dev(g["f32_r3_fmap1"]), dev(g["f32_r3_fmap2"])
+    out, = cc.forward(f1, f2, torch.zeros(1, 0, 2, 3, 3, device="cuda"), torch.zeros(0, dtype=torch.long, device="cuda"),
+                      torch.zeros(0, dtype=torch.long, device="cuda"), 3)
+    assert tuple(out.shape) == (1, 0, 7, 7, 3, 3)
+    os.environ["WVB200_CHECK_INDICES"] = "1"
+    try:
+        with pytest.raises(IndexError):
+            cc.forward(f1, f2, dev(g["f32_r3_coords"][:, :2]), torch.tensor([0, 99], device="cuda"), torch.tensor([0, 0], device="cuda"), 3)
+    finally:
+        del os.environ["WVB200_CHECK_INDICES"]
+
+
+@pytest.mark.parametrize("name,radius", [("f32_r3", 3), ("f32_r1", 1), ("f16_r3", 3)])
+def test_corr_backward_matches_reference(golden, name, radius):
+    cc, _ = pkg().native_modules()
+    g = golden["corr_ref"]
+    g1, g2 = cc.backward(dev(g[name + "_fmap1"]), dev(g[name + "_fmap2"]), dev(g[name + "_coords"]), dev(g[name + "_ii"]),
+                         dev(g[name + "_jj"]), dev(g[name + "_grad"]), radius)
+    for mine, ref in ((g1, g[name + "_g1"]), (g2, g[name + "_g2"])):
+        assert np.abs(mine.cpu().numpy() - ref).max() <= 5e-5 * max(1.0, np.abs(ref).max())
+
+
+@pytest.mark.parametrize("r", [0, 1, 3])
+def test_patchify_matches_reference(golden, r):
+    cc, _ = pkg().native_modules()
+    g = golden["corr_ref"]
+    p, = cc.patchify_forward(dev(g["patchify_net"]), dev(g["patchify_coords"]), r)
+    assert np.array_equal(p.cpu().numpy(), g[f"patchify_r{r}_out"])  # copies: bit-exact
+    ph, = cc.patchify_forward(dev(g["patchify_net"]).half(), dev(g["patchify_coords"]), r)
+    assert np.array_equal(ph.float().cpu().numpy(), torch.from_numpy(g[f"patchify_r{r}_out"]).half().float().numpy())
+    ng, = cc.patchify_backward(dev(g["patchify_net"]), dev(g["patchify_coords"]), dev(g[f"patchify_r{r}_grad"]), r)
+    assert np.abs(ng.cpu().numpy() - g[f"patchify_r{r}_netgrad"]).max() < 1e-5
+
+
+def test_altcorr_python_mirror_autograd(golden):
+    """the host-side mirror of dpvo/altcorr/correlation.py: corr()/patchify() with autograd"""
+    ac = pkg().altcorr
+    g = golden["corr_ref"]
+    f1 = dev(g["f32_r3_fmap1"]).requires_grad_(True)
+    f2 = dev(g["f32_r3_fmap2"]).requires_grad_(True)
+    out = ac.corr(f1, f2, dev(g["f32_r3_coords"]), dev(g["f32_r3_ii"]), dev(g["f32_r3_jj"]), 3)
+    (out * dev(g["f32_r3_grad"])).sum().backward()
+    assert np.abs(f1.grad.cpu().numpy() - g["f32_r3_g1"]).max() <= 5e-5 * np.abs(g["f32_r3_g1"]).max()
+    assert np.abs(f2.grad.cpu().numpy() - g["f32_r3_g2"]).max() <= 5e-5 * np.abs(g["f32_r3_g2"]).max()
+    net = dev(g["patchify_net"])
+    co = dev(g["patchify_coords"])
+    pt = ac.patchify(net, co, 1)
+    assert tuple(pt.shape) == (2, 7, 5, 3, 3)
+    crop = torch.from_numpy(g["patchify_r1_out"]).cuda()
+    fr = co - co.floor()
+    dx, dy = fr[..., 0][:, :, None, None, None], fr[..., 1][:, :, None, None, None]
+    want = (1 - dy) * (1 - dx) * crop[..., :3, :3] + (1 - dy) * dx * crop[..., :3, 1:] + dy * (1 - dx) * crop[..., 1:, :3] + dy * dx * crop[..., 1:, 1:]
+    assert torch.allclose(pt, want, atol=1e-5)
+
+
+# ------------------------------------------------------------------------------------------------- BA
+def _golden_scene(g, name):
+    return {k: g[f"{name}_in_{k}"] for k in ("poses", "patches", "intrinsics", "target", "weight", "lmbda", "ii", "jj", "kk", "patches_est")}
+
+
+@pytest.mark.parametrize("name", ["win", "trk", "off"])
+@pytest.mark.parametrize("tag", ["full", "late", "struct"])
+def test_ba_matches_reference(golden, name, tag):
+    g = golden["ba_ref"]
+    s = _golden_scene(g, name)
+    t0, t1, iters = (int(v) for v in g[f"{name}_{tag}_args"])
+    poses, patches = run_ba(s, t0, t1, iters)
+    rp, rd = g[f"{name}_{tag}_poses"], g[f"{name}_{tag}_patches"]
+    # tolerances (stated): translation atol 2e-4, rotation 1e-4 rad, inverse depth rtol 2e-3 after `iters` iterations
+    assert np.abs(poses[:, :3] - rp[:, :3]).max() < 2e-4
+    assert quat_angle(poses[:, 3:], rp[:, 3:]).max() < 1e-3
+    assert np.abs(patches[:, 2] - rd[:, 2]).max() < 2e-3 * max(1.0, np.abs(rd[:, 2]).max())
+    assert np.array_equal(patches[:, :2], rd[:, :2])  # x, y channels untouched
+    # every PxP entry of the depth channel carries the same value (patch_retr_kernel)
+    assert np.array_equal(patches[:, 2], np.broadcast_to(patches[:, 2, :1, :1], patches[:, 2].shape))
+
+
+@pytest.mark.parametrize("M,edges", [(96, "tracker"), (32, "all")])
+def test_ba_full_size_vs_oracle_and_deterministic(syn, M, edges):
+    n = 40 if edges == "tracker" else 10
+    s = syn.make_ba_scene(seed=2, n=n, M=M, edges=edges)
+    t1 = s["t1"]
+    t0 = t1 - 10 if edges == "tracker" else s["t0"]
+    o = oracle.ba_forward(s["poses"], s["patches"], s["intrinsics"], s["target"], s["weight"], s["lmbda"], s["ii"], s["jj"],
+                          s["kk"], t0, t1, 2, mode=oracle.F64)
+    assert o["status"] == 0
+    poses, patches = run_ba(s, t0, t1, 2)
+    assert np.abs(poses[:, :3] - o["poses"][:, :3]).max() < 1e-4
+    assert quat_angle(poses[:, 3:], o["poses"][:, 3:]).max() < 1e-4
+    d, do = patches[:, 2, 0, 0], o["patches"][:, 2, 0, 0]
+    assert np.abs(d - do).max() < 1e-3 * max(1.0, np.abs(do).max())
+    poses2, patches2 = run_ba(s, t0, t1, 2)
+    assert np.array_equal(poses, poses2) and np.array_equal(patches, patches2)  # fixed summation order
+    os.environ["WVB200_NO_COOP"] = "1"  # multi-launch plan must give the same bits
+    try:
+        poses3, patches3 = run_ba(s, t0, t1, 2)
+    finally:
+        del os.environ["WVB200_NO_COOP"]
+    assert np.array_equal(poses, poses3) and np.array_equal(patches, patches3)
+
+
+def test_ba_general_graph_slow_path(syn):
+    """duplicate (patch, frame) edges and patches observed from two different source frames: the serialised path"""
+    s = syn.make_ba_scene(seed=4, n=7, M=5, edges="all")
+    rng = np.random.default_rng(0)
+    dup = rng.integers(0, len(s["kk"]), 40)
+    for k in ("ii", "jj", "kk", "target", "weight"):
+        s[k] = np.concatenate([s[k], s[k][dup]])
+    s["ii"][-10:] = (s["ii"][-10:] + 1) % 7  # inconsistent source frame for some patches
+    perm = rng.permutation(len(s["kk"]))
+    for k in ("ii", "jj", "kk", "target", "weight"):
+        s[k] = np.ascontiguousarray(s[k][perm])
+    o = oracle.ba_forward(s["poses"], s["patches"], s["intrinsics"], s["target"], s["weight"], s["lmbda"], s["ii"], s["jj"],
+                          s["kk"], s["t0"], s["t1"], 2, mode=oracle.F64)
+    poses, patches = run_ba(s, s["t0"], s["t1"], 2)
+    assert np.abs(poses - o["poses"]).max() < 2e-4
+    assert np.abs(patches[:, 2, 0, 0] - o["patches"][:, 2, 0, 0]).max() < 2e-3
+
+
+def test_ba_many_edges_per_patch(syn):
+    """segments longer than a warp (> 32 edges per patch)"""
+    s = syn.make_ba_scene(seed=6, n=40, M=3, edges="all", pose_noise=0.005)
+    t0, t1 = s["t1"] - 8, s["t1"]
+    o = oracle.ba_forward(s["poses"], s["patches"], s["intrinsics"], s["target"], s["weight"], s["lmbda"], s["ii"], s["jj"],
+                          s["kk"], t0, t1, 2, mode=oracle.F64)
+    poses, patches = run_ba(s, t0, t1, 2)
+    assert np.abs(poses - o["poses"]).max() < 2e-4
+    assert np.abs(patches[:, 2, 0, 0] - o["patches"][:, 2, 0, 0]).max() < 2e-3
+
+
+@pytest.mark.parametrize("name", ["win", "trk"])
+def test_ba_depth_prior_term(golden, syn, name):
+    kw = {"win": dict(seed=0, n=6, M=8, edges="all"), "trk": dict(seed=3, n=12, M=6, edges="tracker", lifetime=5, removal=8)}[name]
+    s = syn.make_ba_scene(**kw)
+    poses, patches = run_ba(s, s["t0"], s["t1"], 1, patches_est=s["patches_est"], mu=2.0)
+    o = oracle.ba_forward(s["poses"], s["patches"], s["intrinsics"], s["target"], s["weight"], s["lmbda"], s["ii"], s["jj"],
+                          s["kk"], s["t0"], s["t1"], 1, patches_est=s["patches_est"], mu=2.0, mode=oracle.F64)
+    assert np.abs(poses - o["poses"]).max() < 1e-4
+    assert np.abs(patches[:, 2, 0, 0] - o["patches"][:, 2, 0, 0]).max() < 1e-3
+    rp = golden["pyba_ref"][f"{name}_prior_poses"]  # the reference's own dpvo/ba.py
+    assert np.abs(poses[:, :3] - rp[:, :3]).max() < 3e-4
+
+
+def test_ba_not_spd_raises_and_recovers(syn):
+    _, cb = pkg().native_modules()
+    s = syn.make_ba_scene(seed=0, n=6, M=8, edges="all")
+    bad = dict(s); bad["weight"] = np.full_like(s["weight"], np.nan)
+    with pytest.raises(RuntimeError):
+        run_ba(bad, s["t0"], s["t1"], 2)
+    poses, _ = run_ba(s, s["t0"], s["t1"], 2)  # status word was cleared: next call is healthy
+    assert np.isfinite(poses).all()
+    with pytest.raises(IndexError):
+        worse = dict(s); worse["kk"] = s["kk"].copy(); worse["kk"][3] = 10 ** 7
+        run_ba(worse, s["t0"], s["t1"], 2)
+
+
+@pytest.mark.parametrize("name", ["win", "trk", "off"])
+def test_reproject_and_neighbors_match_reference(golden, name):
+    _, cb = pkg().native_modules()
+    g = golden["ba_ref"]
+    s = _golden_scene(g, name)
+    rp = cb.reproject(dev(s["poses"]), dev(s["patches"]), dev(s["intrinsics"]), dev(s["ii"]), dev(s["jj"]), dev(s["kk"]))
+    assert tuple(rp.shape) == g[f"{name}_reproject"].shape
+    np.testing.assert_allclose(rp.cpu().numpy(), g[f"{name}_reproject"], rtol=1e-4, atol=2e-3)
+    ix, jx = cb.neighbors(dev(s["kk"]), dev(s["jj"]))
+    assert ix.dtype == torch.int64 and ix.is_cuda
+    assert np.array_equal(ix.cpu().numpy(), g[f"{name}_nb_ix"]) and np.array_equal(jx.cpu().numpy(), g[f"{name}_nb_jx"])
+
+
+def test_neighbors_bit_exact_random_and_full_size(golden, syn):
+    _, cb = pkg().native_modules()
+    g = golden["ba_ref"]
+    ix, jx = cb.neighbors(dev(g["nb_rand_ii"]), dev(g["nb_rand_jj"]))
+    assert np.array_equal(ix.cpu().numpy(), g["nb_rand_ix"]) and np.array_equal(jx.cpu().numpy(), g["nb_rand_jx"])
+    ii, jj, kk = syn.tracker_edges(40, 96)
+    rng = np.random.default_rng(5)
+    perm = rng.permutation(len(kk))
+    for a, b in ((kk, jj), (kk[perm], jj[perm]), (kk + 700000, jj)):
+        ix, jx = cb.neighbors(dev(a), dev(b))
+        oi, oj = oracle.neighbors(a, b)
+        assert np.array_equal(ix.cpu().numpy(), oi) and np.array_equal(jx.cpu().numpy(), oj)
+
+
+def test_solve_system_matches_reference(golden):
+    _, cb = pkg().native_modules()
+    g = golden["ba_ref"]
+    for tag, freen in (("full", -1), ("free4", 4)):
+        d, = cb.solve_system(dev(g["pgo_Ji"]), dev(g["pgo_Jj"]), dev(g["pgo_ii"]), dev(g["pgo_jj"]), dev(g["pgo_res"]), 1e-4, 1e-4, freen)
+        assert d.is_cuda
+        assert np.abs(d.cpu().numpy() - g[f"pgo_{tag}_delta"]).max() < 1e-5
+
+
+# ------------------------------------------------------------------------------------------------- C ABI, host buffers
+def test_c_abi_host_buffer_entries(golden, syn):
+    lib = pkg().capi()
+    assert lib.wv_device_supported() == 1
+    g = golden["corr_ref"]
+    f1, f2, co = (np.ascontiguousarray(g["f32_r3_" + k]) for k in ("fmap1", "fmap2", "coords"))
+    ii, jj = np.ascontiguousarray(g["f32_r3_ii"]), np.ascontiguousarray(g["f32_r3_jj"])
+    out = np.empty_like(g["f32_r3_out"])
+    rc = lib.wv_corr_forward_host(vp(f1), vp(f2), vp(co), vp(ii), vp(jj), vp(out), 1, 1, co.shape[1], f1.shape[2], 3, 3,
+                                  f1.shape[1], f2.shape[1], f2.shape[3], f2.shape[4], 3, None)
+    assert rc == 0
+    np.testing.assert_allclose(out, g["f32_r3_out"], rtol=1e-5, atol=1e-5)
+    s = syn.make_ba_scene(seed=0, n=6, M=8, edges="all")
+    poses, patches = s["poses"].copy(), s["patches"].copy()
+    st = ctypes.c_int(0)
+    f = lib.wv_ba_forward_host
+    f.argtypes = [ctypes.c_void_p] * 9 + [ctypes.c_int64] * 3 + [ctypes.c_int] * 4 + [ctypes.c_void_p, ctypes.c_float,
+                                                                                      ctypes.c_void_p, ctypes.c_void_p]
+    rc = f(vp(poses), vp(patches), vp(s["intrinsics"]), vp(s["target"]), vp(s["weight"]), vp(s["lmbda"]), vp(s["ii"]), vp(s["jj"]),
+           vp(s["kk"]), len(s["kk"]), poses.shape[0], patches.shape[0], 3, s["t0"], s["t1"], 2, None, 2.0, ctypes.byref(st), None)
+    assert rc == 0 and st.value == 0
+    o = oracle.ba_forward(s["poses"], s["patches"], s["intrinsics"], s["target"], s["weight"], s["lmbda"], s["ii"], s["jj"],
+                          s["kk"], s["t0"], s["t1"], 2, mode=oracle.F64)
+    assert np.abs(poses - o["poses"]).max() < 1e-4

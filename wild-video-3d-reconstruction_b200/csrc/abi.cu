@@ -1,0 +1,161 @@
+// extern "C" surface of libwvb200.so (declared in include/wvb200.h): argument validation, dispatch between
+// the tiled sm_100a kernels and the generic ones, and the host-buffer convenience entries.
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <vector>
+
+#include "wv_common.cuh"
+
+namespace wv {
+int g_last_cuda_error = 0;
+
+int sm_count() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+      n = 148;
+  }
+  return n;
+}
+
+// corr_generic.cu
+int corr_forward_generic(const void*, const void*, const float*, const int64_t*, const int64_t*, void*, int, int, int, int,
+                         int, int, int, int, int, int, int, int*, cudaStream_t);
+int corr_backward_generic(const void*, const void*, const float*, const int64_t*, const int64_t*, const float*, float*,
+                          float*, int, int, int, int, int, int, int, int, int, int, int, int*, cudaStream_t);
+int patchify_forward(const void*, const float*, void*, int, int, int, int, int, int, int, cudaStream_t);
+int patchify_backward(const void*, const float*, float*, int, int, int, int, int, int, int, cudaStream_t);
+// corr_sm100.cu
+bool corr_tiled_supported(int dtype, int B, int E, int C, int PH, int PW, int n1, int n2, int H2, int W2, int R);
+size_t corr_tiled_workspace_bytes(int dtype, int B, int E, int C, int PH, int PW, int n1, int n2, int H2, int W2, int R);
+int corr_forward_tiled(const void*, const void*, const float*, const int64_t*, const int64_t*, void*, int, int, int, int,
+                       int, int, int, int, int, int, int, void*, size_t, int*, cudaStream_t);
+// ba_window.cu
+size_t ba_workspace_bytes(int64_t E, int64_t n_patches, int N);
+int ba_forward_window(float*, float*, const float*, const float*, const float*, const float*, const int64_t*,
+                      const int64_t*, const int64_t*, int64_t, int64_t, int64_t, int, int, int, int, const float*, float,
+                      void*, size_t, int*, cudaStream_t);
+int ba_reproject(const float*, const float*, const float*, const int64_t*, const int64_t*, const int64_t*, int64_t,
+                 int64_t, int64_t, int, float*, int*, cudaStream_t);
+int ba_neighbors(const int64_t*, const int64_t*, int64_t, int64_t, int64_t*, int64_t*, void*, size_t, int*, cudaStream_t);
+size_t plan_bytes(int64_t E, int64_t n_groups, int max_ctas);
+int plan_grid();
+}  // namespace wv
+
+using namespace wv;
+
+extern "C" {
+
+const char* wv_strerror(int code) {
+  switch (code) {
+    case WV_OK: return "ok";
+    case WV_EINVAL: return "invalid argument";
+    case WV_ECUDA: return "CUDA call failed";
+    case WV_EWORKSPACE: return "workspace too small";
+    case WV_EUNSUPPORTED: return "shape not supported by this build";
+    case 1: return "matrix not positive definite";
+    default: return "unknown error";
+  }
+}
+
+int wv_last_cuda_error(void) { return g_last_cuda_error; }
+
+int wv_device_supported(void) {
+  int dev = 0, major = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+  if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess) return 0;
+  return major == 10 ? 1 : 0;
+}
+
+static bool corr_args_ok(const void* f1, const void* f2, const float* co, const int64_t* ii, const int64_t* jj, int dtype,
+                         int B, int E, int C, int PH, int PW, int n1, int n2, int H2, int W2, int R) {
+  if (dtype != WV_F16 && dtype != WV_F32) return false;
+  if (B < 0 || E < 0 || C <= 0 || PH <= 0 || PW <= 0 || n1 <= 0 || n2 <= 0 || H2 <= 0 || W2 <= 0 || R < 0) return false;
+  if ((int64_t)B * E > 0 && (!f1 || !f2 || !co || !ii || !jj)) return false;
+  return true;
+}
+
+size_t wv_corr_workspace_bytes(int dtype, int B, int E, int C, int PH, int PW, int n1, int n2, int H2, int W2, int radius) {
+  if (!corr_tiled_supported(dtype, B, E, C, PH, PW, n1, n2, H2, W2, radius)) return 0;
+  return corr_tiled_workspace_bytes(dtype, B, E, C, PH, PW, n1, n2, H2, W2, radius);
+}
+
+int wv_corr_forward(const void* fmap1, const void* fmap2, const float* coords, const int64_t* ii, const int64_t* jj,
+                    void* out, int dtype, int B, int E, int C, int PH, int PW, int n1, int n2, int H2, int W2, int radius,
+                    void* workspace, size_t workspace_bytes, int* status, wv_stream_t stream) {
+  if (!corr_args_ok(fmap1, fmap2, coords, ii, jj, dtype, B, E, C, PH, PW, n1, n2, H2, W2, radius)) return WV_EINVAL;
+  if ((int64_t)B * E == 0) return WV_OK;
+  if (!out) return WV_EINVAL;
+  cudaStream_t st = as_stream(stream);
+  if (workspace && corr_tiled_supported(dtype, B, E, C, PH, PW, n1, n2, H2, W2, radius) &&
+      workspace_bytes >= corr_tiled_workspace_bytes(dtype, B, E, C, PH, PW, n1, n2, H2, W2, radius))
+    return corr_forward_tiled(fmap1, fmap2, coords, ii, jj, out, dtype, B, E, C, PH, PW, n1, n2, H2, W2, radius, workspace,
+                              workspace_bytes, status, st);
+  return corr_forward_generic(fmap1, fmap2, coords, ii, jj, out, dtype, B, E, C, PH, PW, n1, n2, H2, W2, radius, status, st);
+}
+
+int wv_corr_backward(const void* fmap1, const void* fmap2, const float* coords, const int64_t* ii, const int64_t* jj,
+                     const float* grad, float* fmap1_grad, float* fmap2_grad, int dtype, int B, int E, int C, int PH,
+                     int PW, int n1, int n2, int H2, int W2, int radius, int* status, wv_stream_t stream) {
+  if (!corr_args_ok(fmap1, fmap2, coords, ii, jj, dtype, B, E, C, PH, PW, n1, n2, H2, W2, radius)) return WV_EINVAL;
+  if ((int64_t)B * E == 0) return WV_OK;
+  if (!grad || !fmap1_grad || !fmap2_grad) return WV_EINVAL;
+  return corr_backward_generic(fmap1, fmap2, coords, ii, jj, grad, fmap1_grad, fmap2_grad, dtype, B, E, C, PH, PW, n1, n2,
+                               H2, W2, radius, status, as_stream(stream));
+}
+
+int wv_patchify_forward(const void* net, const float* coords, void* patches, int dtype, int B, int M, int C, int H, int W,
+                        int radius, wv_stream_t stream) {
+  if ((dtype != WV_F16 && dtype != WV_F32) || B < 0 || M < 0 || C <= 0 || H <= 0 || W <= 0 || radius < 0) return WV_EINVAL;
+  if ((int64_t)B * M == 0) return WV_OK;
+  if (!net || !coords || !patches) return WV_EINVAL;
+  return patchify_forward(net, coords, patches, dtype, B, M, C, H, W, radius, as_stream(stream));
+}
+
+int wv_patchify_backward(const void* gradient, const float* coords, float* net_grad, int dtype, int B, int M, int C, int H,
+                         int W, int radius, wv_stream_t stream) {
+  if ((dtype != WV_F16 && dtype != WV_F32) || B < 0 || M < 0 || C <= 0 || H <= 0 || W <= 0 || radius < 0) return WV_EINVAL;
+  if ((int64_t)B * M == 0) return WV_OK;
+  if (!gradient || !coords || !net_grad) return WV_EINVAL;
+  return patchify_backward(gradient, coords, net_grad, dtype, B, M, C, H, W, radius, as_stream(stream));
+}
+
+size_t wv_ba_workspace_bytes(int64_t E, int64_t n_patches, int n_free_poses) {
+  if (E < 0 || n_patches < 0 || n_free_poses < 0) return 0;
+  return ba_workspace_bytes(E, n_patches, n_free_poses);
+}
+
+int wv_ba_forward(float* poses, float* patches, const float* intrinsics, const float* target, const float* weight,
+                  const float* lmbda, const int64_t* ii, const int64_t* jj, const int64_t* kk, int64_t E, int64_t n_poses,
+                  int64_t n_patches, int P, int t0, int t1, int iterations, const float* patches_est, float mu,
+                  void* workspace, size_t workspace_bytes, int* status, wv_stream_t stream) {
+  if (E < 0 || n_poses <= 0 || n_patches <= 0 || P <= 0 || t0 < 0 || t1 < t0 || t1 > n_poses) return WV_EINVAL;
+  if (E >= (int64_t)1 << 31 || n_patches >= (int64_t)1 << 31) return WV_EUNSUPPORTED;
+  if (E == 0 || iterations <= 0) return WV_OK;
+  if (!poses || !patches || !intrinsics || !target || !weight || !lmbda || !ii || !jj || !kk || !workspace) return WV_EINVAL;
+  return ba_forward_window(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk, E, n_poses, n_patches, P, t0, t1,
+                           iterations, patches_est, mu, workspace, workspace_bytes, status, as_stream(stream));
+}
+
+int wv_ba_reproject(const float* poses, const float* patches, const float* intrinsics, const int64_t* ii, const int64_t* jj,
+                    const int64_t* kk, int64_t E, int64_t n_poses, int64_t n_patches, int P, float* coords, int* status,
+                    wv_stream_t stream) {
+  if (E < 0 || n_poses <= 0 || n_patches <= 0 || P <= 0) return WV_EINVAL;
+  if (E == 0) return WV_OK;
+  if (!poses || !patches || !intrinsics || !ii || !jj || !kk || !coords) return WV_EINVAL;
+  return ba_reproject(poses, patches, intrinsics, ii, jj, kk, E, n_poses, n_patches, P, coords, status, as_stream(stream));
+}
+
+int wv_neighbors(const int64_t* ii, const int64_t* jj, int64_t E, int64_t n_groups, int64_t* ix, int64_t* jx,
+                 void* workspace, size_t workspace_bytes, int* status, wv_stream_t stream) {
+  if (E < 0 || n_groups <= 0) return WV_EINVAL;
+  if (E >= (int64_t)1 << 31 || n_groups >= (int64_t)1 << 31) return WV_EUNSUPPORTED;
+  if (E == 0) return WV_OK;
+  if (!ii || !jj || !ix || !jx || !workspace) return WV_EINVAL;
+  return ba_neighbors(ii, jj, E, n_groups, ix, jx, workspace, workspace_bytes, status, as_stream(stream));
+}
+
+}  // extern "C"

@@ -1,0 +1,464 @@
+// Sliding-window bundle adjustment: ONE persistent cooperative kernel per cuda_ba.forward call.
+//
+// Replaces, per Gauss-Newton iteration, the reference's 5 zero_() launches, the atomics edge kernel
+// (dpvo/fastba/ba_cuda.cu:214-365: up to 340 global fp32 atomicAdds per edge onto a 6N x 6N matrix), the
+// ~20 ATen launches of the Schur complement / Cholesky (:492-526) and both retraction kernels (:160-211).
+//
+// Design (B200: 148 SMs, 1 CTA each, everything between HBM reads lives in shared memory):
+//   phase A  one warp per patch segment of the plan (ba_plan.cuh); a lane owns one edge.  The patch-level sums
+//            C_k, u_k, E_k are warp reductions; pose-block contributions go to a PER-WARP lower-triangular
+//            table in shared memory (lanes of a patch hit distinct target blocks -> plain read-modify-write,
+//            no atomics); the patch is eliminated on the spot, S_w -= q_k E_k E_k^T, so the dense 6N x Mp
+//            matrix E of the reference is never formed.  Warp tables are summed in fixed order per CTA.
+//   phase B  CTA partials are summed in fixed CTA order (grid-strided over the 6N(6N+1)/2 + 6N entries).
+//   phase C  every CTA factorises the same damped S in shared memory (redundant Cholesky: no broadcast, no
+//            extra grid sync, bitwise identical everywhere), back-substitutes its own patches' depths and
+//            retracts them; CTA 0 retracts the poses.
+// Summation order is a pure function of the edge list, so results are bitwise reproducible run to run
+// (the reference's atomics are not).  fp32 throughout, like the reference.
+#include <cooperative_groups.h>
+
+#include "ba_plan.cuh"
+#include "se3.cuh"
+
+namespace cg = cooperative_groups;
+
+namespace wv {
+
+static constexpr int kBaThreads = 256;
+static constexpr int kBaWarps = kBaThreads / 32;
+static constexpr int kMaxFree = 16;  // 6N <= 96: per-warp tables must fit shared memory
+
+struct BAArgs {
+  float* poses; float* patches; const float* intr; const float* target; const float* weight; const float* lmbda;
+  const int64_t* ii; const int64_t* jj;
+  const float* patches_est; float mu;
+  int P, t0, N, iterations;
+  Plan p;
+  float* partial;  // [grid][nS]
+  float* Sfull;    // [nS]
+  float* Ecols;    // [Mp_cap][6N]
+  float* qk;       // [Mp_cap]
+  float* uk;       // [Mp_cap]
+  int* status;
+};
+
+__device__ __forceinline__ int tri(int r, int c) { return ((r * (r + 1)) >> 1) + c; }  // r >= c
+
+// One residual row of one edge: add its pose-block terms to the warp table.
+//   a = (-Ji at block i, +Jj at block j); B += w a a^T, v += w r a   (ba_cuda.cu:293-316)
+// with_i: also add the (i,i) block / v_i here (serialised slow path); otherwise the caller reduces them.
+__device__ __forceinline__ void scatter_row(float* S, float* y, int fi, int fj, bool free_i, bool free_j,
+                                            const float* Ji, const float* Jj, float w, float r, bool with_i) {
+  if (free_j) {
+    const int b = 6 * fj;
+#pragma unroll
+    for (int a = 0; a < 6; a++) {
+#pragma unroll
+      for (int c = 0; c <= a; c++) S[tri(b + a, b + c)] += w * Jj[a] * Jj[c];
+      y[b + a] += w * r * Jj[a];
+    }
+  }
+  if (free_i && free_j) {
+    if (fi == fj) {
+      const int b = 6 * fi;
+#pragma unroll
+      for (int a = 0; a < 6; a++)
+#pragma unroll
+        for (int c = 0; c <= a; c++) S[tri(b + a, b + c)] -= w * (Ji[a] * Jj[c] + Jj[a] * Ji[c]);
+    } else if (fi > fj) {
+#pragma unroll
+      for (int a = 0; a < 6; a++)
+#pragma unroll
+        for (int c = 0; c < 6; c++) S[tri(6 * fi + a, 6 * fj + c)] -= w * Ji[a] * Jj[c];
+    } else {
+#pragma unroll
+      for (int a = 0; a < 6; a++)
+#pragma unroll
+        for (int c = 0; c < 6; c++) S[tri(6 * fj + c, 6 * fi + a)] -= w * Ji[a] * Jj[c];
+    }
+  }
+  if (with_i && free_i) {
+    const int b = 6 * fi;
+#pragma unroll
+    for (int a = 0; a < 6; a++) {
+#pragma unroll
+      for (int c = 0; c <= a; c++) S[tri(b + a, b + c)] += w * Ji[a] * Ji[c];
+      y[b + a] -= w * r * Ji[a];
+    }
+  }
+}
+
+struct EdgeTerms {  // both residual rows of one edge
+  float Ji[2][6], Jj[2][6], Jz[2], w[2], r[2];
+};
+
+// projection, residual, validity mask and Jacobians of one edge (ba_cuda.cu:242-291, 325-331)
+__device__ __forceinline__ void edge_terms(const BAArgs& a, int e, int ix, int jx, float px, float py, float pd,
+                                           float fx, float fy, float cx, float cy, EdgeTerms& T) {
+  const float* Pi = a.poses + 7 * (size_t)ix;
+  const float* Pj = a.poses + 7 * (size_t)jx;
+  const Vec3 ti{Pi[0], Pi[1], Pi[2]}, tj{Pj[0], Pj[1], Pj[2]};
+  const Quat qi{Pi[3], Pi[4], Pi[5], Pi[6]}, qj{Pj[3], Pj[4], Pj[5], Pj[6]};
+  Vec3 tij; Quat qij;
+  relative_pose(ti, qi, tj, qj, tij, qij);
+  const Vec3 Xi{(px - cx) / fx, (py - cy) / fy, 1.f};
+  const Vec3 Rx = rotate(qij, Xi);
+  const float W = pd;
+  const float X = Rx.x + W * tij.x, Y = Rx.y + W * tij.y, Z = Rx.z + W * tij.z;
+  const float d = (Z >= 0.2f) ? 1.f / Z : 0.f;
+  const float d2 = d * d;
+  const float x1 = fx * (X / Z) + cx, y1 = fy * (Y / Z) + cy;
+  const float tx = a.target[2 * (size_t)e], ty = a.target[2 * (size_t)e + 1];
+  const float rx = tx - x1, ry = ty - y1;
+  const bool ok = (sqrtf(rx * rx + ry * ry) < 128.f) && (Z > 0.2f) && (x1 > -64.f) && (y1 > -64.f) &&
+                  (x1 < 2.f * cx + 64.f) && (y1 < 2.f * cy + 64.f);
+  const float m = ok ? 1.f : 0.f;
+  T.r[0] = rx; T.r[1] = ry;
+  T.w[0] = m * a.weight[2 * (size_t)e]; T.w[1] = m * a.weight[2 * (size_t)e + 1];
+  T.Jz[0] = fx * (tij.x * d - tij.z * (X * d2));
+  T.Jz[1] = fy * (tij.y * d - tij.z * (Y * d2));
+  T.Jj[0][0] = fx * W * d; T.Jj[0][1] = 0.f; T.Jj[0][2] = fx * -X * W * d2;
+  T.Jj[0][3] = fx * -X * Y * d2; T.Jj[0][4] = fx * (1.f + X * X * d2); T.Jj[0][5] = fx * -Y * d;
+  T.Jj[1][0] = 0.f; T.Jj[1][1] = fy * W * d; T.Jj[1][2] = fy * -Y * W * d2;
+  T.Jj[1][3] = fy * (-1.f - Y * Y * d2); T.Jj[1][4] = fy * (X * Y * d2); T.Jj[1][5] = fy * X * d;
+  adjoint_T(tij, qij, T.Jj[0], T.Ji[0]);
+  adjoint_T(tij, qij, T.Jj[1], T.Ji[1]);
+}
+
+__global__ void __launch_bounds__(kBaThreads, 1) ba_window_kernel(BAArgs a) {
+  extern __shared__ float sm[];
+  cg::grid_group grid = cg::this_grid();
+  const int N = a.N, n6 = 6 * N, nT = (n6 * (n6 + 1)) >> 1, nS = nT + n6;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float* tabs = sm;                      // [kBaWarps][nS]  (S lower triangle | y)
+  float* myS = tabs + warp * nS;
+  float* myY = myS + nT;
+  float* myE = sm + kBaWarps * nS + warp * n6;  // E_k of the patch in flight
+  const int PP = a.P * a.P, ctr = (a.P / 2) * a.P + a.P / 2;
+  const float fx = a.intr[0], fy = a.intr[1], cx = a.intr[2], cy = a.intr[3];  // row 0 only (ba_cuda.cu:232-238)
+  const float lambda = a.lmbda[0];
+  const int Mp = a.p.hdr->Mp;
+  const int per = (Mp + (int)gridDim.x - 1) / (int)gridDim.x;
+  const int r_lo = min(Mp, (int)blockIdx.x * per), r_hi = min(Mp, r_lo + per);
+  const unsigned FULL = 0xffffffffu;
+
+  for (int itr = 0; itr < a.iterations; itr++) {
+    for (int t = threadIdx.x; t < kBaWarps * nS; t += blockDim.x) tabs[t] = 0.f;
+    __syncthreads();
+
+    // ------------------------------------------------------------------ phase A: edges -> tables
+    for (int r = r_lo + warp; r < r_hi; r += kBaWarps) {
+      const int id = a.p.kx[r], off = a.p.seg_off[r], n = a.p.seg_off[r + 1] - off;
+      const float* pc = a.patches + (size_t)id * 3 * PP;
+      const float px = pc[ctr], py = pc[PP + ctr], pd = pc[2 * PP + ctr];
+      for (int c = lane; c < n6; c += 32) myE[c] = 0.f;
+      __syncwarp();
+      float Csum = 0.f, usum = 0.f;
+      for (int base = 0; base < n; base += 32) {
+        const bool act = base + lane < n;
+        const int e = act ? a.p.eperm[off + base + lane] : 0;
+        const int ix = act ? (int)a.ii[e] : -1, jx = act ? (int)a.jj[e] : -2 - lane;
+        const int fi = ix - a.t0, fj = jx - a.t0;
+        const bool free_i = act && fi >= 0 && fi < N, free_j = act && fj >= 0 && fj < N;
+        EdgeTerms T;
+        if (act) {
+          edge_terms(a, e, ix, jx, px, py, pd, fx, fy, cx, cy, T);
+          Csum += T.w[0] * T.Jz[0] * T.Jz[0] + T.w[1] * T.Jz[1] * T.Jz[1];
+          usum += T.w[0] * T.r[0] * T.Jz[0] + T.w[1] * T.r[1] * T.Jz[1];
+        }
+        if (N == 0) continue;
+        // fast path: one source frame for the whole chunk, all target frames distinct
+        const int ix0 = __shfl_sync(FULL, ix, 0);
+        const bool uni = __all_sync(FULL, !act || ix == ix0);
+        const unsigned same = __match_any_sync(FULL, jx);
+        const bool dup = __any_sync(FULL, act && (same & ~(1u << lane)) != 0u);
+        if (uni && !dup) {
+          float II[21], vi[6], Ei[6];
+#pragma unroll
+          for (int t = 0; t < 21; t++) II[t] = 0.f;
+#pragma unroll
+          for (int t = 0; t < 6; t++) { vi[t] = 0.f; Ei[t] = 0.f; }
+          if (act) {
+#pragma unroll
+            for (int row = 0; row < 2; row++) {
+              scatter_row(myS, myY, fi, fj, free_i, free_j, T.Ji[row], T.Jj[row], T.w[row], T.r[row], false);
+              if (free_j) {
+#pragma unroll
+                for (int c = 0; c < 6; c++) myE[6 * fj + c] += T.w[row] * T.Jz[row] * T.Jj[row][c];
+              }
+              if (free_i) {
+                int t = 0;
+#pragma unroll
+                for (int p = 0; p < 6; p++) {
+#pragma unroll
+                  for (int c = 0; c <= p; c++) II[t++] += T.w[row] * T.Ji[row][p] * T.Ji[row][c];
+                  vi[p] += T.w[row] * T.r[row] * T.Ji[row][p];
+                  Ei[p] += T.w[row] * T.Jz[row] * T.Ji[row][p];
+                }
+              }
+            }
+          }
+          __syncwarp();
+          const int f0 = ix0 - a.t0;
+          if (f0 >= 0 && f0 < N) {  // (i,i) block, v_i, E_i: warp-reduced, then added by one lane each
+            const int b = 6 * f0;
+            int t = 0;
+#pragma unroll
+            for (int p = 0; p < 6; p++)
+#pragma unroll
+              for (int c = 0; c <= p; c++) {
+                const float v = warp_sum(II[t]);
+                if (lane == t) myS[tri(b + p, b + c)] += v;
+                t++;
+              }
+#pragma unroll
+            for (int p = 0; p < 6; p++) {
+              const float v = warp_sum(vi[p]);
+              if (lane == 21 + p) myY[b + p] -= v;
+              const float w = warp_sum(Ei[p]);
+              if (lane == p) myE[b + p] -= w;
+            }
+          }
+          __syncwarp();
+        } else {  // general graph: serialise the lanes of this chunk (deterministic, rare)
+          for (int l = 0; l < 32; l++) {
+            if (lane == l && act) {
+#pragma unroll
+              for (int row = 0; row < 2; row++) {
+                scatter_row(myS, myY, fi, fj, free_i, free_j, T.Ji[row], T.Jj[row], T.w[row], T.r[row], true);
+#pragma unroll
+                for (int c = 0; c < 6; c++) {
+                  if (free_j) myE[6 * fj + c] += T.w[row] * T.Jz[row] * T.Jj[row][c];
+                  if (free_i) myE[6 * fi + c] -= T.w[row] * T.Jz[row] * T.Ji[row][c];
+                }
+              }
+            }
+            __syncwarp();
+          }
+        }
+      }
+      // ---- eliminate the patch: C_k, u_k (+ depth prior, dpvo/ba.py:151-159), q_k, Schur update
+      float C = warp_sum(Csum), u = warp_sum(usum);
+      if (a.patches_est) {
+        const float dest = a.patches_est[(size_t)id * 3 * PP + 2 * PP + ctr];
+        if (dest > 0.f) { C += a.mu; u -= a.mu * (pd - dest); }
+      }
+      const float q = 1.f / (C + lambda);
+      if (lane == 0) { a.qk[r] = q; a.uk[r] = u; }
+      if (N > 0) {
+        for (int c = lane; c < n6; c += 32) a.Ecols[(size_t)r * n6 + c] = myE[c];
+        for (int pr = lane; pr < (n6 >> 1); pr += 32) {
+#pragma unroll
+          for (int h = 0; h < 2; h++) {
+            const int rr = h ? n6 - 1 - pr : pr;
+            const float er = q * myE[rr];
+            float* Sr = myS + tri(rr, 0);
+            for (int c = 0; c <= rr; c++) Sr[c] -= er * myE[c];
+            myY[rr] -= er * u;
+          }
+        }
+      }
+      __syncwarp();
+    }
+    __syncthreads();
+
+    bool failed = false;
+    if (N > 0) {
+      // ---------------------------------------------------------------- phase B: fixed-order reductions
+      for (int t = threadIdx.x; t < nS; t += blockDim.x) {
+        float s = 0.f;
+#pragma unroll
+        for (int w = 0; w < kBaWarps; w++) s += tabs[w * nS + t];
+        a.partial[(size_t)blockIdx.x * nS + t] = s;
+      }
+      grid.sync();
+      for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < nS; t += gridDim.x * blockDim.x) {
+        float s = 0.f;
+        for (int c = 0; c < (int)gridDim.x; c++) s += a.partial[(size_t)c * nS + t];
+        a.Sfull[t] = s;
+      }
+      grid.sync();
+      // ---------------------------------------------------------------- phase C: damped Cholesky (every CTA)
+      const int ld = n6 + 1;
+      float* A = sm;            // [n6][ld]
+      float* dg = A + n6 * ld;  // [n6]
+      float* bx = dg + n6;      // [n6] rhs -> solution
+      for (int t = threadIdx.x; t < n6 * n6; t += blockDim.x) {
+        const int rr = t / n6, cc = t % n6;
+        float s = a.Sfull[rr >= cc ? tri(rr, cc) : tri(cc, rr)];
+        if (rr == cc) s = s + (s * 1e-4f + 1.0f);  // S += I * (1e-4 * S + 1.0), ba_cuda.cu:517-518
+        A[rr * ld + cc] = s;
+      }
+      for (int t = threadIdx.x; t < n6; t += blockDim.x) bx[t] = a.Sfull[nT + t];
+      for (int j = 0; j < n6; j++) {
+        __syncthreads();
+        const float d = A[j * ld + j];
+        if (!(d > 0.f)) { failed = true; break; }  // same value in every thread of every CTA
+        const float dj = sqrtf(d);
+        if (threadIdx.x == 0) dg[j] = dj;
+        for (int i = j + 1 + threadIdx.x; i < n6; i += blockDim.x) A[i * ld + j] = A[i * ld + j] / dj;
+        __syncthreads();
+        const int m = n6 - j - 1;
+        for (int t = threadIdx.x; t < m * m; t += blockDim.x) {
+          const int i = j + 1 + t / m, k = j + 1 + t % m;
+          if (k <= i) A[i * ld + k] -= A[i * ld + j] * A[k * ld + j];
+        }
+      }
+      __syncthreads();
+      if (failed) {
+        if (blockIdx.x == 0 && threadIdx.x == 0) set_status(a.status, WV_STATUS_NOT_SPD);
+        break;
+      }
+      if (warp == 0) {  // L z = y, L^T x = z (column-oriented, one warp)
+        for (int i = 0; i < n6; i++) {
+          const float z = bx[i] / dg[i];
+          __syncwarp();
+          if (lane == 0) bx[i] = z;
+          for (int k = i + 1 + lane; k < n6; k += 32) bx[k] -= A[k * ld + i] * z;
+          __syncwarp();
+        }
+        for (int i = n6 - 1; i >= 0; i--) {
+          const float x = bx[i] / dg[i];
+          __syncwarp();
+          if (lane == 0) bx[i] = x;
+          for (int k = lane; k < i; k += 32) bx[k] -= A[i * ld + k] * x;
+          __syncwarp();
+        }
+      }
+      __syncthreads();
+      // depth back-substitution dZ = Q (u - E^T dX) and patch retraction for this CTA's patches
+      for (int r = r_lo + threadIdx.x; r < r_hi; r += blockDim.x) {
+        const float* Ek = a.Ecols + (size_t)r * n6;
+        float s = 0.f;
+        for (int c = 0; c < n6; c++) s += Ek[c] * bx[c];
+        const float dz = a.qk[r] * (a.uk[r] - s);
+        float* pdz = a.patches + (size_t)a.p.kx[r] * 3 * PP + 2 * PP;
+        float dd = pdz[0] + dz;
+        dd = (dd > 20.f) ? 1.0f : dd;  // patch_retr_kernel, ba_cuda.cu:200-203
+        dd = fmaxf(dd, 1e-4f);
+        for (int t = 0; t < PP; t++) pdz[t] = dd;
+      }
+      if (blockIdx.x == 0 && threadIdx.x < N) {  // pose_retr_kernel, ba_cuda.cu:160-188
+        float* Pp = a.poses + 7 * (size_t)(a.t0 + threadIdx.x);
+        Vec3 t{Pp[0], Pp[1], Pp[2]};
+        Quat q{Pp[3], Pp[4], Pp[5], Pp[6]};
+        se3_retract(bx + 6 * threadIdx.x, t, q);
+        Pp[0] = t.x; Pp[1] = t.y; Pp[2] = t.z; Pp[3] = q.x; Pp[4] = q.y; Pp[5] = q.z; Pp[6] = q.w;
+      }
+      grid.sync();
+    } else {  // structure-only (ba_cuda.cu:494-506): dZ = Q u
+      for (int r = r_lo + threadIdx.x; r < r_hi; r += blockDim.x) {
+        float* pdz = a.patches + (size_t)a.p.kx[r] * 3 * PP + 2 * PP;
+        float dd = pdz[0] + a.qk[r] * a.uk[r];
+        dd = (dd > 20.f) ? 1.0f : dd;
+        dd = fmaxf(dd, 1e-4f);
+        for (int t = 0; t < PP; t++) pdz[t] = dd;
+      }
+      __syncthreads();
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// reproject: fused per-edge projection of all PxP pixels, no depth clamp (ba_cuda.cu:368-418)
+// ---------------------------------------------------------------------------------------------------
+__global__ void ba_reproject_kernel(const float* __restrict__ poses, const float* __restrict__ patches,
+                                    const float* __restrict__ intr, const int64_t* __restrict__ ii,
+                                    const int64_t* __restrict__ jj, const int64_t* __restrict__ kk, int64_t E,
+                                    int64_t n_poses, int64_t n_patches, int P, float* __restrict__ coords, int* status) {
+  const int PP = P * P;
+  const float fx = intr[0], fy = intr[1], cx = intr[2], cy = intr[3];
+  const int64_t total = E * PP;
+  for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t n = t / PP; const int q = (int)(t % PP);
+    const int64_t ix = ii[n], jx = jj[n], kx = kk[n];
+    float* o = coords + n * 2 * PP + q;
+    if (ix < 0 || ix >= n_poses || jx < 0 || jx >= n_poses || kx < 0 || kx >= n_patches) {
+      set_status(status, WV_STATUS_BAD_INDEX);
+      o[0] = 0.f; o[PP] = 0.f;
+      continue;
+    }
+    const float* Pi = poses + 7 * ix; const float* Pj = poses + 7 * jx;
+    Vec3 tij; Quat qij;
+    relative_pose({Pi[0], Pi[1], Pi[2]}, {Pi[3], Pi[4], Pi[5], Pi[6]}, {Pj[0], Pj[1], Pj[2]}, {Pj[3], Pj[4], Pj[5], Pj[6]}, tij, qij);
+    const float* pc = patches + kx * 3 * PP + q;
+    const Vec3 Xi{(pc[0] - cx) / fx, (pc[PP] - cy) / fy, 1.f};
+    const float W = pc[2 * PP];
+    const Vec3 Rx = rotate(qij, Xi);
+    const float X = Rx.x + W * tij.x, Y = Rx.y + W * tij.y, Z = Rx.z + W * tij.z;
+    o[0] = fx * (X / Z) + cx;
+    o[PP] = fy * (Y / Z) + cy;
+  }
+}
+
+int ba_reproject(const float* poses, const float* patches, const float* intr, const int64_t* ii, const int64_t* jj,
+                 const int64_t* kk, int64_t E, int64_t n_poses, int64_t n_patches, int P, float* coords, int* status,
+                 cudaStream_t st) {
+  if (E == 0) return WV_OK;
+  const int64_t total = E * P * P;
+  int64_t g = (total + 255) / 256;
+  const int64_t cap = (int64_t)sm_count() * 16;
+  if (g > cap) g = cap;
+  ba_reproject_kernel<<<(int)g, 256, 0, st>>>(poses, patches, intr, ii, jj, kk, E, n_poses, n_patches, P, coords, status);
+  WV_LAUNCH_CHECK();
+  return WV_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// host side of cuda_ba.forward (windowed path) and cuda_ba.neighbors
+// ---------------------------------------------------------------------------------------------------
+static inline size_t al256(size_t x) { return (x + 255) & ~(size_t)255; }
+int plan_grid();  // ba_plan.cu
+
+size_t ba_workspace_bytes(int64_t E, int64_t n_patches, int N) {
+  const int G = plan_grid();
+  const int64_t n6 = 6 * (int64_t)N, nS = n6 * (n6 + 1) / 2 + n6;
+  const int64_t mp_cap = E < n_patches ? E : n_patches;
+  return plan_bytes(E, n_patches, G) + al256(sizeof(float) * (size_t)(G * nS + 1)) + al256(sizeof(float) * (size_t)(nS + 1)) +
+         al256(sizeof(float) * (size_t)(mp_cap * n6 + 1)) + 2 * al256(sizeof(float) * (size_t)(mp_cap + 1));
+}
+
+int ba_forward_window(float* poses, float* patches, const float* intr, const float* target, const float* weight,
+                      const float* lmbda, const int64_t* ii, const int64_t* jj, const int64_t* kk, int64_t E,
+                      int64_t n_poses, int64_t n_patches, int P, int t0, int t1, int iterations,
+                      const float* patches_est, float mu, void* ws, size_t ws_bytes, int* status, cudaStream_t st) {
+  const int N = t1 - t0;
+  if (N > kMaxFree) return WV_EUNSUPPORTED;
+  if (E == 0 || iterations <= 0) return WV_OK;
+  if (ws_bytes < ba_workspace_bytes(E, n_patches, N)) return WV_EWORKSPACE;
+  const int G = plan_grid();
+  const int n6 = 6 * N, nS = n6 * (n6 + 1) / 2 + n6;
+  BAArgs a{};
+  char* b = (char*)ws;
+  size_t o = plan_carve(&a.p, ws, E, n_patches, G);
+  auto take = [&](size_t bytes) { void* r = b + o; o += al256(bytes); return r; };
+  a.partial = (float*)take(sizeof(float) * (size_t)(G * nS + 1));
+  a.Sfull = (float*)take(sizeof(float) * (size_t)(nS + 1));
+  a.Ecols = (float*)take(sizeof(float) * (size_t)(a.p.Mp_cap * n6 + 1));
+  a.qk = (float*)take(sizeof(float) * (size_t)(a.p.Mp_cap + 1));
+  a.uk = (float*)take(sizeof(float) * (size_t)(a.p.Mp_cap + 1));
+  a.poses = poses; a.patches = patches; a.intr = intr; a.target = target; a.weight = weight; a.lmbda = lmbda;
+  a.ii = ii; a.jj = jj; a.patches_est = patches_est; a.mu = mu; a.P = P; a.t0 = t0; a.N = N; a.iterations = iterations;
+  a.status = status;
+  int rc = plan_build(a.p, kk, jj, ii, n_poses, nullptr, nullptr, status, st);
+  if (rc != WV_OK) return rc;
+  const size_t smem = sizeof(float) * (size_t)(kBaWarps * nS + kBaWarps * n6 + 64);
+  if (smem > 48 * 1024)
+    WV_CUDA_TRY(cudaFuncSetAttribute(ba_window_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  void* args[] = {&a};
+  WV_CUDA_TRY(cudaLaunchCooperativeKernel((const void*)ba_window_kernel, dim3(G), dim3(kBaThreads), args, smem, st));
+  return WV_OK;
+}
+
+int ba_neighbors(const int64_t* g, const int64_t* jj, int64_t E, int64_t n_groups, int64_t* ix, int64_t* jx, void* ws,
+                 size_t ws_bytes, int* status, cudaStream_t st) {
+  if (E == 0) return WV_OK;
+  const int G = plan_grid();
+  if (ws_bytes < plan_bytes(E, n_groups, G)) return WV_EWORKSPACE;
+  Plan p;
+  plan_carve(&p, ws, E, n_groups, G);
+  return plan_build(p, g, jj, nullptr, 0, ix, jx, status, st);
+}
+
+}  // namespace wv

@@ -1,0 +1,135 @@
+// torch extension `cuda_ba`: same module name and m.def table as the reference's dpvo/fastba/ba.cpp:236-241
+// (forward / neighbors / reproject / solve_system), so dpvo/fastba/ba.py:2 and
+// dpvo/loop_closure/optim_utils.py:1 import it unchanged.  `forward` additionally takes two OPTIONAL trailing
+// arguments (patches_est, mu) for the depth-prior term of dpvo/ba.py:151-159; the 12-argument call is the
+// reference behaviour.
+#include "bind_common.h"
+
+using namespace wvbind;
+
+namespace {
+
+torch::Tensor workspace(const torch::Device& dev, size_t bytes) {
+  // grown on demand, kept per device: the plan never needs it cleared (ba_plan.cuh)
+  static std::map<int, torch::Tensor> ws;
+  auto it = ws.find(dev.index());
+  if (it == ws.end() || (size_t)it->second.numel() < bytes) {
+    ws[dev.index()] = torch::empty({(int64_t)(bytes + (bytes >> 2) + 4096)}, torch::dtype(torch::kUInt8).device(dev));
+    it = ws.find(dev.index());
+  }
+  return it->second;
+}
+
+void check_f32c(const torch::Tensor& t, const char* name) {
+  check_cuda(t, name);
+  TORCH_CHECK(t.scalar_type() == torch::kFloat, "cuda_ba: ", name, " must be float32");
+  TORCH_CHECK(t.is_contiguous(), "cuda_ba: ", name, " must be contiguous");
+}
+
+torch::Tensor idx(const torch::Tensor& t, const char* name) {
+  check_cuda(t, name);
+  TORCH_CHECK(t.scalar_type() == torch::kLong, "cuda_ba: ", name, " must be int64");
+  return t.contiguous().view({-1});
+}
+
+std::vector<torch::Tensor> ba_forward(torch::Tensor poses, torch::Tensor patches, torch::Tensor intrinsics, torch::Tensor target,
+                                      torch::Tensor weight, torch::Tensor lmbda, torch::Tensor ii, torch::Tensor jj,
+                                      torch::Tensor kk, int t0, int t1, int iterations,
+                                      c10::optional<torch::Tensor> patches_est, double mu) {
+  check_f32c(poses, "poses"); check_f32c(patches, "patches"); check_f32c(intrinsics, "intrinsics");
+  TORCH_CHECK(patches.dim() >= 4, "cuda_ba: patches must be [..., 3, P, P]");
+  c10::cuda::CUDAGuard guard(poses.device());
+  const int P = patches.size(-1);
+  const int64_t n_poses = poses.numel() / 7, n_patches = patches.numel() / (3 * P * P);
+  torch::Tensor tg = target.to(torch::kFloat).contiguous().view({-1, 2}), wt = weight.to(torch::kFloat).contiguous().view({-1, 2});
+  torch::Tensor lm = lmbda.to(torch::kFloat).contiguous().view({-1});
+  check_cuda(tg, "target"); check_cuda(wt, "weight"); check_cuda(lm, "lmbda");
+  torch::Tensor iic = idx(ii, "ii"), jjc = idx(jj, "jj"), kkc = idx(kk, "kk");
+  const int64_t E = iic.numel();
+  TORCH_CHECK(jjc.numel() == E && kkc.numel() == E && tg.size(0) == E && wt.size(0) == E, "cuda_ba: inconsistent edge count");
+  TORCH_CHECK(t0 >= 0 && t1 >= t0 && t1 <= n_poses, "cuda_ba: bad pose window [t0, t1)");
+  const float* est = nullptr;
+  torch::Tensor estc;
+  if (patches_est.has_value() && patches_est->defined()) {
+    estc = patches_est->to(torch::kFloat).contiguous();
+    TORCH_CHECK(estc.numel() == patches.numel() && estc.is_cuda(), "cuda_ba: patches_est must match patches");
+    est = estc.data_ptr<float>();
+  }
+  if (E == 0 || iterations <= 0) return {};
+  const size_t wsb = wv_ba_workspace_bytes(E, n_patches, t1 - t0);
+  torch::Tensor ws = workspace(poses.device(), wsb);
+  check_rc(wv_ba_forward(poses.data_ptr<float>(), patches.data_ptr<float>(), intrinsics.data_ptr<float>(), tg.data_ptr<float>(),
+                         wt.data_ptr<float>(), lm.data_ptr<float>(), iic.data_ptr<int64_t>(), jjc.data_ptr<int64_t>(),
+                         kkc.data_ptr<int64_t>(), E, n_poses, n_patches, P, t0, t1, iterations, est, (float)mu, ws.data_ptr(),
+                         (size_t)ws.numel(), status_word(poses.device()).data_ptr<int>(), current_stream()),
+           "cuda_ba.forward");
+  // The reference raises from torch::linalg::cholesky inside this call (dpvo/dpvo.py:733 lets it propagate);
+  // reading the status word costs one host sync.  WVB200_ASYNC=1 skips it (capture-safe, errors stay sticky).
+  if (!env_flag("WVB200_ASYNC")) raise_on_status(poses.device(), "cuda_ba.forward");
+  return {};
+}
+
+std::vector<torch::Tensor> neighbors(torch::Tensor ii, torch::Tensor jj) {
+  torch::Tensor iic = idx(ii, "ii"), jjc = idx(jj, "jj");
+  TORCH_CHECK(iic.numel() == jjc.numel(), "neighbors: ii and jj must have the same length");
+  c10::cuda::CUDAGuard guard(iic.device());
+  const int64_t E = iic.numel();
+  torch::Tensor ix = torch::empty({E}, iic.options()), jx = torch::empty({E}, iic.options());
+  if (E == 0) return {ix, jx};
+  const int64_t n_groups = (int64_t)1 << 22;  // ids (patch indices) must lie in a window of 4M values
+  const size_t wsb = wv_ba_workspace_bytes(E, n_groups, 0);
+  torch::Tensor ws = workspace(iic.device(), wsb);
+  check_rc(wv_neighbors(iic.data_ptr<int64_t>(), jjc.data_ptr<int64_t>(), E, n_groups, ix.data_ptr<int64_t>(),
+                        jx.data_ptr<int64_t>(), ws.data_ptr(), (size_t)ws.numel(), status_word(iic.device()).data_ptr<int>(),
+                        current_stream()),
+           "cuda_ba.neighbors");
+  if (env_flag("WVB200_CHECK_INDICES")) raise_on_status(iic.device(), "cuda_ba.neighbors");
+  return {ix, jx};
+}
+
+torch::Tensor reproject(torch::Tensor poses, torch::Tensor patches, torch::Tensor intrinsics, torch::Tensor ii, torch::Tensor jj,
+                        torch::Tensor kk) {
+  check_cuda(poses, "poses"); check_cuda(patches, "patches"); check_cuda(intrinsics, "intrinsics");
+  c10::cuda::CUDAGuard guard(poses.device());
+  torch::Tensor po = poses.to(torch::kFloat).contiguous(), pa = patches.to(torch::kFloat).contiguous(),
+                in = intrinsics.to(torch::kFloat).contiguous();
+  const int P = pa.size(-1);
+  const int64_t n_poses = po.numel() / 7, n_patches = pa.numel() / (3 * P * P);
+  torch::Tensor iic = idx(ii, "ii"), jjc = idx(jj, "jj"), kkc = idx(kk, "kk");
+  const int64_t E = iic.numel();
+  torch::Tensor coords = torch::empty({1, E, 2, P, P}, po.options());
+  check_rc(wv_ba_reproject(po.data_ptr<float>(), pa.data_ptr<float>(), in.data_ptr<float>(), iic.data_ptr<int64_t>(),
+                           jjc.data_ptr<int64_t>(), kkc.data_ptr<int64_t>(), E, n_poses, n_patches, P, coords.data_ptr<float>(),
+                           status_word(po.device()).data_ptr<int>(), current_stream()),
+           "cuda_ba.reproject");
+  return coords;
+}
+
+std::vector<torch::Tensor> solve_system(torch::Tensor J_Ginv_i, torch::Tensor J_Ginv_j, torch::Tensor ii, torch::Tensor jj,
+                                        torch::Tensor res, float ep, float lm, int freen) {
+  const torch::Device device = res.device();
+  torch::Tensor Ji = J_Ginv_i.to(torch::kCPU, torch::kFloat).contiguous(), Jj = J_Ginv_j.to(torch::kCPU, torch::kFloat).contiguous();
+  torch::Tensor ic = ii.to(torch::kCPU, torch::kLong).contiguous(), jc = jj.to(torch::kCPU, torch::kLong).contiguous();
+  torch::Tensor rs = res.to(torch::kCPU, torch::kFloat).contiguous();
+  const int64_t r = rs.size(0);
+  int64_t n = 0;
+  int rc = wv_solve_system_host(Ji.data_ptr<float>(), Jj.data_ptr<float>(), ic.data_ptr<int64_t>(), jc.data_ptr<int64_t>(),
+                                rs.data_ptr<float>(), r, ep, lm, freen, nullptr, &n);
+  TORCH_CHECK(rc == WV_OK, "solve_system: an edge connects a pose to itself or has a negative index");
+  torch::Tensor delta = torch::zeros({n, 7}, torch::dtype(torch::kFloat));
+  rc = wv_solve_system_host(Ji.data_ptr<float>(), Jj.data_ptr<float>(), ic.data_ptr<int64_t>(), jc.data_ptr<int64_t>(),
+                            rs.data_ptr<float>(), r, ep, lm, freen, delta.data_ptr<float>(), &n);
+  TORCH_CHECK(rc == WV_OK, "solve_system: ", wv_strerror(rc));
+  return {delta.to(device)};
+}
+
+}  // namespace
+
+PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
+  m.def("forward", &ba_forward, "BA forward operator", py::arg("poses"), py::arg("patches"), py::arg("intrinsics"),
+        py::arg("target"), py::arg("weight"), py::arg("lmbda"), py::arg("ii"), py::arg("jj"), py::arg("kk"), py::arg("t0"),
+        py::arg("t1"), py::arg("iterations"), py::arg("patches_est") = py::none(), py::arg("mu") = 2.0);
+  m.def("neighbors", &neighbors, "temporal neighboor indicies");
+  m.def("reproject", &reproject, "fused reprojection of all patch pixels");
+  m.def("solve_system", &solve_system, "solve system");
+}

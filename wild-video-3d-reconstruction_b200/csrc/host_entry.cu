@@ -1,0 +1,178 @@
+// Host-pointer entry points of include/wvb200.h: solve_system (CPU, fp64, like the reference) and the
+// host-buffer forms of corr / BA that wrap the device entry points with H2D / D2H copies on one stream.
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "wv_common.cuh"
+
+namespace {
+
+// Banded-aware dense LL^T in double on the lower triangle (row-major n x n); returns false if not SPD.
+// PGO systems here are <= a few thousand unknowns with a chain + a few loop edges, so the profile
+// (first non-zero column of every row) stays short and the factorisation is O(n * profile^2).
+bool profile_cholesky_solve(std::vector<double>& A, std::vector<double>& b, int64_t n) {
+  std::vector<int64_t> first(n);
+  for (int64_t i = 0; i < n; i++) {
+    int64_t f = i;
+    for (int64_t k = 0; k < i; k++)
+      if (A[i * n + k] != 0.0) { f = k; break; }
+    first[i] = f;
+  }
+  for (int64_t i = 0; i < n; i++) {  // fill-in can only lower a row's first column to that of rows it touches
+    for (int64_t j = first[i]; j <= i; j++) {
+      double s = A[i * n + j];
+      const int64_t k0 = std::max(first[i], first[j]);
+      for (int64_t k = k0; k < j; k++) s -= A[i * n + k] * A[j * n + k];
+      if (j < i) {
+        A[i * n + j] = s / A[j * n + j];
+      } else {
+        if (!(s > 0.0)) return false;
+        A[i * n + i] = sqrt(s);
+      }
+    }
+  }
+  for (int64_t i = 0; i < n; i++) {
+    double s = b[i];
+    for (int64_t k = first[i]; k < i; k++) s -= A[i * n + k] * b[k];
+    b[i] = s / A[i * n + i];
+  }
+  for (int64_t i = n - 1; i >= 0; i--) {
+    b[i] /= A[i * n + i];
+    const double x = b[i];
+    for (int64_t k = first[i]; k < i; k++) b[k] -= A[i * n + k] * x;
+  }
+  return true;
+}
+
+}  // namespace
+
+extern "C" {
+
+// dpvo/fastba/ba.cpp:174-234: A = J^T J from 7x7 blocks, A_dd += lm * A_dd + ep, b = -J^T res, solve in double.
+int wv_solve_system_host(const float* J_i, const float* J_j, const int64_t* ii, const int64_t* jj, const float* res,
+                         int64_t r, float ep, float lm, int freen, float* delta, int64_t* n_out) {
+  if (r < 0 || (r > 0 && (!J_i || !J_j || !ii || !jj || !res))) return WV_EINVAL;
+  int64_t n = 0;
+  for (int64_t x = 0; x < r; x++) {
+    if (ii[x] < 0 || jj[x] < 0 || ii[x] == jj[x]) return WV_EINVAL;  // the reference exit(1)s on i == j (:205-206)
+    n = std::max(n, std::max(ii[x], jj[x]) + 1);
+  }
+  if (n_out) *n_out = n;
+  if (!delta) return WV_OK;
+  const int64_t n7 = n * 7;
+  int64_t m = freen < 0 ? n7 : std::min<int64_t>(n7, (int64_t)freen * 7);  // solve(A, b, freen*7), ba.cpp:156-172
+  for (int64_t a = 0; a < n7; a++) delta[a] = 0.f;
+  if (m == 0) return WV_OK;
+  std::vector<double> A((size_t)m * m, 0.0), b((size_t)m, 0.0);
+  for (int64_t x = 0; x < r; x++) {
+    const int64_t cb[2] = {ii[x] * 7, jj[x] * 7};
+    const float* Jb[2] = {J_i + x * 49, J_j + x * 49};
+    for (int p = 0; p < 2; p++) {
+      if (cb[p] >= m) continue;
+      for (int q = 0; q < 2; q++) {
+        if (cb[q] >= m) continue;
+        for (int l = 0; l < 7; l++)
+          for (int c = 0; c < 7; c++) {
+            double s = 0;
+            for (int k = 0; k < 7; k++) s += (double)Jb[p][k * 7 + l] * (double)Jb[q][k * 7 + c];
+            A[(size_t)(cb[p] + l) * m + cb[q] + c] += s;
+          }
+      }
+      for (int l = 0; l < 7; l++) {
+        double s = 0;
+        for (int k = 0; k < 7; k++) s += (double)Jb[p][k * 7 + l] * (double)res[x * 7 + k];
+        b[(size_t)cb[p] + l] -= s;
+      }
+    }
+  }
+  for (int64_t d = 0; d < m; d++) { A[(size_t)d * m + d] += A[(size_t)d * m + d] * (double)lm; A[(size_t)d * m + d] += (double)ep; }
+  if (!profile_cholesky_solve(A, b, m)) return 1;
+  for (int64_t a = 0; a < m; a++) delta[a] = (float)b[a];
+  return WV_OK;
+}
+
+// ---- host-buffer forms ---------------------------------------------------------------------------
+#define HB_TRY(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) { rc = ::wv::cuda_fail(_e); goto done; } } while (0)
+
+int wv_corr_forward_host(const void* fmap1, const void* fmap2, const float* coords, const int64_t* ii, const int64_t* jj,
+                         void* out, int dtype, int B, int E, int C, int PH, int PW, int n1, int n2, int H2, int W2,
+                         int radius, wv_stream_t stream) {
+  if (dtype != WV_F16 && dtype != WV_F32) return WV_EINVAL;
+  if ((int64_t)B * E <= 0) return B < 0 || E < 0 ? WV_EINVAL : WV_OK;
+  cudaStream_t st = ::wv::as_stream(stream);
+  const size_t es = dtype == WV_F16 ? 2 : 4, T = 2 * radius + 1;
+  const size_t b1 = (size_t)B * n1 * C * PH * PW * es, b2 = (size_t)B * n2 * C * H2 * W2 * es;
+  const size_t bc = (size_t)B * E * 2 * PH * PW * 4, bi = (size_t)E * 8, bo = (size_t)B * E * T * T * PH * PW * es;
+  const size_t bw = wv_corr_workspace_bytes(dtype, B, E, C, PH, PW, n1, n2, H2, W2, radius);
+  char* d = nullptr;
+  int rc = WV_OK, status = 0;
+  auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
+  const size_t o1 = 0, o2 = o1 + al(b1), oc = o2 + al(b2), oi = oc + al(bc), oj = oi + al(bi), oo = oj + al(bi),
+               os = oo + al(bo), ow = os + 256, total = ow + al(bw);
+  HB_TRY(cudaMallocAsync((void**)&d, total, st));
+  HB_TRY(cudaMemcpyAsync(d + o1, fmap1, b1, cudaMemcpyHostToDevice, st));
+  HB_TRY(cudaMemcpyAsync(d + o2, fmap2, b2, cudaMemcpyHostToDevice, st));
+  HB_TRY(cudaMemcpyAsync(d + oc, coords, bc, cudaMemcpyHostToDevice, st));
+  HB_TRY(cudaMemcpyAsync(d + oi, ii, bi, cudaMemcpyHostToDevice, st));
+  HB_TRY(cudaMemcpyAsync(d + oj, jj, bi, cudaMemcpyHostToDevice, st));
+  HB_TRY(cudaMemsetAsync(d + os, 0, 4, st));
+  rc = wv_corr_forward(d + o1, d + o2, (const float*)(d + oc), (const int64_t*)(d + oi), (const int64_t*)(d + oj), d + oo,
+                       dtype, B, E, C, PH, PW, n1, n2, H2, W2, radius, bw ? d + ow : nullptr, bw, (int*)(d + os), stream);
+  if (rc != WV_OK) goto done;
+  HB_TRY(cudaMemcpyAsync(out, d + oo, bo, cudaMemcpyDeviceToHost, st));
+  HB_TRY(cudaMemcpyAsync(&status, d + os, 4, cudaMemcpyDeviceToHost, st));
+  HB_TRY(cudaStreamSynchronize(st));
+  if (status & WV_STATUS_BAD_INDEX) rc = WV_EINVAL;
+done:
+  if (d) cudaFreeAsync(d, st);
+  return rc;
+}
+
+int wv_ba_forward_host(float* poses, float* patches, const float* intrinsics, const float* target, const float* weight,
+                       const float* lmbda, const int64_t* ii, const int64_t* jj, const int64_t* kk, int64_t E,
+                       int64_t n_poses, int64_t n_patches, int P, int t0, int t1, int iterations, const float* patches_est,
+                       float mu, int* status_out, wv_stream_t stream) {
+  if (E < 0 || n_poses <= 0 || n_patches <= 0 || P <= 0 || t1 < t0) return WV_EINVAL;
+  if (status_out) *status_out = 0;
+  if (E == 0 || iterations <= 0) return WV_OK;
+  cudaStream_t st = ::wv::as_stream(stream);
+  auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
+  const size_t bp = (size_t)n_poses * 7 * 4, bq = (size_t)n_patches * 3 * P * P * 4, bn = (size_t)n_poses * 4 * 4;
+  const size_t bt = (size_t)E * 2 * 4, be = (size_t)E * 8, bw = wv_ba_workspace_bytes(E, n_patches, t1 - t0);
+  const size_t op = 0, oq = op + al(bp), oe = oq + al(bq), on = oe + (patches_est ? al(bq) : 0), ot = on + al(bn),
+               ow = ot + al(bt), ol = ow + al(bt), oi = ol + 256, oj = oi + al(be), ok = oj + al(be), os = ok + al(be),
+               owk = os + 256, total = owk + al(bw);
+  char* d = nullptr;
+  int rc = WV_OK, status = 0;
+  HB_TRY(cudaMallocAsync((void**)&d, total, st));
+  HB_TRY(cudaMemcpyAsync(d + op, poses, bp, cudaMemcpyHostToDevice, st));
+  HB_TRY(cudaMemcpyAsync(d + oq, patches, bq, cudaMemcpyHostToDevice, st));
+  if (patches_est) HB_TRY(cudaMemcpyAsync(d + oe, patches_est, bq, cudaMemcpyHostToDevice, st));
+  HB_TRY(cudaMemcpyAsync(d + on, intrinsics, bn, cudaMemcpyHostToDevice, st));
+  HB_TRY(cudaMemcpyAsync(d + ot, target, bt, cudaMemcpyHostToDevice, st));
+  HB_TRY(cudaMemcpyAsync(d + ow, weight, bt, cudaMemcpyHostToDevice, st));
+  HB_TRY(cudaMemcpyAsync(d + ol, lmbda, 4, cudaMemcpyHostToDevice, st));
+  HB_TRY(cudaMemcpyAsync(d + oi, ii, be, cudaMemcpyHostToDevice, st));
+  HB_TRY(cudaMemcpyAsync(d + oj, jj, be, cudaMemcpyHostToDevice, st));
+  HB_TRY(cudaMemcpyAsync(d + ok, kk, be, cudaMemcpyHostToDevice, st));
+  HB_TRY(cudaMemsetAsync(d + os, 0, 4, st));
+  rc = wv_ba_forward((float*)(d + op), (float*)(d + oq), (const float*)(d + on), (const float*)(d + ot),
+                     (const float*)(d + ow), (const float*)(d + ol), (const int64_t*)(d + oi), (const int64_t*)(d + oj),
+                     (const int64_t*)(d + ok), E, n_poses, n_patches, P, t0, t1, iterations,
+                     patches_est ? (const float*)(d + oe) : nullptr, mu, d + owk, bw, (int*)(d + os), stream);
+  if (rc != WV_OK) goto done;
+  HB_TRY(cudaMemcpyAsync(poses, d + op, bp, cudaMemcpyDeviceToHost, st));
+  HB_TRY(cudaMemcpyAsync(patches, d + oq, bq, cudaMemcpyDeviceToHost, st));
+  HB_TRY(cudaMemcpyAsync(&status, d + os, 4, cudaMemcpyDeviceToHost, st));
+  HB_TRY(cudaStreamSynchronize(st));
+  if (status_out) *status_out = status;
+done:
+  if (d) cudaFreeAsync(d, st);
+  return rc;
+}
+
+}  // extern "C"
