@@ -139,9 +139,17 @@ def test_ba_full_size_vs_oracle_and_deterministic(syn, M, edges):
     o = oracle.ba_forward(s["poses"], s["patches"], s["intrinsics"], s["target"], s["weight"], s["lmbda"], s["ii"], s["jj"],
                           s["kk"], t0, t1, 2, mode=oracle.F64)
     assert o["status"] == 0
+    # the same arithmetic in fp32 in the reference's own evaluation order: how far fp32 rounding alone moves the
+    # answer on this scene (the all-pairs window is ill conditioned: 4e-4; the tracker graph: 4e-6)
+    o32 = oracle.ba_forward(s["poses"], s["patches"], s["intrinsics"], s["target"], s["weight"], s["lmbda"], s["ii"], s["jj"],
+                            s["kk"], t0, t1, 2, mode=oracle.F32)
     poses, patches = run_ba(s, t0, t1, 2)
-    assert np.abs(poses[:, :3] - o["poses"][:, :3]).max() < 1e-4
-    assert quat_angle(poses[:, 3:], o["poses"][:, 3:]).max() < 1e-4
+    # tolerance (stated): translation max(1e-4, the reference-order fp32 deviation from fp64), rotation likewise in rad,
+    # inverse depth rtol 1e-3
+    tol_t = max(1e-4, np.abs(o32["poses"][:, :3] - o["poses"][:, :3]).max())
+    tol_r = max(1e-4, quat_angle(o32["poses"][:, 3:], o["poses"][:, 3:]).max())
+    assert np.abs(poses[:, :3] - o["poses"][:, :3]).max() < tol_t
+    assert quat_angle(poses[:, 3:], o["poses"][:, 3:]).max() < tol_r
     d, do = patches[:, 2, 0, 0], o["patches"][:, 2, 0, 0]
     assert np.abs(d - do).max() < 1e-3 * max(1.0, np.abs(do).max())
     poses2, patches2 = run_ba(s, t0, t1, 2)
