@@ -277,3 +277,88 @@ def test_c_abi_host_buffer_entries(golden, syn):
     o = oracle.ba_forward(s["poses"], s["patches"], s["intrinsics"], s["target"], s["weight"], s["lmbda"], s["ii"], s["jj"],
                           s["kk"], s["t0"], s["t1"], 2, mode=oracle.F64)
     assert np.abs(poses - o["poses"]).max() < 1e-4
+
+
+# ------------------------------------------------------------------------------------------------- tiled (TMA + mma) corr
+def _tiled(on):
+    class _Ctx:
+        def __enter__(self):
+            self.old = os.environ.get("WVB200_CORR_TILED")
+            os.environ["WVB200_CORR_TILED"] = "1" if on else "0"
+
+        def __exit__(self, *a):
+            if self.old is None:
+                del os.environ["WVB200_CORR_TILED"]
+            else:
+                os.environ["WVB200_CORR_TILED"] = self.old
+    return _Ctx()
+
+
+def _check_tiled(g, f, co, ii, jj):
+    """tiled path vs fp64 oracle (half an fp16 ulp of the result scale) and vs the generic kernel"""
+    with _tiled(True):
+        out = run_corr(g, f, co, ii, jj, 3, torch.float16)
+    with _tiled(False):
+        gen = run_corr(g, f, co, ii, jj, 3, torch.float16)
+    g16 = torch.from_numpy(g).half().float().numpy()
+    f16 = torch.from_numpy(f).half().float().numpy()
+    truth = oracle.corr_forward(g16, f16, co, ii, jj, 3, mode=oracle.F64)
+    scale = max(1.0, np.abs(truth).max())
+    assert np.abs(out - truth).max() <= 2.0 ** -10 * scale
+    # both paths accumulate in fp32 and round once: they may differ by one fp16 rounding where the sums differ in the last bits
+    assert np.abs(out - gen).max() <= 2.0 ** -9 * scale
+    return out
+
+
+@pytest.mark.parametrize("lvl", [0, 1])
+def test_corr_tiled_tracker_workload(syn, lvl):
+    w = syn.make_corr_workload(seed=1, M=8, pmem=12, n_frames=14, ht=24, wd=32, C=128, lifetime=6, removal=9, oob_frac=0.15)
+    fm, div = ((w["fmap0"], 1.0), (w["fmap1"], 4.0))[lvl]
+    _check_tiled(w["gmap"], fm, (w["coords"] / div).astype(np.float32), w["ii1"], w["jj1"])
+
+
+def test_corr_tiled_magnified_patches_and_odd_map(syn):
+    """patch spacing 1.0 .. 3.5 px: small box, large box and the direct-gather path; 23x31 map (odd HW: scalar restaging)"""
+    rng = np.random.default_rng(7)
+    n1, n2, H, W, E = 40, 5, 23, 31, 600
+    g = (0.25 * rng.standard_normal((1, n1, 128, 3, 3))).astype(np.float32)
+    f = (0.25 * rng.standard_normal((1, n2, 128, H, W))).astype(np.float32)
+    ctr = np.stack([rng.uniform(-6, W + 6, E), rng.uniform(-6, H + 6, E)], -1)
+    sp = rng.uniform(1.0, 3.5, E)
+    gy, gx = np.meshgrid(np.arange(-1, 2), np.arange(-1, 2), indexing="ij")
+    co = np.stack([ctr[:, 0, None, None] + sp[:, None, None] * gx, ctr[:, 1, None, None] + sp[:, None, None] * gy], 1)[None].astype(np.float32)
+    ii = rng.integers(0, n1, E); jj = rng.integers(0, n2, E)
+    ii[100:130] = ii[100]  # runs of edges that share a patch (A-fragment reuse)
+    out = _check_tiled(g, f, co, ii.astype(np.int64), jj.astype(np.int64))
+    assert np.abs(out).max() > 0.1
+
+
+def test_corr_tiled_batch_and_few_edges(syn):
+    """B = 2 and fewer edges than consumer warps"""
+    rng = np.random.default_rng(8)
+    n1, n2, H, W, E = 6, 3, 24, 32, 5
+    g = (0.25 * rng.standard_normal((2, n1, 128, 3, 3))).astype(np.float32)
+    f = (0.25 * rng.standard_normal((2, n2, 128, H, W))).astype(np.float32)
+    c = rng.uniform(2, 20, (2, E, 2))
+    gy, gx = np.meshgrid(np.arange(-1, 2), np.arange(-1, 2), indexing="ij")
+    co = np.stack([c[..., 0, None, None] + gx, c[..., 1, None, None] + gy], 2).astype(np.float32)
+    _check_tiled(g, f, co, rng.integers(0, n1, E).astype(np.int64), rng.integers(0, n2, E).astype(np.int64))
+
+
+def test_corr_tiled_bad_index_and_nonfinite(golden):
+    cc, _ = pkg().native_modules()
+    rng = np.random.default_rng(9)
+    g = dev((0.25 * rng.standard_normal((1, 4, 128, 3, 3))).astype(np.float32), torch.float16)
+    f = dev((0.25 * rng.standard_normal((1, 2, 128, 24, 32))).astype(np.float32), torch.float16)
+    co = np.full((1, 3, 2, 3, 3), 10.25, np.float32)
+    co[0, 1] = np.inf
+    os.environ["WVB200_CHECK_INDICES"] = "1"
+    try:
+        with _tiled(True):
+            out, = cc.forward(g, f, dev(co), torch.tensor([0, 1, 2], device="cuda"), torch.tensor([0, 1, 1], device="cuda"), 3)
+            torch.cuda.synchronize()
+            assert torch.isfinite(out[0, 0]).all() and torch.isfinite(out[0, 2]).all()
+            with pytest.raises(IndexError):
+                cc.forward(g, f, dev(co), torch.tensor([0, 9, 2], device="cuda"), torch.tensor([0, 1, 1], device="cuda"), 3)
+    finally:
+        del os.environ["WVB200_CHECK_INDICES"]

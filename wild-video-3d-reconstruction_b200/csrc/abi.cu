@@ -91,9 +91,11 @@ int wv_corr_forward(const void* fmap1, const void* fmap2, const float* coords, c
   if (!out) return WV_EINVAL;
   cudaStream_t st = as_stream(stream);
   if (workspace && corr_tiled_supported(dtype, B, E, C, PH, PW, n1, n2, H2, W2, radius) &&
-      workspace_bytes >= corr_tiled_workspace_bytes(dtype, B, E, C, PH, PW, n1, n2, H2, W2, radius))
-    return corr_forward_tiled(fmap1, fmap2, coords, ii, jj, out, dtype, B, E, C, PH, PW, n1, n2, H2, W2, radius, workspace,
-                              workspace_bytes, status, st);
+      workspace_bytes >= corr_tiled_workspace_bytes(dtype, B, E, C, PH, PW, n1, n2, H2, W2, radius)) {
+    const int rc = corr_forward_tiled(fmap1, fmap2, coords, ii, jj, out, dtype, B, E, C, PH, PW, n1, n2, H2, W2, radius, workspace,
+                                      workspace_bytes, status, st);
+    if (rc != WV_EUNSUPPORTED) return rc;  // e.g. a misaligned base pointer: the generic kernel takes any
+  }
   return corr_forward_generic(fmap1, fmap2, coords, ii, jj, out, dtype, B, E, C, PH, PW, n1, n2, H2, W2, radius, status, st);
 }
 
