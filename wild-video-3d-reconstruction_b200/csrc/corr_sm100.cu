@@ -44,7 +44,7 @@ constexpr int kRawStride = 152;                            // floats per patch-p
 constexpr int kRawBytes = kPP * kRawStride * 4;            // 5 472
 constexpr int kPatchBytes = kC * kPP * 2;                  // 2 304
 constexpr int kWarpBytes = kRawBytes + kPatchBytes;        // 7 776
-constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kConsumers * kWarpBytes + 2 * kStages * 8 + 64;
+constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kConsumers * kWarpBytes + (kConsumers + kStages) * 8 + 64;
 constexpr int kClamp = 1 << 20;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -60,6 +60,8 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t byt
 }
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   uint32_t ok;
+  long long t0 = 0;
+  int spins = 0;
   do {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
@@ -68,6 +70,12 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         : "=r"(ok)
         : "r"(bar), "r"(parity)
         : "memory");
+    // watchdog: a protocol bug must surface as a CUDA error in seconds, not as a hung GPU (4e9 cycles ~ 2 s)
+    if (!ok && (++spins & 0x3ff) == 0) {
+      const long long now = clock64();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > 4000000000LL) __trap();
+    }
   } while (!ok);
 }
 __device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2, int c3) {
@@ -208,12 +216,18 @@ corr_tiled_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_co
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* stages = smem;                                              // [kStages][2][kHalfBytes], 1024-B aligned
   uint8_t* warp_area = stages + kStages * kStageBytes;                 // [kConsumers][raw | patch]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(warp_area + kConsumers * kWarpBytes);  // full[kStages], empty[kStages]
+  // Barriers.  full[w]: one per CONSUMER WARP (not per stage) -- tile q goes to warp q % 8 and stage q % 4, so a warp's
+  // consecutive tiles reuse one stage and its barrier can never run a phase ahead of the warp; a per-stage barrier would be
+  // waited on by two warps that are a phase apart, which a parity wait cannot tell from "already complete".
+  // empty[s]: one per stage, waited on by the producer alone, in order.
+  uint64_t* bars = reinterpret_cast<uint64_t*>(warp_area + kConsumers * kWarpBytes);  // full[kConsumers], empty[kStages]
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + kStages);
+  const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + kConsumers);
+  static_assert(kConsumers % kStages == 0, "a warp's tiles must always land in the same stage");
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < kStages; s++) { mbar_init(full0 + 8 * s, 1); mbar_init(empty0 + 8 * s, 1); }
+    for (int w = 0; w < kConsumers; w++) mbar_init(full0 + 8 * w, 1);
+    for (int s = 0; s < kStages; s++) mbar_init(empty0 + 8 * s, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
@@ -237,7 +251,7 @@ corr_tiled_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_co
         kind = g.kind; x0 = g.x0; y0 = g.y0; slot = g.slot;
       }
       if (lane == 0) {
-        const uint32_t bar = full0 + 8 * s;
+        const uint32_t bar = full0 + 8 * w;
         if (kind <= 1) {
           const int box = kind == 0 ? kBoxSmall : kBoxLarge;
           const CUtensorMap* map = kind == 0 ? &map_small : &map_large;
@@ -264,9 +278,9 @@ corr_tiled_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_co
 
   for (int k = 0; k < per; k++) {
     const int q = k * kConsumers + warp, s = q % kStages;
-    const uint32_t fullb = full0 + 8 * s, emptyb = empty0 + 8 * s;
+    const uint32_t fullb = full0 + 8 * warp, emptyb = empty0 + 8 * s;
     if (k >= cnt) {  // padding slot of the ring: keep the protocol in step
-      mbar_wait(fullb, (q / kStages) & 1);
+      mbar_wait(fullb, k & 1);
       if (lane == 0) mbar_arrive(emptyb);
       continue;
     }
@@ -303,7 +317,7 @@ corr_tiled_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_co
       gr[0] = __int_as_float(wy * BX + wx); gr[1] = g.dx; gr[2] = g.dy;
     }
 
-    mbar_wait(fullb, (q / kStages) & 1);
+    mbar_wait(fullb, k & 1);
     if (g.kind <= 1) {
       // -------------------------------------------------------------- tensor-core contraction from the TMA tile
       const int npix = BX * BX, ntiles = (npix + 7) >> 3;
