@@ -171,11 +171,23 @@ struct EdgeGeom {
   long long patch; // warp-uniform: b * n1 + ii
 };
 
-__device__ __forceinline__ EdgeGeom edge_geom(const CorrParams& P, long long be, int lane) {
+// the raw global loads of one edge, issued one iteration ahead of their use (software prefetch)
+struct EdgeRaw { float cv; int64_t ix, jx; long long be; };
+
+__device__ __forceinline__ EdgeRaw edge_load(const CorrParams& P, long long be, int lane) {
+  EdgeRaw r;
+  const int e = (int)(be % P.E);
+  r.be = be;
+  r.ix = P.ii[e]; r.jx = P.jj[e];
+  r.cv = lane < 2 * kPP ? P.coords[be * (2 * kPP) + lane] : 0.f;
+  return r;
+}
+
+__device__ __forceinline__ EdgeGeom edge_geom(const CorrParams& P, const EdgeRaw& raw, int lane) {
   EdgeGeom g;
-  const int b = (int)(be / P.E), e = (int)(be % P.E);
-  const int64_t ix = P.ii[e], jx = P.jj[e];
-  const float cv = lane < 2 * kPP ? P.coords[be * (2 * kPP) + lane] : 0.f;
+  const int b = (int)(raw.be / P.E);
+  const int64_t ix = raw.ix, jx = raw.jx;
+  const float cv = raw.cv;
   const float x = __shfl_sync(0xffffffffu, cv, lane < kPP ? lane : 0);
   const float y = __shfl_sync(0xffffffffu, cv, lane < kPP ? lane + kPP : kPP);
   g.fx = clamp_floor(x); g.fy = clamp_floor(y);
@@ -203,6 +215,31 @@ __device__ __forceinline__ EdgeGeom edge_geom(const CorrParams& P, long long be,
   return g;
 }
 
+// the producer's view of an edge, computed by ONE lane (32 edges per warp pass, loads in flight together)
+__device__ __forceinline__ void edge_box(const CorrParams& P, long long be, int& kind, int& x0, int& y0, int& slot) {
+  const int b = (int)(be / P.E), e = (int)(be % P.E);
+  const int64_t ix = P.ii[e], jx = P.jj[e];
+  const float2* c2 = reinterpret_cast<const float2*>(P.coords + be * (2 * kPP));  // 72-B records: 8-byte aligned
+  float v[2 * kPP];
+#pragma unroll
+  for (int i = 0; i < kPP; i++) { const float2 t = c2[i]; v[2 * i] = t.x; v[2 * i + 1] = t.y; }
+  int mnx = kClamp * 2, mxx = -kClamp * 2, mny = kClamp * 2, mxy = -kClamp * 2;
+#pragma unroll
+  for (int p = 0; p < kPP; p++) {
+    const int fx = clamp_floor(v[p]), fy = clamp_floor(v[kPP + p]);
+    mnx = min(mnx, fx); mxx = max(mxx, fx); mny = min(mny, fy); mxy = max(mxy, fy);
+  }
+  x0 = mnx - kR; y0 = mny - kR;
+  const int wdt = mxx - mnx + kD, hgt = mxy - mny + kD;
+  const bool bad = ix < 0 || ix >= P.n1 || jx < 0 || jx >= P.n2;
+  const bool outside = x0 >= P.W || y0 >= P.H || x0 + wdt <= 0 || y0 + hgt <= 0;
+  if (bad || outside) kind = 3;
+  else if (wdt <= kBoxSmall && hgt <= kBoxSmall) kind = 0;
+  else if (wdt <= kBoxLarge && hgt <= kBoxLarge) kind = 1;
+  else kind = 2;
+  slot = bad ? 0 : b * P.n2 + (int)jx;
+}
+
 }  // namespace
 
 // ---------------------------------------------------------------------------------------------------
@@ -210,10 +247,41 @@ __device__ __forceinline__ EdgeGeom edge_geom(const CorrParams& P, long long be,
 // ---------------------------------------------------------------------------------------------------
 namespace {
 
+// NT (<= 4) pixel tiles of 8 px: D[16 x 8*NT] = A[16 x 128] . tile^T, B fragments double-buffered one 32-channel step ahead.
+// a0 / a1: this lane's ldmatrix address in tile 0 for chunks 0..3 / 4..7 of the 128-B rows (swizzle folded in).
+template <int NT>
+__device__ __forceinline__ void mma_group(uint32_t a0, uint32_t a1, const uint32_t (&A)[8][4], float* d0, float* d8, bool has8) {
+  float acc[NT][4];
+  uint32_t b[2][NT][4];
+#pragma unroll
+  for (int u = 0; u < NT; u++) {
+    acc[u][0] = 0.f; acc[u][1] = 0.f; acc[u][2] = 0.f; acc[u][3] = 0.f;
+    ldmatrix_x4(a0 + u * 1024, b[0][u][0], b[0][u][1], b[0][u][2], b[0][u][3]);
+  }
+#pragma unroll
+  for (int hq = 0; hq < 4; hq++) {  // channels 32*hq .. 32*hq+31 = k-steps 2*hq, 2*hq+1
+    if (hq < 3) {
+      const uint32_t an = (((hq + 1) & 1) ? a1 : a0) + ((hq + 1) >> 1) * kHalfBytes;
+#pragma unroll
+      for (int u = 0; u < NT; u++)
+        ldmatrix_x4(an + u * 1024, b[(hq + 1) & 1][u][0], b[(hq + 1) & 1][u][1], b[(hq + 1) & 1][u][2], b[(hq + 1) & 1][u][3]);
+    }
+#pragma unroll
+    for (int u = 0; u < NT; u++) mma_16816(acc[u], A[2 * hq], b[hq & 1][u][0], b[hq & 1][u][1]);
+#pragma unroll
+    for (int u = 0; u < NT; u++) mma_16816(acc[u], A[2 * hq + 1], b[hq & 1][u][2], b[hq & 1][u][3]);
+  }
+#pragma unroll
+  for (int u = 0; u < NT; u++) {
+    *reinterpret_cast<float2*>(d0 + 8 * u) = make_float2(acc[u][0], acc[u][1]);
+    if (has8) *reinterpret_cast<float2*>(d8 + 8 * u) = make_float2(acc[u][2], acc[u][3]);
+  }
+}
+
 __global__ void __launch_bounds__(kThreads, 1)
 corr_tiled_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_constant__ CUtensorMap map_large, const CorrParams P) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // stays a shared-space pointer (LDS/STS, not generic LD/ST)
   uint8_t* stages = smem;                                              // [kStages][2][kHalfBytes], 1024-B aligned
   uint8_t* warp_area = stages + kStages * kStageBytes;                 // [kConsumers][raw | patch]
   // Barriers.  full[w]: one per CONSUMER WARP (not per stage) -- tile q goes to warp q % 8 and stage q % 4, so a warp's
@@ -241,26 +309,32 @@ corr_tiled_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_co
   if (warp == kConsumers) {
     // ================================================================= producer
     const int total = per * kConsumers;
-    for (int q = 0; q < total; q++) {
-      const int w = q % kConsumers, k = q / kConsumers, s = q % kStages;
-      const int idx = w * per + k;
-      mbar_wait(empty0 + 8 * s, ((q / kStages) & 1) ^ 1);
+    for (int q0 = 0; q0 < total; q0 += 32) {
+      // every lane works out the box of one tile of this batch (their global loads overlap) ...
       int kind = 3, x0 = 0, y0 = 0, slot = 0;
-      if (idx < nt) {
-        const EdgeGeom g = edge_geom(P, lo + idx, lane);
-        kind = g.kind; x0 = g.x0; y0 = g.y0; slot = g.slot;
+      {
+        const int q = q0 + lane, idx = (q % kConsumers) * per + q / kConsumers;
+        if (q < total && idx < nt) edge_box(P, lo + idx, kind, x0, y0, slot);
       }
-      if (lane == 0) {
-        const uint32_t bar = full0 + 8 * w;
-        if (kind <= 1) {
-          const int box = kind == 0 ? kBoxSmall : kBoxLarge;
-          const CUtensorMap* map = kind == 0 ? &map_small : &map_large;
-          const uint32_t dst = smem_u32(stages + (size_t)s * kStageBytes);
-          mbar_arrive_expect_tx(bar, (uint32_t)(2 * box * box * 128));
-          tma_load_4d(dst, map, bar, 0, x0, y0, slot);
-          tma_load_4d(dst + kHalfBytes, map, bar, 64, x0, y0, slot);
-        } else {
-          mbar_arrive(bar);
+      // ... then lane 0 feeds the ring in order
+      const int nb = min(32, total - q0);
+      for (int i = 0; i < nb; i++) {
+        const int q = q0 + i, w = q % kConsumers, s = q % kStages;
+        const int kd = __shfl_sync(0xffffffffu, kind, i), bx = __shfl_sync(0xffffffffu, x0, i);
+        const int by = __shfl_sync(0xffffffffu, y0, i), sl = __shfl_sync(0xffffffffu, slot, i);
+        if (lane == 0) {
+          mbar_wait(empty0 + 8 * s, ((q / kStages) & 1) ^ 1);
+          const uint32_t bar = full0 + 8 * w;
+          if (kd <= 1) {
+            const int box = kd == 0 ? kBoxSmall : kBoxLarge;
+            const CUtensorMap* map = kd == 0 ? &map_small : &map_large;
+            const uint32_t dst = smem_u32(stages + (size_t)s * kStageBytes);
+            mbar_arrive_expect_tx(bar, (uint32_t)(2 * box * box * 128));
+            tma_load_4d(dst, map, bar, 0, bx, by, sl);
+            tma_load_4d(dst + kHalfBytes, map, bar, 64, bx, by, sl);
+          } else {
+            mbar_arrive(bar);
+          }
         }
       }
       __syncwarp();
@@ -269,12 +343,19 @@ corr_tiled_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_co
   }
 
   // =================================================================== consumers
-  float* rawD = reinterpret_cast<float*>(warp_area + (size_t)warp * kWarpBytes);  // [9][kRawStride]: cols 0..143 D, 144..147 geometry
+  float* rawD = reinterpret_cast<float*>(warp_area + (size_t)warp * kWarpBytes);  // [9][kRawStride]: cols 0..143 D, 144..146 geometry
   __half* patch = reinterpret_cast<__half*>(warp_area + (size_t)warp * kWarpBytes + kRawBytes);  // [128][9]
   const int g8 = lane >> 2, t4 = lane & 3;
+  const uint32_t lds_off0 = (uint32_t)((lane & 7) * 128 + ((((lane >> 3) ^ (lane & 7)) & 7) << 4));  // ldmatrix row + swizzled chunk
+  const uint32_t lds_off1 = lds_off0 ^ 64u;                                                            // chunks 4..7 of the 128-B row
+  float* const d0 = rawD + g8 * kRawStride + 2 * t4;
+  float* const d8 = rawD + 8 * kRawStride + 2 * t4;
   uint32_t A[8][4];
-  long long cur_patch = -1;
+  long long cur_patch = -1, pf_patch = -1;
+  uint4 pf[5];
   const int cnt = max(0, min(per, nt - warp * per));
+  EdgeRaw raw{};
+  if (cnt > 0) raw = edge_load(P, lo + warp * per, lane);
 
   for (int k = 0; k < per; k++) {
     const int q = k * kConsumers + warp, s = q % kStages;
@@ -285,14 +366,20 @@ corr_tiled_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_co
       continue;
     }
     const long long be = lo + warp * per + k;
-    const EdgeGeom g = edge_geom(P, be, lane);
+    const EdgeGeom g = edge_geom(P, raw, lane);
+    if (k + 1 < cnt) raw = edge_load(P, be + 1, lane);  // next edge's loads fly during this edge's work
 
-    // ---- A operand: the 3x3x128 source patch (reused while consecutive edges share it)
+    // ---- A operand: the 3x3x128 source patch (reused while consecutive edges share it; prefetched otherwise)
     if (g.kind != 3 && g.patch != cur_patch) {
-      const uint4* src = reinterpret_cast<const uint4*>(P.fmap1 + g.patch * (kC * kPP));
       uint4* dstp = reinterpret_cast<uint4*>(patch);
+      if (pf_patch != g.patch) {
+        const uint4* src = reinterpret_cast<const uint4*>(P.fmap1 + g.patch * (kC * kPP));
+#pragma unroll
+        for (int i = 0; i < 5; i++) if (lane + 32 * i < kPatchBytes / 16) pf[i] = src[lane + 32 * i];
+      }
       __syncwarp();
-      for (int t = lane; t < kPatchBytes / 16; t += 32) dstp[t] = src[t];
+#pragma unroll
+      for (int i = 0; i < 5; i++) if (lane + 32 * i < kPatchBytes / 16) dstp[lane + 32 * i] = pf[i];
       __syncwarp();
       const unsigned short* ps = reinterpret_cast<const unsigned short*>(patch);
 #pragma unroll
@@ -320,36 +407,17 @@ corr_tiled_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_co
     mbar_wait(fullb, k & 1);
     if (g.kind <= 1) {
       // -------------------------------------------------------------- tensor-core contraction from the TMA tile
-      const int npix = BX * BX, ntiles = (npix + 7) >> 3;
       const uint32_t st = smem_u32(stages + (size_t)s * kStageBytes);
-      const int m = lane >> 3, r = lane & 7;
-      for (int j0 = 0; j0 < ntiles; j0 += 4) {
-        float acc[4][4];
-#pragma unroll
-        for (int u = 0; u < 4; u++) { acc[u][0] = 0.f; acc[u][1] = 0.f; acc[u][2] = 0.f; acc[u][3] = 0.f; }
-#pragma unroll
-        for (int hq = 0; hq < 4; hq++) {  // hq = 2*half + q: channels 32*hq .. 32*hq+31 (k-steps 2*hq, 2*hq+1)
-          const int h = hq >> 1, qq = hq & 1;
-#pragma unroll
-          for (int u = 0; u < 4; u++) {
-            if (j0 + u < ntiles) {
-              const int n = 8 * (j0 + u) + r;
-              const uint32_t addr = st + h * kHalfBytes + n * 128 + ((((4 * qq + m) ^ r) & 7) << 4);
-              uint32_t b0, b1, b2, b3;
-              ldmatrix_x4(addr, b0, b1, b2, b3);
-              mma_16816(acc[u], A[2 * hq], b0, b1);
-              mma_16816(acc[u], A[2 * hq + 1], b2, b3);
-            }
-          }
-        }
-#pragma unroll
-        for (int u = 0; u < 4; u++) {
-          if (j0 + u < ntiles) {
-            const int col = 8 * (j0 + u) + 2 * t4;
-            *reinterpret_cast<float2*>(rawD + g8 * kRawStride + col) = make_float2(acc[u][0], acc[u][1]);
-            if (g8 == 0) *reinterpret_cast<float2*>(rawD + 8 * kRawStride + col) = make_float2(acc[u][2], acc[u][3]);
-          }
-        }
+      const uint32_t a0 = st + lds_off0, a1 = st + lds_off1;
+      const bool has8 = g8 == 0;
+      mma_group<4>(a0, a1, A, d0, d8, has8);
+      mma_group<4>(a0 + 4 * 1024, a1 + 4 * 1024, A, d0 + 32, d8 + 32, has8);
+      mma_group<4>(a0 + 8 * 1024, a1 + 8 * 1024, A, d0 + 64, d8 + 64, has8);
+      if (g.kind == 0) {
+        mma_group<1>(a0 + 12 * 1024, a1 + 12 * 1024, A, d0 + 96, d8 + 96, has8);   // 13 tiles: 100 px (+4 unused)
+      } else {
+        mma_group<4>(a0 + 12 * 1024, a1 + 12 * 1024, A, d0 + 96, d8 + 96, has8);
+        mma_group<2>(a0 + 16 * 1024, a1 + 16 * 1024, A, d0 + 128, d8 + 128, has8);  // 18 tiles: 144 px
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(emptyb);
@@ -361,7 +429,7 @@ corr_tiled_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_co
         const __half* f2 = P.fmap2 + (size_t)g.slot * kC * plane;
         for (int t = lane; t < kPP * kD * kD; t += 32) {
           const int b = t & 7, a = (t >> 3) & 7, p = t >> 6;
-          const int i1 = __shfl_sync(__activemask(), g.fy, p) + a - kR, j1 = __shfl_sync(__activemask(), g.fx, p) + b - kR;
+          const int i1 = __shfl_sync(0xffffffffu, g.fy, p) + a - kR, j1 = __shfl_sync(0xffffffffu, g.fx, p) + b - kR;
           float sacc = 0.f;
           if (i1 >= 0 && i1 < P.H && j1 >= 0 && j1 < P.W) {
             const __half* p2 = f2 + (size_t)i1 * P.W + j1;
@@ -375,19 +443,41 @@ corr_tiled_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_co
       __syncwarp();
     }
 
-    // ---- bilinear blend of each patch pixel's own 8x8 window + permuted store (correlation_kernel.cu:221-232)
+    // ---- prefetch the next edge's patch into registers; the blend below hides its latency
+    if (k + 1 < cnt) {
+      const int64_t nix = raw.ix;
+      const long long np = (long long)((be + 1) / P.E) * P.n1 + nix;
+      if (nix >= 0 && nix < P.n1 && np != cur_patch && np != pf_patch) {
+        const uint4* src = reinterpret_cast<const uint4*>(P.fmap1 + np * (kC * kPP));
+#pragma unroll
+        for (int i = 0; i < 5; i++) if (lane + 32 * i < kPatchBytes / 16) pf[i] = src[lane + 32 * i];
+        pf_patch = np;
+      }
+    }
+
+    // ---- bilinear blend of each patch pixel's own 8x8 window + permuted store (correlation_kernel.cu:221-232).
+    // item = (patch pixel p, x-tap b): 63 items, two per lane; separable: 8 horizontal lerps, then 7 vertical ones
     __half* o = P.out + be * (kT * kT * kPP);
-    for (int t = lane; t < kT * kT * kPP; t += 32) {
-      const int p = t % kPP, a = (t / kPP) % kT, b = t / (kPP * kT);
-      const float* row = rawD + p * kRawStride;
-      const int org = __float_as_int(row[kMaxPix]);
-      const float dx = row[kMaxPix + 1], dy = row[kMaxPix + 2];
-      const float* rr = row + org + a * BX + b;
-      float v = ((1.f - dx) * (1.f - dy)) * rr[0];
-      v += (dx * (1.f - dy)) * rr[1];
-      v += ((1.f - dx) * dy) * rr[BX];
-      v += (dx * dy) * rr[BX + 1];
-      o[t] = __float2half_rn(v);
+#pragma unroll
+    for (int half_i = 0; half_i < 2; half_i++) {
+      const int item = lane + 32 * half_i;
+      if (item < kPP * kT) {
+        const int p = item % kPP, b = item / kPP;
+        const float* row = rawD + p * kRawStride;
+        const int org = __float_as_int(row[kMaxPix]);
+        const float dx = row[kMaxPix + 1], dy = row[kMaxPix + 2];
+        const float* rr = row + org + b;
+        float Hh[kD];
+#pragma unroll
+        for (int a = 0; a < kD; a++) {
+          const float r0 = rr[0], r1 = rr[1];
+          Hh[a] = fmaf(dx, r1 - r0, r0);
+          rr += BX;
+        }
+        __half* op = o + b * (kT * kPP) + p;
+#pragma unroll
+        for (int a = 0; a < kT; a++) op[a * kPP] = __float2half_rn(fmaf(dy, Hh[a + 1] - Hh[a], Hh[a]));
+      }
     }
     __syncwarp();
   }
