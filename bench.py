@@ -211,6 +211,9 @@ def run_reference(args):
 # our arm
 # ----------------------------------------------------------------------------------------------------------
 def run_b200(args):
+    # keep stdout for the ONE JSON line: libraries (NCCL's version banner) print there too
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     import torch
     import torch.distributed as dist
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -355,7 +358,8 @@ def run_b200(args):
                 line["cpu_baseline"] = ref["cpu_baseline"]
             except Exception as ex:  # the baseline is a reported number, not the product
                 line["cpu_baseline"] = {"error": repr(ex)}
-        print(json.dumps(line), flush=True)
+        real_stdout.write(json.dumps(line) + "\n")
+        real_stdout.flush()
     if world > 1:
         dist.destroy_process_group()
     return 0
