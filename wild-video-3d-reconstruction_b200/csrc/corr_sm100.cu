@@ -2,18 +2,22 @@
 //
 // Replaces corr_forward_kernel + the ATen blend (dpvo/altcorr/correlation_kernel.cu:82-136, 193-233) with
 //
-//   pass 1  nchw_to_nhwc_kernel: the frame-feature ring fmap2 [slot][C][H][W] is restaged channels-last
-//           [slot][H][W][C] in the caller's workspace, so that one pixel's 128 channels are one aligned 256-B line
-//           (in NCHW the contiguous unit is a ~20-B x-run per (c, y): every 32-B sector fetched is 2/3 waste).
+//   pass 1  restage_kernel: the frame-feature ring fmap2 [slot][C][H][W] is restaged channels-last [slot][H][W][C] in the
+//           caller's workspace, so that one pixel's 128 channels are one aligned 256-B line (in NCHW the contiguous unit
+//           is a ~20-B x-run per (c, y): every 32-B sector fetched is 2/3 waste); the source patches gmap [n][C][3][3] are
+//           restaged pixel-major [n][9][C] (the tensor-core A operand, fetched with one bulk copy).
 //   pass 2  corr_tiled_kernel, persistent, one CTA per SM, warp-specialised:
-//             producer warp   per edge: bounding box of the nine 8x8 tap windows -> two TMA tile loads
-//                             (cp.async.bulk.tensor.4d, box {64 ch, BX, BY, 1}, 128-B swizzle, OOB zero fill ==
-//                             the reference's within_bounds rule) into a 4-stage shared-memory ring, mbarrier
-//                             complete_tx signalling.
-//             8 consumer warps  per edge: D[9 x npix] = patch[9 x 128] . tile[128 x npix] with mma.sync m16n8k16
-//                             (fp16 in, fp32 accumulate; B fragments by ldmatrix from the swizzled tile), then the
-//                             4-corner bilinear blend of every patch pixel's own 8x8 sub-window and the permuted
-//                             [x-tap][y-tap][3][3] fp16 store (correlation_kernel.cu:221-232), fused.
+//             producer warp   owns all global reads.  32 edges per pass (one lane each): bounding box of the nine 8x8 tap
+//                             windows, per-pixel window origin + bilinear fractions.  Then, per edge, into the next stage
+//                             of a 6-stage shared-memory ring: a 128-B record (STS), two TMA tile loads
+//                             (cp.async.bulk.tensor.4d, 64 channels x 10x10 px, 128-B swizzle, OOB zero fill == the
+//                             reference's within_bounds rule), one bulk copy of the 2 304-B patch, all completing on the
+//                             owning consumer warp's mbarrier.  Windows up to 12x12 px go as two 12x6 half tiles.
+//             8 consumer warps  no global reads: A fragments by ldmatrix from the patch, B fragments by ldmatrix from the
+//                             swizzled tile, D[9 x npix] = patch[9 x 128] . tile[128 x npix] with mma.sync m16n8k16
+//                             (fp16 in, fp32 accumulate), stage released, then the 4-corner bilinear blend of every
+//                             patch pixel's own 8x8 sub-window and the permuted [x-tap][y-tap][3][3] fp16 store
+//                             (correlation_kernel.cu:221-232), fused.
 //
 // Why tensor cores here (BASELINE north_star: "only if ncu shows that step is compute-bound"): the contraction is
 // 2*128*64*9 = 147 kflop per edge and level, 13.4 GFLOP per two-level call; on the fp32 pipe (fp16 -> fp32 converts
@@ -21,8 +25,8 @@
 // As a [16 x 128] x [128 x npix] MMA per edge it is ~1 % of the tensor pipe and the kernel goes back to being bound
 // by L2 -> SM tile traffic.
 //
-// Edges whose windows do not fit the larger TMA box (patch magnified > ~2x between frames), and edges with an
-// out-of-range index, take a per-warp direct-gather path inside the same kernel (same arithmetic, no tile).
+// Edges whose windows do not fit 12x12 px (patch magnified > ~2x between frames) take a per-warp direct-gather path
+// inside the same kernel (same arithmetic, no tile); edges with an out-of-range index produce zeros and set the status.
 #include <cuda.h>
 #include <mma.h>
 
@@ -35,17 +39,35 @@ namespace {
 constexpr int kC = 128, kP = 3, kPP = 9, kR = 3, kD = 8, kT = 7;
 constexpr int kConsumers = 8;
 constexpr int kThreads = 32 * (kConsumers + 1);
-constexpr int kStages = 4;
-constexpr int kBoxSmall = 10, kBoxLarge = 12;              // tile edge in pixels (two tensor maps)
-constexpr int kMaxPix = kBoxLarge * kBoxLarge;             // 144
-constexpr int kHalfBytes = kMaxPix * 128;                  // 18 432: one 64-channel half of a stage (1024-B multiple)
-constexpr int kStageBytes = 2 * kHalfBytes;                // 36 864
+constexpr int kStages = 6;
+constexpr int kBoxSmall = 10, kBoxLarge = 12, kBoxLargeRows = 6;  // tile shapes: 10x10, or 12x12 as two 12x6 halves
+constexpr int kMaxPix = kBoxLarge * kBoxLarge;             // 144 columns of D at most
+constexpr int kHalfBytes = 13 * 1024;                      // one 64-channel half of a stage: 100 px x 128 B = 12 800 (1024-B aligned slots)
+constexpr int kPatchOff = 2 * kHalfBytes;                  // 26 624: the [9][128] fp16 patch
+constexpr int kPatchBytes = kC * kPP * 2;                  // 2 304
+constexpr int kRecOff = kPatchOff + kPatchBytes;           // 28 928: the 128-B edge record
+constexpr int kStageBytes = 29 * 1024;                     // 29 696
 constexpr int kRawStride = 152;                            // floats per patch-pixel row of D (bank-conflict-free stores)
 constexpr int kRawBytes = kPP * kRawStride * 4;            // 5 472
-constexpr int kPatchBytes = kC * kPP * 2;                  // 2 304
-constexpr int kWarpBytes = kRawBytes + kPatchBytes;        // 7 776
-constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kConsumers * kWarpBytes + (kConsumers + kStages) * 8 + 64;
+constexpr int kBarBytes = (kStages + 2 * kConsumers) * 8 + kConsumers * 4 + 32;
+constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kConsumers * kRawBytes + kBarBytes;
 constexpr int kClamp = 1 << 20;
+static_assert(kBoxSmall * kBoxSmall * 128 <= kHalfBytes && kBoxLarge * kBoxLargeRows * 128 <= kHalfBytes, "tile must fit its slot");
+static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
+
+// the record the producer writes next to each tile
+struct EdgeRec {
+  long long be;        // b * E + e
+  int kind;            // 0 small tile, 1 half of a large tile, 2 direct gather, 3 nothing to read (outside / bad index)
+  int part, nparts;    // large tiles arrive as two slots
+  int BX;              // row pitch of the D column space (10, 12; 8 for the gather path)
+  int has_patch;       // the patch differs from the one of the warp's previous edge: (re)load the A fragments
+  int slot;            // b * n2 + jj (gather path)
+  int org[kPP];        // column of pixel p's window origin in D
+  float dx[kPP], dy[kPP];
+  int fx[kPP], fy[kPP];  // kind 2 only: integer tap origins in the map
+};
+static_assert(kRecOff + sizeof(EdgeRec) <= kStageBytes, "record slot");
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -105,139 +127,76 @@ __device__ __forceinline__ int clamp_floor(float v) {
 
 }  // namespace
 
+
 // ---------------------------------------------------------------------------------------------------
-// pass 1: [slot][C=128][HW] -> [slot][HW][C=128], 64-pixel tiles through shared memory
+// pass 1: restaging.  Blocks [0, n_tiles): fmap2 [slot][128][HW] -> [slot][HW][128] in 64-pixel tiles through shared
+// memory; blocks beyond: gmap [n][128][9] -> [n][9][128], one warp per patch.
 // ---------------------------------------------------------------------------------------------------
 namespace {
 
 constexpr int kTrPix = 64;
 constexpr int kTrStrideW = 65;  // 32-bit words per pixel row in smem (64 + 1: odd stride)
 
-__global__ void __launch_bounds__(256) nchw_to_nhwc_kernel(const __half* __restrict__ src, __half* __restrict__ dst,
-                                                           int HW, int tiles_per_slot, long long n_tiles, int vec_ok) {
+__global__ void __launch_bounds__(256) restage_kernel(const __half* __restrict__ fmap2, __half* __restrict__ nhwc, int HW,
+                                                      int tiles_per_slot, long long n_tiles, int vec_ok,
+                                                      const __half* __restrict__ gmap, __half* __restrict__ gT, long long n_patches,
+                                                      int tile_blocks) {
   __shared__ uint32_t T[kTrPix * kTrStrideW];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const bool even = vec_ok != 0;  // HW even and src 4-byte aligned: half2 loads
-  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+  if ((int)blockIdx.x >= tile_blocks) {
+    // ---- patches: out word (p, channel pair) = (in[2cp][p], in[2cp+1][p])
+    const long long w0 = (long long)(blockIdx.x - tile_blocks) * 8 + warp, wstep = (long long)(gridDim.x - tile_blocks) * 8;
+    for (long long n = w0; n < n_patches; n += wstep) {
+      const unsigned short* in = reinterpret_cast<const unsigned short*>(gmap) + n * (kC * kPP);
+      uint32_t* out = reinterpret_cast<uint32_t*>(gT + n * (kC * kPP));
+#pragma unroll
+      for (int i = 0; i < kPP * 64 / 32; i++) {
+        const int o = i * 32 + lane, p = o >> 6, cp = o & 63;
+        out[o] = (uint32_t)in[(2 * cp) * kPP + p] | ((uint32_t)in[(2 * cp + 1) * kPP + p] << 16);
+      }
+    }
+    return;
+  }
+  for (long long tile = blockIdx.x; tile < n_tiles; tile += tile_blocks) {
     const long long slot = tile / tiles_per_slot;
     const int p0 = (int)(tile % tiles_per_slot) * kTrPix;
-    const __half* s = src + slot * (long long)kC * HW;
-    // read: warp handles channel pairs (c, c+1); lane handles pixels p0 + 2*lane, +1
-    for (int cp = warp; cp < kC / 2; cp += 8) {
-      const int c = 2 * cp, px = p0 + 2 * lane;
-      __half a0 = __float2half(0.f), a1 = a0, b0 = a0, b1 = a0;
-      const __half* r0 = s + (long long)c * HW + px;
-      const __half* r1 = r0 + HW;
-      if (even && px + 1 < HW) {
-        const __half2 v0 = *reinterpret_cast<const __half2*>(r0), v1 = *reinterpret_cast<const __half2*>(r1);
-        a0 = __low2half(v0); a1 = __high2half(v0); b0 = __low2half(v1); b1 = __high2half(v1);
-      } else {
-        if (px < HW) { a0 = r0[0]; b0 = r1[0]; }
-        if (px + 1 < HW) { a1 = r0[1]; b1 = r1[1]; }
+    const __half* s = fmap2 + slot * (long long)kC * HW;
+    if (vec_ok && p0 + kTrPix <= HW) {
+      // 16-B loads: work item = (channel pair cp, 8-pixel group xg); a warp covers 4 channel rows x 128 B per load
+#pragma unroll
+      for (int it = 0; it < 2; it++) {
+        const int xg = lane & 7, cp = it * 32 + warp * 4 + (lane >> 3);
+        const uint4 a = *reinterpret_cast<const uint4*>(s + (long long)(2 * cp) * HW + p0 + 8 * xg);
+        const uint4 b = *reinterpret_cast<const uint4*>(s + (long long)(2 * cp + 1) * HW + p0 + 8 * xg);
+        uint32_t* t = T + (8 * xg) * kTrStrideW + cp;
+        t[0 * kTrStrideW] = __byte_perm(a.x, b.x, 0x5410); t[1 * kTrStrideW] = __byte_perm(a.x, b.x, 0x7632);
+        t[2 * kTrStrideW] = __byte_perm(a.y, b.y, 0x5410); t[3 * kTrStrideW] = __byte_perm(a.y, b.y, 0x7632);
+        t[4 * kTrStrideW] = __byte_perm(a.z, b.z, 0x5410); t[5 * kTrStrideW] = __byte_perm(a.z, b.z, 0x7632);
+        t[6 * kTrStrideW] = __byte_perm(a.w, b.w, 0x5410); t[7 * kTrStrideW] = __byte_perm(a.w, b.w, 0x7632);
       }
-      const __half2 w0 = __halves2half2(a0, b0), w1 = __halves2half2(a1, b1);  // (c, c+1) of pixel px / px+1
-      T[(2 * lane) * kTrStrideW + cp] = *reinterpret_cast<const uint32_t*>(&w0);
-      T[(2 * lane + 1) * kTrStrideW + cp] = *reinterpret_cast<const uint32_t*>(&w1);
+    } else {
+      // ragged / unaligned maps: scalar loads
+      const unsigned short* su = reinterpret_cast<const unsigned short*>(s);
+      for (int cp = warp; cp < kC / 2; cp += 8) {
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+          const int px = p0 + lane + 32 * h;
+          uint32_t v = 0;
+          if (px < HW) v = (uint32_t)su[(long long)(2 * cp) * HW + px] | ((uint32_t)su[(long long)(2 * cp + 1) * HW + px] << 16);
+          T[(lane + 32 * h) * kTrStrideW + cp] = v;
+        }
+      }
     }
     __syncthreads();
-    // write: one pixel = 64 words = 256 B; a warp writes 2 x 128 B per pixel
-    uint32_t* d = reinterpret_cast<uint32_t*>(dst + (slot * (long long)HW + p0) * kC);
-    for (int t = threadIdx.x; t < kTrPix * 64; t += 256) {
-      const int px = t >> 6, wd = t & 63;
+    // write: one pixel = 64 words = 256 B; a warp writes 128 B per instruction
+    uint32_t* d = reinterpret_cast<uint32_t*>(nhwc + (slot * (long long)HW + p0) * kC);
+#pragma unroll
+    for (int it = 0; it < 16; it++) {
+      const int t = it * 256 + threadIdx.x, px = t >> 6, wd = t & 63;
       if (p0 + px < HW) d[t] = T[px * kTrStrideW + wd];
     }
     __syncthreads();
   }
-}
-
-struct CorrParams {
-  const __half* fmap1;  // [B][n1][128][3][3]
-  const __half* fmap2;  // [B][n2][128][H][W]  (original layout, direct-gather path only)
-  const float* coords;  // [B][E][2][3][3]
-  const int64_t* ii;
-  const int64_t* jj;
-  __half* out;          // [B][E][7][7][3][3]
-  int B, E, n1, n2, H, W;
-  int* status;
-};
-
-// geometry of one edge, evaluated redundantly by the producer warp and by the consumer warp that owns the edge
-struct EdgeGeom {
-  int fx, fy;      // lane p < 9: integer tap origin of patch pixel p (floor of its coordinate)
-  float dx, dy;    // lane p < 9: bilinear fractions
-  int x0, y0;      // warp-uniform: top-left of the tile (min floor - R)
-  int kind;        // warp-uniform: 0 small box, 1 large box, 2 direct gather, 3 nothing to read (all taps outside / bad index)
-  int slot;        // warp-uniform: b * n2 + jj
-  long long patch; // warp-uniform: b * n1 + ii
-};
-
-// the raw global loads of one edge, issued one iteration ahead of their use (software prefetch)
-struct EdgeRaw { float cv; int64_t ix, jx; long long be; };
-
-__device__ __forceinline__ EdgeRaw edge_load(const CorrParams& P, long long be, int lane) {
-  EdgeRaw r;
-  const int e = (int)(be % P.E);
-  r.be = be;
-  r.ix = P.ii[e]; r.jx = P.jj[e];
-  r.cv = lane < 2 * kPP ? P.coords[be * (2 * kPP) + lane] : 0.f;
-  return r;
-}
-
-__device__ __forceinline__ EdgeGeom edge_geom(const CorrParams& P, const EdgeRaw& raw, int lane) {
-  EdgeGeom g;
-  const int b = (int)(raw.be / P.E);
-  const int64_t ix = raw.ix, jx = raw.jx;
-  const float cv = raw.cv;
-  const float x = __shfl_sync(0xffffffffu, cv, lane < kPP ? lane : 0);
-  const float y = __shfl_sync(0xffffffffu, cv, lane < kPP ? lane + kPP : kPP);
-  g.fx = clamp_floor(x); g.fy = clamp_floor(y);
-  g.dx = x - floorf(x); g.dy = y - floorf(y);
-  int mnx = lane < kPP ? g.fx : kClamp * 2, mxx = lane < kPP ? g.fx : -kClamp * 2;
-  int mny = lane < kPP ? g.fy : kClamp * 2, mxy = lane < kPP ? g.fy : -kClamp * 2;
-#pragma unroll
-  for (int o = 8; o > 0; o >>= 1) {
-    mnx = min(mnx, __shfl_xor_sync(0xffffffffu, mnx, o)); mxx = max(mxx, __shfl_xor_sync(0xffffffffu, mxx, o));
-    mny = min(mny, __shfl_xor_sync(0xffffffffu, mny, o)); mxy = max(mxy, __shfl_xor_sync(0xffffffffu, mxy, o));
-  }
-  mnx = __shfl_sync(0xffffffffu, mnx, 0); mxx = __shfl_sync(0xffffffffu, mxx, 0);
-  mny = __shfl_sync(0xffffffffu, mny, 0); mxy = __shfl_sync(0xffffffffu, mxy, 0);
-  g.x0 = mnx - kR; g.y0 = mny - kR;
-  const int wdt = mxx - mnx + kD, hgt = mxy - mny + kD;
-  const bool bad = ix < 0 || ix >= P.n1 || jx < 0 || jx >= P.n2;
-  const bool outside = g.x0 >= P.W || g.y0 >= P.H || g.x0 + wdt <= 0 || g.y0 + hgt <= 0;
-  if (bad || outside) g.kind = 3;
-  else if (wdt <= kBoxSmall && hgt <= kBoxSmall) g.kind = 0;
-  else if (wdt <= kBoxLarge && hgt <= kBoxLarge) g.kind = 1;
-  else g.kind = 2;
-  if (bad && lane == 0) set_status(P.status, WV_STATUS_BAD_INDEX);
-  g.slot = bad ? 0 : b * P.n2 + (int)jx;
-  g.patch = bad ? 0 : (long long)b * P.n1 + ix;
-  return g;
-}
-
-// the producer's view of an edge, computed by ONE lane (32 edges per warp pass, loads in flight together)
-__device__ __forceinline__ void edge_box(const CorrParams& P, long long be, int& kind, int& x0, int& y0, int& slot) {
-  const int b = (int)(be / P.E), e = (int)(be % P.E);
-  const int64_t ix = P.ii[e], jx = P.jj[e];
-  const float2* c2 = reinterpret_cast<const float2*>(P.coords + be * (2 * kPP));  // 72-B records: 8-byte aligned
-  float v[2 * kPP];
-#pragma unroll
-  for (int i = 0; i < kPP; i++) { const float2 t = c2[i]; v[2 * i] = t.x; v[2 * i + 1] = t.y; }
-  int mnx = kClamp * 2, mxx = -kClamp * 2, mny = kClamp * 2, mxy = -kClamp * 2;
-#pragma unroll
-  for (int p = 0; p < kPP; p++) {
-    const int fx = clamp_floor(v[p]), fy = clamp_floor(v[kPP + p]);
-    mnx = min(mnx, fx); mxx = max(mxx, fx); mny = min(mny, fy); mxy = max(mxy, fy);
-  }
-  x0 = mnx - kR; y0 = mny - kR;
-  const int wdt = mxx - mnx + kD, hgt = mxy - mny + kD;
-  const bool bad = ix < 0 || ix >= P.n1 || jx < 0 || jx >= P.n2;
-  const bool outside = x0 >= P.W || y0 >= P.H || x0 + wdt <= 0 || y0 + hgt <= 0;
-  if (bad || outside) kind = 3;
-  else if (wdt <= kBoxSmall && hgt <= kBoxSmall) kind = 0;
-  else if (wdt <= kBoxLarge && hgt <= kBoxLarge) kind = 1;
-  else kind = 2;
-  slot = bad ? 0 : b * P.n2 + (int)jx;
 }
 
 }  // namespace
@@ -246,6 +205,23 @@ __device__ __forceinline__ void edge_box(const CorrParams& P, long long be, int&
 // pass 2: persistent warp-specialised kernel
 // ---------------------------------------------------------------------------------------------------
 namespace {
+
+struct CorrParams {
+  const __half* gT;     // [B][n1][9][128]   restaged patches (workspace)
+  const __half* fmap2;  // [B][n2][128][H][W] original layout (direct-gather path only)
+  const float* coords;  // [B][E][2][3][3]
+  const int64_t* ii;
+  const int64_t* jj;
+  __half* out;          // [B][E][7][7][3][3]
+  int B, E, n1, n2, H, W;
+  int* status;
+};
+
+__device__ __forceinline__ void bulk_copy_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(dst), "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
 
 // NT (<= 4) pixel tiles of 8 px: D[16 x 8*NT] = A[16 x 128] . tile^T, B fragments double-buffered one 32-channel step ahead.
 // a0 / a1: this lane's ldmatrix address in tile 0 for chunks 0..3 / 4..7 of the 128-B rows (swizzle folded in).
@@ -279,22 +255,22 @@ __device__ __forceinline__ void mma_group(uint32_t a0, uint32_t a1, const uint32
 }
 
 __global__ void __launch_bounds__(kThreads, 1)
-corr_tiled_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_constant__ CUtensorMap map_large, const CorrParams P) {
+corr_tiled_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_constant__ CUtensorMap map_half, const CorrParams P) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // stays a shared-space pointer (LDS/STS, not generic LD/ST)
-  uint8_t* stages = smem;                                              // [kStages][2][kHalfBytes], 1024-B aligned
-  uint8_t* warp_area = stages + kStages * kStageBytes;                 // [kConsumers][raw | patch]
-  // Barriers.  full[w]: one per CONSUMER WARP (not per stage) -- tile q goes to warp q % 8 and stage q % 4, so a warp's
-  // consecutive tiles reuse one stage and its barrier can never run a phase ahead of the warp; a per-stage barrier would be
-  // waited on by two warps that are a phase apart, which a parity wait cannot tell from "already complete".
-  // empty[s]: one per stage, waited on by the producer alone, in order.
-  uint64_t* bars = reinterpret_cast<uint64_t*>(warp_area + kConsumers * kWarpBytes);  // full[kConsumers], empty[kStages]
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);  // stays a shared-space pointer
+  uint8_t* stages = smem;                                              // [kStages][kStageBytes], 1024-B aligned
+  uint8_t* raw_area = stages + kStages * kStageBytes;                  // [kConsumers][kRawBytes]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(raw_area + kConsumers * kRawBytes);
+  // Barriers.  full[w] (per CONSUMER WARP): the tile, patch and record of warp w's next slot have landed.  taken[w]: warp w
+  // has picked that slot up -- the producer keeps at most one slot per warp outstanding, so a warp never waits on a
+  // barrier that is a phase ahead of it (parity waits cannot tell "two phases ago" from "now").  empty[s] (per stage): the
+  // consumer is done reading stage s; waited on by the producer alone, in ring order.
+  const uint32_t full0 = smem_u32(bars), taken0 = full0 + 8 * kConsumers, empty0 = taken0 + 8 * kConsumers;
+  volatile int* mailbox = reinterpret_cast<volatile int*>(bars + 2 * kConsumers + kStages);  // [kConsumers]: stage of the slot
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + kConsumers);
-  static_assert(kConsumers % kStages == 0, "a warp's tiles must always land in the same stage");
 
   if (threadIdx.x == 0) {
-    for (int w = 0; w < kConsumers; w++) mbar_init(full0 + 8 * w, 1);
+    for (int w = 0; w < kConsumers; w++) { mbar_init(full0 + 8 * w, 1); mbar_init(taken0 + 8 * w, 1); }
     for (int s = 0; s < kStages; s++) mbar_init(empty0 + 8 * s, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -304,156 +280,188 @@ corr_tiled_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_co
   const long long BE = (long long)P.B * P.E;
   const long long lo = BE * blockIdx.x / gridDim.x, hi = BE * (blockIdx.x + 1) / gridDim.x;
   const int nt = (int)(hi - lo);
-  const int per = (nt + kConsumers - 1) / kConsumers;  // edges per consumer warp (contiguous runs: patch reuse)
+  const int per = (nt + kConsumers - 1) / kConsumers;  // edges per consumer warp (contiguous runs: consecutive edges share patches)
 
   if (warp == kConsumers) {
     // ================================================================= producer
-    const int total = per * kConsumers;
-    for (int q0 = 0; q0 < total; q0 += 32) {
-      // every lane works out the box of one tile of this batch (their global loads overlap) ...
-      int kind = 3, x0 = 0, y0 = 0, slot = 0;
-      {
-        const int q = q0 + lane, idx = (q % kConsumers) * per + q / kConsumers;
-        if (q < total && idx < nt) edge_box(P, lo + idx, kind, x0, y0, slot);
+    const int pw = lane >> 2, pj = lane & 3;             // this lane prepares edge 4*batch + pj of consumer warp pw
+    const int cntw = max(0, min(per, nt - pw * per));
+    long long carry_pid = -1;                            // patch of warp pw's last edge of the previous batch
+    int my_m = 0;                                        // lanes 0..7: slots emitted so far to consumer warp `lane`
+    int seq = 0;                                         // slots emitted so far (warp-uniform)
+    const int nbatch = (per + 3) >> 2;
+    for (int bt = 0; bt < nbatch; bt++) {
+      // ---- every lane prepares one edge; the 32 edges' global loads overlap
+      const int k = 4 * bt + pj;
+      const bool valid = k < cntw;
+      EdgeRec r;
+      r.kind = 3; r.nparts = 1; r.BX = kD; r.slot = 0; r.be = 0; r.has_patch = 0;
+      int x0 = 0, y0 = 0;
+      long long pid = -1;
+      if (valid) {
+        const long long be = lo + (long long)pw * per + k;
+        const int b = (int)(be / P.E), e = (int)(be % P.E);
+        const int64_t ix = P.ii[e], jx = P.jj[e];
+        const float2* c2 = reinterpret_cast<const float2*>(P.coords + be * (2 * kPP));  // 72-B records: 8-byte aligned
+        float v[2 * kPP];
+#pragma unroll
+        for (int i = 0; i < kPP; i++) { const float2 t = c2[i]; v[2 * i] = t.x; v[2 * i + 1] = t.y; }
+        int mnx = kClamp * 2, mxx = -kClamp * 2, mny = kClamp * 2, mxy = -kClamp * 2;
+#pragma unroll
+        for (int p = 0; p < kPP; p++) {
+          r.fx[p] = clamp_floor(v[p]); r.fy[p] = clamp_floor(v[kPP + p]);
+          r.dx[p] = v[p] - floorf(v[p]); r.dy[p] = v[kPP + p] - floorf(v[kPP + p]);
+          mnx = min(mnx, r.fx[p]); mxx = max(mxx, r.fx[p]); mny = min(mny, r.fy[p]); mxy = max(mxy, r.fy[p]);
+        }
+        x0 = mnx - kR; y0 = mny - kR;
+        const int wdt = mxx - mnx + kD, hgt = mxy - mny + kD;
+        const bool bad = ix < 0 || ix >= P.n1 || jx < 0 || jx >= P.n2;
+        const bool outside = x0 >= P.W || y0 >= P.H || x0 + wdt <= 0 || y0 + hgt <= 0;
+        if (bad) set_status(P.status, WV_STATUS_BAD_INDEX);
+        if (bad || outside) r.kind = 3;
+        else if (wdt <= kBoxSmall && hgt <= kBoxSmall) { r.kind = 0; r.BX = kBoxSmall; }
+        else if (wdt <= kBoxLarge && hgt <= kBoxLarge) { r.kind = 1; r.BX = kBoxLarge; r.nparts = 2; }
+        else r.kind = 2;
+        r.be = be;
+        r.slot = bad ? 0 : b * P.n2 + (int)jx;
+        if (r.kind <= 2) pid = (long long)b * P.n1 + ix;
+#pragma unroll
+        for (int p = 0; p < kPP; p++) r.org[p] = r.kind <= 1 ? (r.fy[p] - mny) * r.BX + (r.fx[p] - mnx) : 0;
       }
-      // ... then lane 0 feeds the ring in order
-      const int nb = min(32, total - q0);
-      for (int i = 0; i < nb; i++) {
-        const int q = q0 + i, w = q % kConsumers, s = q % kStages;
-        const int kd = __shfl_sync(0xffffffffu, kind, i), bx = __shfl_sync(0xffffffffu, x0, i);
-        const int by = __shfl_sync(0xffffffffu, y0, i), sl = __shfl_sync(0xffffffffu, slot, i);
-        if (lane == 0) {
-          mbar_wait(empty0 + 8 * s, ((q / kStages) & 1) ^ 1);
-          const uint32_t bar = full0 + 8 * w;
-          if (kd <= 1) {
-            const int box = kd == 0 ? kBoxSmall : kBoxLarge;
-            const CUtensorMap* map = kd == 0 ? &map_small : &map_large;
-            const uint32_t dst = smem_u32(stages + (size_t)s * kStageBytes);
-            mbar_arrive_expect_tx(bar, (uint32_t)(2 * box * box * 128));
-            tma_load_4d(dst, map, bar, 0, bx, by, sl);
-            tma_load_4d(dst + kHalfBytes, map, bar, 64, bx, by, sl);
-          } else {
-            mbar_arrive(bar);
+      {
+        const long long up = __shfl_up_sync(0xffffffffu, pid, 1);
+        const long long prev = pj == 0 ? carry_pid : up;
+        r.has_patch = (pid >= 0 && (pid != prev || r.kind == 2)) ? 1 : 0;
+        carry_pid = __shfl_sync(0xffffffffu, pid, (lane & ~3) | 3);
+      }
+      const unsigned vmask = __ballot_sync(0xffffffffu, valid), lmask = __ballot_sync(0xffffffffu, valid && r.kind == 1);
+
+      // ---- lane 0 feeds the ring: warps round-robin, each warp's slots in order
+      for (int jp = 0; jp < 8; jp++) {
+        const int j = jp >> 1, part = jp & 1;
+        const unsigned cand = part == 0 ? vmask : lmask;
+        for (int w = 0; w < kConsumers; w++) {
+          const int src = 4 * w + j;
+          if (!((cand >> src) & 1u)) continue;
+          const int stage = seq % kStages;
+          uint8_t* sb = stages + (size_t)stage * kStageBytes;
+          const int kd = __shfl_sync(0xffffffffu, r.kind, src), hp = __shfl_sync(0xffffffffu, r.has_patch, src);
+          const int bx = __shfl_sync(0xffffffffu, x0, src), by = __shfl_sync(0xffffffffu, y0, src);
+          const int sl = __shfl_sync(0xffffffffu, r.slot, src), m = __shfl_sync(0xffffffffu, my_m, w);
+          const long long pd = __shfl_sync(0xffffffffu, pid, src);
+          if (lane == 0) {
+            mbar_wait(empty0 + 8 * stage, ((seq / kStages) & 1) ^ 1);
+            if (m > 0) mbar_wait(taken0 + 8 * w, (m - 1) & 1);
           }
+          __syncwarp();
+          if (lane == src) {
+            EdgeRec* d = reinterpret_cast<EdgeRec*>(sb + kRecOff);
+            d->be = r.be; d->kind = r.kind; d->part = part; d->nparts = r.nparts; d->BX = r.BX;
+            d->has_patch = part == 0 ? r.has_patch : 0; d->slot = r.slot;
+#pragma unroll
+            for (int p = 0; p < kPP; p++) { d->org[p] = r.org[p]; d->dx[p] = r.dx[p]; d->dy[p] = r.dy[p]; }
+            if (r.kind == 2) {
+#pragma unroll
+              for (int p = 0; p < kPP; p++) { d->fx[p] = r.fx[p]; d->fy[p] = r.fy[p]; }
+            }
+          }
+          __syncwarp();
+          if (lane == 0) {
+            mailbox[w] = stage;
+            const uint32_t bar = full0 + 8 * w, dst = smem_u32(sb);
+            const bool patch_now = hp && part == 0;
+            const int npix = kd == 0 ? kBoxSmall * kBoxSmall : kBoxLarge * kBoxLargeRows;
+            const uint32_t bytes = (kd <= 1 ? 2u * npix * 128u : 0u) + (patch_now ? (uint32_t)kPatchBytes : 0u);
+            if (bytes) mbar_arrive_expect_tx(bar, bytes); else mbar_arrive(bar);
+            if (kd <= 1) {
+              const CUtensorMap* map = kd == 0 ? &map_small : &map_half;
+              const int yy = by + part * kBoxLargeRows;
+              tma_load_4d(dst, map, bar, 0, bx, yy, sl);
+              tma_load_4d(dst + kHalfBytes, map, bar, 64, bx, yy, sl);
+            }
+            if (patch_now) bulk_copy_g2s(dst + kPatchOff, P.gT + pd * (kC * kPP), kPatchBytes, bar);
+          }
+          if (lane == w) my_m++;
+          seq++;
         }
       }
-      __syncwarp();
     }
     return;
   }
 
-  // =================================================================== consumers
-  float* rawD = reinterpret_cast<float*>(warp_area + (size_t)warp * kWarpBytes);  // [9][kRawStride]: cols 0..143 D, 144..146 geometry
-  __half* patch = reinterpret_cast<__half*>(warp_area + (size_t)warp * kWarpBytes + kRawBytes);  // [128][9]
+  // =================================================================== consumers (no global reads)
+  float* rawD = reinterpret_cast<float*>(raw_area + (size_t)warp * kRawBytes);  // [9][kRawStride]: cols 0..143 D, 144..146 geometry
   const int g8 = lane >> 2, t4 = lane & 3;
   const uint32_t lds_off0 = (uint32_t)((lane & 7) * 128 + ((((lane >> 3) ^ (lane & 7)) & 7) << 4));  // ldmatrix row + swizzled chunk
   const uint32_t lds_off1 = lds_off0 ^ 64u;                                                            // chunks 4..7 of the 128-B row
+  // A-fragment ldmatrix address inside the [9][128] patch: matrices (rows 0-7 | 8-15) x (k 0-7 | 8-15); rows > 8 alias row 8
+  const uint32_t a_off = (uint32_t)(min(((lane >> 3) & 1) * 8 + (lane & 7), 8) * 256 + (lane >> 4) * 16);
   float* const d0 = rawD + g8 * kRawStride + 2 * t4;
   float* const d8 = rawD + 8 * kRawStride + 2 * t4;
+  const bool has8 = g8 == 0;
   uint32_t A[8][4];
-  long long cur_patch = -1, pf_patch = -1;
-  uint4 pf[5];
+#pragma unroll
+  for (int ks = 0; ks < 8; ks++) { A[ks][0] = 0u; A[ks][1] = 0u; A[ks][2] = 0u; A[ks][3] = 0u; }
   const int cnt = max(0, min(per, nt - warp * per));
-  EdgeRaw raw{};
-  if (cnt > 0) raw = edge_load(P, lo + warp * per, lane);
+  const uint32_t fullb = full0 + 8 * warp, takenb = taken0 + 8 * warp;
 
-  for (int k = 0; k < per; k++) {
-    const int q = k * kConsumers + warp, s = q % kStages;
-    const uint32_t fullb = full0 + 8 * warp, emptyb = empty0 + 8 * s;
-    if (k >= cnt) {  // padding slot of the ring: keep the protocol in step
-      mbar_wait(fullb, k & 1);
-      if (lane == 0) mbar_arrive(emptyb);
-      continue;
-    }
-    const long long be = lo + warp * per + k;
-    const EdgeGeom g = edge_geom(P, raw, lane);
-    if (k + 1 < cnt) raw = edge_load(P, be + 1, lane);  // next edge's loads fly during this edge's work
+  int m = 0;
+  for (int done = 0; done < cnt;) {
+    mbar_wait(fullb, m & 1);
+    const int stage = mailbox[warp];
+    const uint8_t* sb = stages + (size_t)stage * kStageBytes;
+    const EdgeRec* rec = reinterpret_cast<const EdgeRec*>(sb + kRecOff);
+    const long long be = rec->be;
+    const int kind = rec->kind, part = rec->part, nparts = rec->nparts, BX = rec->BX, has_patch = rec->has_patch;
+    __syncwarp();
+    if (lane == 0) mbar_arrive(takenb);
+    m++;
+    const uint32_t st = smem_u32(sb);
 
-    // ---- A operand: the 3x3x128 source patch (reused while consecutive edges share it; prefetched otherwise)
-    if (g.kind != 3 && g.patch != cur_patch) {
-      uint4* dstp = reinterpret_cast<uint4*>(patch);
-      if (pf_patch != g.patch) {
-        const uint4* src = reinterpret_cast<const uint4*>(P.fmap1 + g.patch * (kC * kPP));
-#pragma unroll
-        for (int i = 0; i < 5; i++) if (lane + 32 * i < kPatchBytes / 16) pf[i] = src[lane + 32 * i];
-      }
-      __syncwarp();
-#pragma unroll
-      for (int i = 0; i < 5; i++) if (lane + 32 * i < kPatchBytes / 16) dstp[lane + 32 * i] = pf[i];
-      __syncwarp();
-      const unsigned short* ps = reinterpret_cast<const unsigned short*>(patch);
-#pragma unroll
-      for (int ks = 0; ks < 8; ks++) {
-        const int c0 = 16 * ks + 2 * t4;
-        A[ks][0] = (uint32_t)ps[c0 * kPP + g8] | ((uint32_t)ps[(c0 + 1) * kPP + g8] << 16);
-        A[ks][2] = (uint32_t)ps[(c0 + 8) * kPP + g8] | ((uint32_t)ps[(c0 + 9) * kPP + g8] << 16);
-        A[ks][1] = 0u; A[ks][3] = 0u;
-        if (g8 == 0) {  // row 8 of the 16-row fragment = patch pixel 8; rows 9..15 stay zero
-          A[ks][1] = (uint32_t)ps[c0 * kPP + 8] | ((uint32_t)ps[(c0 + 1) * kPP + 8] << 16);
-          A[ks][3] = (uint32_t)ps[(c0 + 8) * kPP + 8] | ((uint32_t)ps[(c0 + 9) * kPP + 8] << 16);
-        }
-      }
-      cur_patch = g.patch;
-    }
-
-    // ---- geometry of each patch pixel next to its D row
-    int BX = kD, wx = 0, wy = 0;
-    if (g.kind <= 1) { BX = g.kind == 0 ? kBoxSmall : kBoxLarge; wx = g.fx - kR - g.x0; wy = g.fy - kR - g.y0; }
-    if (lane < kPP) {
+    if (part == 0 && lane < kPP) {  // geometry of each patch pixel next to its D row
       float* gr = rawD + lane * kRawStride + kMaxPix;
-      gr[0] = __int_as_float(wy * BX + wx); gr[1] = g.dx; gr[2] = g.dy;
+      gr[0] = __int_as_float(rec->org[lane]); gr[1] = rec->dx[lane]; gr[2] = rec->dy[lane];
     }
-
-    mbar_wait(fullb, k & 1);
-    if (g.kind <= 1) {
-      // -------------------------------------------------------------- tensor-core contraction from the TMA tile
-      const uint32_t st = smem_u32(stages + (size_t)s * kStageBytes);
-      const uint32_t a0 = st + lds_off0, a1 = st + lds_off1;
-      const bool has8 = g8 == 0;
-      mma_group<4>(a0, a1, A, d0, d8, has8);
-      mma_group<4>(a0 + 4 * 1024, a1 + 4 * 1024, A, d0 + 32, d8 + 32, has8);
-      mma_group<4>(a0 + 8 * 1024, a1 + 8 * 1024, A, d0 + 64, d8 + 64, has8);
-      if (g.kind == 0) {
-        mma_group<1>(a0 + 12 * 1024, a1 + 12 * 1024, A, d0 + 96, d8 + 96, has8);   // 13 tiles: 100 px (+4 unused)
-      } else {
-        mma_group<4>(a0 + 12 * 1024, a1 + 12 * 1024, A, d0 + 96, d8 + 96, has8);
-        mma_group<2>(a0 + 16 * 1024, a1 + 16 * 1024, A, d0 + 128, d8 + 128, has8);  // 18 tiles: 144 px
-      }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(emptyb);
-    } else {
-      if (lane == 0) mbar_arrive(emptyb);
-      if (g.kind == 2) {
-        // ------------------------------------------------------------ direct gather (windows too far apart for a tile)
-        const size_t plane = (size_t)P.H * P.W;
-        const __half* f2 = P.fmap2 + (size_t)g.slot * kC * plane;
-        for (int t = lane; t < kPP * kD * kD; t += 32) {
-          const int b = t & 7, a = (t >> 3) & 7, p = t >> 6;
-          const int i1 = __shfl_sync(0xffffffffu, g.fy, p) + a - kR, j1 = __shfl_sync(0xffffffffu, g.fx, p) + b - kR;
-          float sacc = 0.f;
-          if (i1 >= 0 && i1 < P.H && j1 >= 0 && j1 < P.W) {
-            const __half* p2 = f2 + (size_t)i1 * P.W + j1;
-            for (int c = 0; c < kC; c++) sacc = fmaf(__half2float(patch[c * kPP + p]), __half2float(p2[(size_t)c * plane]), sacc);
-          }
-          rawD[p * kRawStride + a * kD + b] = sacc;
-        }
-      } else {
-        for (int t = lane; t < kPP * kD * kD; t += 32) rawD[(t >> 6) * kRawStride + (t & 63)] = 0.f;
-      }
-      __syncwarp();
-    }
-
-    // ---- prefetch the next edge's patch into registers; the blend below hides its latency
-    if (k + 1 < cnt) {
-      const int64_t nix = raw.ix;
-      const long long np = (long long)((be + 1) / P.E) * P.n1 + nix;
-      if (nix >= 0 && nix < P.n1 && np != cur_patch && np != pf_patch) {
-        const uint4* src = reinterpret_cast<const uint4*>(P.fmap1 + np * (kC * kPP));
+    if (has_patch) {
 #pragma unroll
-        for (int i = 0; i < 5; i++) if (lane + 32 * i < kPatchBytes / 16) pf[i] = src[lane + 32 * i];
-        pf_patch = np;
-      }
+      for (int ks = 0; ks < 8; ks++) ldmatrix_x4(st + kPatchOff + a_off + ks * 32, A[ks][0], A[ks][1], A[ks][2], A[ks][3]);
     }
+
+    if (kind <= 1) {
+      // -------------------------------------------------------------- tensor-core contraction from the TMA tile
+      const uint32_t a0 = st + lds_off0, a1 = st + lds_off1;
+      if (kind == 0) {  // 100 px -> 13 pixel tiles (the last one half used)
+        mma_group<4>(a0, a1, A, d0, d8, has8);
+        mma_group<4>(a0 + 4 * 1024, a1 + 4 * 1024, A, d0 + 32, d8 + 32, has8);
+        mma_group<4>(a0 + 8 * 1024, a1 + 8 * 1024, A, d0 + 64, d8 + 64, has8);
+        mma_group<1>(a0 + 12 * 1024, a1 + 12 * 1024, A, d0 + 96, d8 + 96, has8);
+      } else {          // half of a 12x12 window: 72 px -> 9 pixel tiles, D columns 72*part ..
+        const int c0 = part * (kBoxLarge * kBoxLargeRows);
+        mma_group<4>(a0, a1, A, d0 + c0, d8 + c0, has8);
+        mma_group<4>(a0 + 4 * 1024, a1 + 4 * 1024, A, d0 + c0 + 32, d8 + c0 + 32, has8);
+        mma_group<1>(a0 + 8 * 1024, a1 + 8 * 1024, A, d0 + c0 + 64, d8 + c0 + 64, has8);
+      }
+    } else if (kind == 2) {
+      // -------------------------------------------------------------- direct gather (windows too far apart for a tile)
+      const size_t plane = (size_t)P.H * P.W;
+      const __half* f2 = P.fmap2 + (size_t)rec->slot * kC * plane;
+      const __half* pt = reinterpret_cast<const __half*>(sb + kPatchOff);  // [9][128]
+      for (int t = lane; t < kPP * kD * kD; t += 32) {
+        const int b = t & 7, a = (t >> 3) & 7, p = t >> 6;
+        const int i1 = rec->fy[p] + a - kR, j1 = rec->fx[p] + b - kR;
+        float sacc = 0.f;
+        if (i1 >= 0 && i1 < P.H && j1 >= 0 && j1 < P.W) {
+          const __half* p2 = f2 + (size_t)i1 * P.W + j1;
+          for (int c = 0; c < kC; c++) sacc = fmaf(__half2float(pt[p * kC + c]), __half2float(p2[(size_t)c * plane]), sacc);
+        }
+        rawD[p * kRawStride + a * kD + b] = sacc;
+      }
+    } else {
+      for (int t = lane; t < kPP * kD * kD; t += 32) rawD[(t >> 6) * kRawStride + (t & 63)] = 0.f;
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(empty0 + 8 * stage);  // record, patch and tile of this stage are no longer read
+    if (part != nparts - 1) continue;
 
     // ---- bilinear blend of each patch pixel's own 8x8 window + permuted store (correlation_kernel.cu:221-232).
     // item = (patch pixel p, x-tap b): 63 items, two per lane; separable: 8 horizontal lerps, then 7 vertical ones
@@ -480,6 +488,7 @@ corr_tiled_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_co
       }
     }
     __syncwarp();
+    done++;
   }
 }
 
@@ -509,12 +518,12 @@ EncodeTiledFn encode_tiled_fn() {
   return fn;
 }
 
-bool make_map(CUtensorMap* m, void* nhwc, int W, int H, long long slots, int box) {
+bool make_map(CUtensorMap* m, void* nhwc, int W, int H, long long slots, int box_x, int box_y) {
   EncodeTiledFn fn = encode_tiled_fn();
   if (!fn) return false;
   const cuuint64_t dims[4] = {(cuuint64_t)kC, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)slots};
   const cuuint64_t strides[3] = {(cuuint64_t)kC * 2, (cuuint64_t)kC * 2 * W, (cuuint64_t)kC * 2 * W * H};
-  const cuuint32_t boxd[4] = {64, (cuuint32_t)box, (cuuint32_t)box, 1};
+  const cuuint32_t boxd[4] = {64, (cuuint32_t)box_x, (cuuint32_t)box_y, 1};
   const cuuint32_t estr[4] = {1, 1, 1, 1};
   return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 4, nhwc, dims, strides, boxd, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
@@ -526,6 +535,8 @@ int tiled_mode() {  // WVB200_CORR_TILED: unset = heuristic, 0 = never, 1 = when
   return s[0] == '0' ? 0 : 1;
 }
 
+inline size_t al1k(size_t x) { return (x + 1023) & ~(size_t)1023; }
+
 }  // namespace
 
 bool corr_tiled_supported(int dtype, int B, int E, int C, int PH, int PW, int n1, int n2, int H2, int W2, int R) {
@@ -535,13 +546,14 @@ bool corr_tiled_supported(int dtype, int B, int E, int C, int PH, int PW, int n1
   if (B <= 0 || E <= 0 || n1 <= 0 || (long long)B * n2 > 0x7fffffffLL || H2 > (1 << 20) || W2 > (1 << 20)) return false;
   if (!encode_tiled_fn()) return false;
   if (mode == 1) return true;
-  // restaging the ring costs one read + one write of it: worth it once the edges' tile traffic dominates
-  const double ring = (double)B * n2 * H2 * W2 * kC * 2.0, tiles = (double)B * E * 2.0 * kBoxSmall * kBoxSmall * 128.0;
+  // restaging costs one read + one write of the ring and of the patches: worth it once the edges' tile traffic dominates
+  const double ring = ((double)B * n2 * H2 * W2 + (double)B * n1 * kPP) * kC * 2.0;
+  const double tiles = (double)B * E * 2.0 * kBoxSmall * kBoxSmall * 128.0;
   return (long long)B * E >= 1024 && tiles >= 0.5 * ring;
 }
 
-size_t corr_tiled_workspace_bytes(int, int B, int, int, int, int, int, int n2, int H2, int W2, int) {
-  return (size_t)B * n2 * H2 * W2 * kC * 2 + 2048;
+size_t corr_tiled_workspace_bytes(int, int B, int, int, int, int, int n1, int n2, int H2, int W2, int) {
+  return 1024 + al1k((size_t)B * n2 * H2 * W2 * kC * 2) + al1k((size_t)B * n1 * kPP * kC * 2);
 }
 
 int corr_forward_tiled(const void* fmap1, const void* fmap2, const float* coords, const int64_t* ii, const int64_t* jj, void* out,
@@ -549,18 +561,26 @@ int corr_forward_tiled(const void* fmap1, const void* fmap2, const float* coords
                        size_t workspace_bytes, int* status, cudaStream_t st) {
   if (!corr_tiled_supported(dtype, B, E, C, PH, PW, n1, n2, H2, W2, R)) return WV_EUNSUPPORTED;
   if (workspace_bytes < corr_tiled_workspace_bytes(dtype, B, E, C, PH, PW, n1, n2, H2, W2, R)) return WV_EWORKSPACE;
-  if ((reinterpret_cast<uintptr_t>(fmap1) & 15) || (reinterpret_cast<uintptr_t>(fmap2) & 1)) return WV_EUNSUPPORTED;
-  __half* nhwc = reinterpret_cast<__half*>((reinterpret_cast<uintptr_t>(workspace) + 1023) & ~(uintptr_t)1023);
-  const long long slots = (long long)B * n2;
+  if ((reinterpret_cast<uintptr_t>(fmap1) & 1) || (reinterpret_cast<uintptr_t>(fmap2) & 1) ||
+      (reinterpret_cast<uintptr_t>(coords) & 7))
+    return WV_EUNSUPPORTED;
+  const long long slots = (long long)B * n2, n_patches = (long long)B * n1;
   const int HW = H2 * W2;
-  CUtensorMap ms, ml;
-  if (!make_map(&ms, nhwc, W2, H2, slots, kBoxSmall) || !make_map(&ml, nhwc, W2, H2, slots, kBoxLarge)) return WV_EUNSUPPORTED;
+  __half* nhwc = reinterpret_cast<__half*>((reinterpret_cast<uintptr_t>(workspace) + 1023) & ~(uintptr_t)1023);
+  __half* gT = reinterpret_cast<__half*>(reinterpret_cast<char*>(nhwc) + al1k((size_t)slots * HW * kC * 2));
+  CUtensorMap ms, mh;
+  if (!make_map(&ms, nhwc, W2, H2, slots, kBoxSmall, kBoxSmall) || !make_map(&mh, nhwc, W2, H2, slots, kBoxLarge, kBoxLargeRows))
+    return WV_EUNSUPPORTED;
 
   const int tiles_per_slot = (HW + kTrPix - 1) / kTrPix;
   const long long n_tiles = slots * tiles_per_slot;
   const long long cap = (long long)sm_count() * 8;
-  const int vec_ok = ((HW & 1) == 0 && (reinterpret_cast<uintptr_t>(fmap2) & 3) == 0) ? 1 : 0;
-  nchw_to_nhwc_kernel<<<(int)(n_tiles < cap ? n_tiles : cap), 256, 0, st>>>((const __half*)fmap2, nhwc, HW, tiles_per_slot, n_tiles, vec_ok);
+  const int tile_blocks = (int)(n_tiles < cap ? n_tiles : cap);
+  const long long pb = (n_patches + 7) / 8;
+  const int patch_blocks = (int)(pb < sm_count() ? pb : sm_count());
+  const int vec_ok = ((HW & 7) == 0 && (reinterpret_cast<uintptr_t>(fmap2) & 15) == 0) ? 1 : 0;
+  restage_kernel<<<tile_blocks + patch_blocks, 256, 0, st>>>((const __half*)fmap2, nhwc, HW, tiles_per_slot, n_tiles, vec_ok,
+                                                            (const __half*)fmap1, gT, n_patches, tile_blocks);
   WV_LAUNCH_CHECK();
 
   static bool attr_set = false;
@@ -568,11 +588,11 @@ int corr_forward_tiled(const void* fmap1, const void* fmap2, const float* coords
     WV_CUDA_TRY(cudaFuncSetAttribute(corr_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
     attr_set = true;
   }
-  CorrParams P{(const __half*)fmap1, (const __half*)fmap2, coords, ii, jj, (__half*)out, B, E, n1, n2, H2, W2, status};
+  CorrParams P{gT, (const __half*)fmap2, coords, ii, jj, (__half*)out, B, E, n1, n2, H2, W2, status};
   const long long BE = (long long)B * E;
   const long long want = (BE + kConsumers - 1) / kConsumers;
   const int grid = (int)(want < sm_count() ? want : sm_count());
-  corr_tiled_kernel<<<grid, kThreads, kSmemBytes, st>>>(ms, ml, P);
+  corr_tiled_kernel<<<grid, kThreads, kSmemBytes, st>>>(ms, mh, P);
   WV_LAUNCH_CHECK();
   return WV_OK;
 }
