@@ -45,29 +45,25 @@ constexpr int kMaxPix = kBoxLarge * kBoxLarge;             // 144 columns of D a
 constexpr int kHalfBytes = 13 * 1024;                      // one 64-channel half of a stage: 100 px x 128 B = 12 800 (1024-B aligned slots)
 constexpr int kPatchOff = 2 * kHalfBytes;                  // 26 624: the [9][128] fp16 patch
 constexpr int kPatchBytes = kC * kPP * 2;                  // 2 304
-constexpr int kRecOff = kPatchOff + kPatchBytes;           // 28 928: the 128-B edge record
 constexpr int kStageBytes = 29 * 1024;                     // 29 696
 constexpr int kRawStride = 152;                            // floats per patch-pixel row of D (bank-conflict-free stores)
 constexpr int kRawBytes = kPP * kRawStride * 4;            // 5 472
+constexpr int kRecBytes = 96;                              // per-edge record (below)
+constexpr int kRecRing = 2 * 32 * kRecBytes;               // two producer batches of 32 records
 constexpr int kBarBytes = (kStages + 2 * kConsumers) * 8 + kConsumers * 4 + 32;
-constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kConsumers * kRawBytes + kBarBytes;
+constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kConsumers * kRawBytes + kRecRing + kBarBytes;
 constexpr int kClamp = 1 << 20;
 static_assert(kBoxSmall * kBoxSmall * 128 <= kHalfBytes && kBoxLarge * kBoxLargeRows * 128 <= kHalfBytes, "tile must fit its slot");
+static_assert(kPatchOff + kPatchBytes <= kStageBytes, "patch must fit its slot");
 static_assert(kSmemBytes <= 227 * 1024, "shared memory budget");
 
-// the record the producer writes next to each tile
+// the record the producer leaves for the consumer of an edge (all 32 lanes write theirs at once)
 struct EdgeRec {
-  long long be;        // b * E + e
-  int kind;            // 0 small tile, 1 half of a large tile, 2 direct gather, 3 nothing to read (outside / bad index)
-  int part, nparts;    // large tiles arrive as two slots
-  int BX;              // row pitch of the D column space (10, 12; 8 for the gather path)
-  int has_patch;       // the patch differs from the one of the warp's previous edge: (re)load the A fragments
-  int slot;            // b * n2 + jj (gather path)
-  int org[kPP];        // column of pixel p's window origin in D
-  float dx[kPP], dy[kPP];
-  int fx[kPP], fy[kPP];  // kind 2 only: integer tap origins in the map
+  int flags;                  // kind (bits 0-1): 0 small tile, 1 large tile in two halves, 2 direct gather, 3 nothing to read; bit 2: load the patch
+  unsigned char org[12];      // column of pixel p's window origin in the D column space (< 144)
+  float dx[kPP], dy[kPP];     // bilinear fractions
 };
-static_assert(kRecOff + sizeof(EdgeRec) <= kStageBytes, "record slot");
+static_assert(sizeof(EdgeRec) <= kRecBytes, "record slot");
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -266,7 +262,8 @@ corr_tiled_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_co
   // barrier that is a phase ahead of it (parity waits cannot tell "two phases ago" from "now").  empty[s] (per stage): the
   // consumer is done reading stage s; waited on by the producer alone, in ring order.
   const uint32_t full0 = smem_u32(bars), taken0 = full0 + 8 * kConsumers, empty0 = taken0 + 8 * kConsumers;
-  volatile int* mailbox = reinterpret_cast<volatile int*>(bars + 2 * kConsumers + kStages);  // [kConsumers]: stage of the slot
+  volatile int* mailbox = reinterpret_cast<volatile int*>(bars + 2 * kConsumers + kStages);  // [kConsumers]: stage | record << 8 | half << 16
+  uint8_t* recring = reinterpret_cast<uint8_t*>(bars) + kBarBytes;                           // [2][32] EdgeRec
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 
   if (threadIdx.x == 0) {
@@ -284,20 +281,19 @@ corr_tiled_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_co
 
   if (warp == kConsumers) {
     // ================================================================= producer
-    const int pw = lane >> 2, pj = lane & 3;             // this lane prepares edge 4*batch + pj of consumer warp pw
+    const int pw = lane >> 2, pj = lane & 3;             // this lane prepares AND issues edge 4*batch + pj of consumer warp pw
     const int cntw = max(0, min(per, nt - pw * per));
     long long carry_pid = -1;                            // patch of warp pw's last edge of the previous batch
-    int my_m = 0;                                        // lanes 0..7: slots emitted so far to consumer warp `lane`
-    int seq = 0;                                         // slots emitted so far (warp-uniform)
+    int m_mine = 0;                                      // slots issued so far to consumer warp pw (same in its four lanes)
+    int seq = 0;                                         // slots issued so far by the whole warp (uniform)
     const int nbatch = (per + 3) >> 2;
     for (int bt = 0; bt < nbatch; bt++) {
       // ---- every lane prepares one edge; the 32 edges' global loads overlap
       const int k = 4 * bt + pj;
       const bool valid = k < cntw;
-      EdgeRec r;
-      r.kind = 3; r.nparts = 1; r.BX = kD; r.slot = 0; r.be = 0; r.has_patch = 0;
-      int x0 = 0, y0 = 0;
+      int kind = 3, x0 = 0, y0 = 0, slot = 0, has_patch = 0;
       long long pid = -1;
+      EdgeRec* myrec = reinterpret_cast<EdgeRec*>(recring + ((bt & 1) * 32 + lane) * kRecBytes);
       if (valid) {
         const long long be = lo + (long long)pw * per + k;
         const int b = (int)(be / P.E), e = (int)(be % P.E);
@@ -306,83 +302,69 @@ corr_tiled_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_co
         float v[2 * kPP];
 #pragma unroll
         for (int i = 0; i < kPP; i++) { const float2 t = c2[i]; v[2 * i] = t.x; v[2 * i + 1] = t.y; }
+        int fx[kPP], fy[kPP];
         int mnx = kClamp * 2, mxx = -kClamp * 2, mny = kClamp * 2, mxy = -kClamp * 2;
 #pragma unroll
         for (int p = 0; p < kPP; p++) {
-          r.fx[p] = clamp_floor(v[p]); r.fy[p] = clamp_floor(v[kPP + p]);
-          r.dx[p] = v[p] - floorf(v[p]); r.dy[p] = v[kPP + p] - floorf(v[kPP + p]);
-          mnx = min(mnx, r.fx[p]); mxx = max(mxx, r.fx[p]); mny = min(mny, r.fy[p]); mxy = max(mxy, r.fy[p]);
+          fx[p] = clamp_floor(v[p]); fy[p] = clamp_floor(v[kPP + p]);
+          myrec->dx[p] = v[p] - floorf(v[p]); myrec->dy[p] = v[kPP + p] - floorf(v[kPP + p]);
+          mnx = min(mnx, fx[p]); mxx = max(mxx, fx[p]); mny = min(mny, fy[p]); mxy = max(mxy, fy[p]);
         }
         x0 = mnx - kR; y0 = mny - kR;
         const int wdt = mxx - mnx + kD, hgt = mxy - mny + kD;
         const bool bad = ix < 0 || ix >= P.n1 || jx < 0 || jx >= P.n2;
         const bool outside = x0 >= P.W || y0 >= P.H || x0 + wdt <= 0 || y0 + hgt <= 0;
         if (bad) set_status(P.status, WV_STATUS_BAD_INDEX);
-        if (bad || outside) r.kind = 3;
-        else if (wdt <= kBoxSmall && hgt <= kBoxSmall) { r.kind = 0; r.BX = kBoxSmall; }
-        else if (wdt <= kBoxLarge && hgt <= kBoxLarge) { r.kind = 1; r.BX = kBoxLarge; r.nparts = 2; }
-        else r.kind = 2;
-        r.be = be;
-        r.slot = bad ? 0 : b * P.n2 + (int)jx;
-        if (r.kind <= 2) pid = (long long)b * P.n1 + ix;
+        int BX = kD;
+        if (bad || outside) kind = 3;
+        else if (wdt <= kBoxSmall && hgt <= kBoxSmall) { kind = 0; BX = kBoxSmall; }
+        else if (wdt <= kBoxLarge && hgt <= kBoxLarge) { kind = 1; BX = kBoxLarge; }
+        else kind = 2;
+        slot = bad ? 0 : b * P.n2 + (int)jx;
+        if (kind <= 2) pid = (long long)b * P.n1 + ix;
 #pragma unroll
-        for (int p = 0; p < kPP; p++) r.org[p] = r.kind <= 1 ? (r.fy[p] - mny) * r.BX + (r.fx[p] - mnx) : 0;
+        for (int p = 0; p < kPP; p++) myrec->org[p] = (unsigned char)(kind <= 1 ? (fy[p] - mny) * BX + (fx[p] - mnx) : 0);
       }
       {
         const long long up = __shfl_up_sync(0xffffffffu, pid, 1);
         const long long prev = pj == 0 ? carry_pid : up;
-        r.has_patch = (pid >= 0 && (pid != prev || r.kind == 2)) ? 1 : 0;
+        has_patch = (pid >= 0 && (pid != prev || kind == 2)) ? 1 : 0;
         carry_pid = __shfl_sync(0xffffffffu, pid, (lane & ~3) | 3);
       }
-      const unsigned vmask = __ballot_sync(0xffffffffu, valid), lmask = __ballot_sync(0xffffffffu, valid && r.kind == 1);
+      if (valid) myrec->flags = kind | (has_patch << 2);
+      const unsigned vmask = __ballot_sync(0xffffffffu, valid), lmask = __ballot_sync(0xffffffffu, valid && kind == 1);
+      __syncwarp();
 
-      // ---- lane 0 feeds the ring: warps round-robin, each warp's slots in order
+      // ---- the ring is fed in a fixed order (edge j, half, warp w): warps round-robin, each warp's slots in order.
+      // The lane that prepared an edge issues it itself (its operands are in its own registers).
       for (int jp = 0; jp < 8; jp++) {
         const int j = jp >> 1, part = jp & 1;
-        const unsigned cand = part == 0 ? vmask : lmask;
-        for (int w = 0; w < kConsumers; w++) {
-          const int src = 4 * w + j;
-          if (!((cand >> src) & 1u)) continue;
+        unsigned sub = ((part == 0 ? vmask : lmask) >> j) & 0x11111111u;
+        while (sub) {
+          const int bit = __ffs(sub) - 1;
+          sub &= sub - 1;
+          const int w = bit >> 2, src = bit + j;
           const int stage = seq % kStages;
-          uint8_t* sb = stages + (size_t)stage * kStageBytes;
-          const int kd = __shfl_sync(0xffffffffu, r.kind, src), hp = __shfl_sync(0xffffffffu, r.has_patch, src);
-          const int bx = __shfl_sync(0xffffffffu, x0, src), by = __shfl_sync(0xffffffffu, y0, src);
-          const int sl = __shfl_sync(0xffffffffu, r.slot, src), m = __shfl_sync(0xffffffffu, my_m, w);
-          const long long pd = __shfl_sync(0xffffffffu, pid, src);
-          if (lane == 0) {
-            mbar_wait(empty0 + 8 * stage, ((seq / kStages) & 1) ^ 1);
-            if (m > 0) mbar_wait(taken0 + 8 * w, (m - 1) & 1);
-          }
-          __syncwarp();
           if (lane == src) {
-            EdgeRec* d = reinterpret_cast<EdgeRec*>(sb + kRecOff);
-            d->be = r.be; d->kind = r.kind; d->part = part; d->nparts = r.nparts; d->BX = r.BX;
-            d->has_patch = part == 0 ? r.has_patch : 0; d->slot = r.slot;
-#pragma unroll
-            for (int p = 0; p < kPP; p++) { d->org[p] = r.org[p]; d->dx[p] = r.dx[p]; d->dy[p] = r.dy[p]; }
-            if (r.kind == 2) {
-#pragma unroll
-              for (int p = 0; p < kPP; p++) { d->fx[p] = r.fx[p]; d->fy[p] = r.fy[p]; }
-            }
-          }
-          __syncwarp();
-          if (lane == 0) {
-            mailbox[w] = stage;
-            const uint32_t bar = full0 + 8 * w, dst = smem_u32(sb);
-            const bool patch_now = hp && part == 0;
-            const int npix = kd == 0 ? kBoxSmall * kBoxSmall : kBoxLarge * kBoxLargeRows;
-            const uint32_t bytes = (kd <= 1 ? 2u * npix * 128u : 0u) + (patch_now ? (uint32_t)kPatchBytes : 0u);
+            mbar_wait(empty0 + 8 * stage, ((seq / kStages) & 1) ^ 1);
+            if (m_mine > 0) mbar_wait(taken0 + 8 * w, (m_mine - 1) & 1);
+            mailbox[w] = stage | (((bt & 1) * 32 + lane) << 8) | (part << 16);
+            const uint32_t bar = full0 + 8 * w, dst = smem_u32(stages + (size_t)stage * kStageBytes);
+            const bool patch_now = has_patch && part == 0;
+            const int npix = kind == 0 ? kBoxSmall * kBoxSmall : kBoxLarge * kBoxLargeRows;
+            const uint32_t bytes = (kind <= 1 ? 2u * npix * 128u : 0u) + (patch_now ? (uint32_t)kPatchBytes : 0u);
             if (bytes) mbar_arrive_expect_tx(bar, bytes); else mbar_arrive(bar);
-            if (kd <= 1) {
-              const CUtensorMap* map = kd == 0 ? &map_small : &map_half;
-              const int yy = by + part * kBoxLargeRows;
-              tma_load_4d(dst, map, bar, 0, bx, yy, sl);
-              tma_load_4d(dst + kHalfBytes, map, bar, 64, bx, yy, sl);
+            if (kind <= 1) {
+              const CUtensorMap* map = kind == 0 ? &map_small : &map_half;
+              const int yy = y0 + part * kBoxLargeRows;
+              tma_load_4d(dst, map, bar, 0, x0, yy, slot);
+              tma_load_4d(dst + kHalfBytes, map, bar, 64, x0, yy, slot);
             }
-            if (patch_now) bulk_copy_g2s(dst + kPatchOff, P.gT + pd * (kC * kPP), kPatchBytes, bar);
+            if (patch_now) bulk_copy_g2s(dst + kPatchOff, P.gT + pid * (kC * kPP), kPatchBytes, bar);
           }
-          if (lane == w) my_m++;
+          if (w == pw) m_mine++;
           seq++;
+          __syncwarp();
         }
       }
     }
@@ -408,20 +390,22 @@ corr_tiled_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_co
   int m = 0;
   for (int done = 0; done < cnt;) {
     mbar_wait(fullb, m & 1);
-    const int stage = mailbox[warp];
+    const int mb = mailbox[warp];
+    const int stage = mb & 0xff, part = (mb >> 16) & 1;
     const uint8_t* sb = stages + (size_t)stage * kStageBytes;
-    const EdgeRec* rec = reinterpret_cast<const EdgeRec*>(sb + kRecOff);
-    const long long be = rec->be;
-    const int kind = rec->kind, part = rec->part, nparts = rec->nparts, BX = rec->BX, has_patch = rec->has_patch;
+    const EdgeRec* rec = reinterpret_cast<const EdgeRec*>(recring + ((mb >> 8) & 0xff) * kRecBytes);
+    const int flags = rec->flags, kind = flags & 3, has_patch = part == 0 ? (flags >> 2) & 1 : 0;
+    const int nparts = kind == 1 ? 2 : 1, BX = kind == 0 ? kBoxSmall : (kind == 1 ? kBoxLarge : kD);
+    const long long be = lo + (long long)warp * per + done;
+    if (part == 0 && lane < kPP) {  // geometry of each patch pixel next to its D row
+      float* gr = rawD + lane * kRawStride + kMaxPix;
+      gr[0] = __int_as_float((int)rec->org[lane]); gr[1] = rec->dx[lane]; gr[2] = rec->dy[lane];
+    }
     __syncwarp();
-    if (lane == 0) mbar_arrive(takenb);
+    if (lane == 0) mbar_arrive(takenb);  // the record and the mailbox may be reused from here on
     m++;
     const uint32_t st = smem_u32(sb);
 
-    if (part == 0 && lane < kPP) {  // geometry of each patch pixel next to its D row
-      float* gr = rawD + lane * kRawStride + kMaxPix;
-      gr[0] = __int_as_float(rec->org[lane]); gr[1] = rec->dx[lane]; gr[2] = rec->dy[lane];
-    }
     if (has_patch) {
 #pragma unroll
       for (int ks = 0; ks < 8; ks++) ldmatrix_x4(st + kPatchOff + a_off + ks * 32, A[ks][0], A[ks][1], A[ks][2], A[ks][3]);
@@ -443,12 +427,16 @@ corr_tiled_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_co
       }
     } else if (kind == 2) {
       // -------------------------------------------------------------- direct gather (windows too far apart for a tile)
+      // (rare; this path alone reads global memory from a consumer: coords and jj of its edge)
       const size_t plane = (size_t)P.H * P.W;
-      const __half* f2 = P.fmap2 + (size_t)rec->slot * kC * plane;
+      const int eb = (int)(be / P.E), ee = (int)(be % P.E);
+      const __half* f2 = P.fmap2 + ((size_t)eb * P.n2 + (size_t)P.jj[ee]) * kC * plane;
       const __half* pt = reinterpret_cast<const __half*>(sb + kPatchOff);  // [9][128]
+      const float cv = lane < 2 * kPP ? P.coords[be * (2 * kPP) + lane] : 0.f;
+      const int fl = clamp_floor(cv);
       for (int t = lane; t < kPP * kD * kD; t += 32) {
         const int b = t & 7, a = (t >> 3) & 7, p = t >> 6;
-        const int i1 = rec->fy[p] + a - kR, j1 = rec->fx[p] + b - kR;
+        const int i1 = __shfl_sync(0xffffffffu, fl, kPP + p) + a - kR, j1 = __shfl_sync(0xffffffffu, fl, p) + b - kR;
         float sacc = 0.f;
         if (i1 >= 0 && i1 < P.H && j1 >= 0 && j1 < P.W) {
           const __half* p2 = f2 + (size_t)i1 * P.W + j1;
