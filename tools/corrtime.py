@@ -1,0 +1,23 @@
+import sys, os, importlib, numpy as np, torch
+sys.path.insert(0, os.getcwd())
+pkg = importlib.import_module("wild-video-3d-reconstruction_b200")
+cc, cb = pkg.native_modules()
+syn = pkg.synthetic
+w = syn.make_corr_workload(seed=1)
+dev = torch.device("cuda")
+g = torch.from_numpy(w["gmap"]).half().to(dev)
+f0 = torch.from_numpy(w["fmap0"]).half().to(dev); f1 = torch.from_numpy(w["fmap1"]).half().to(dev)
+c0 = torch.from_numpy(w["coords"]).to(dev); c1 = (c0 / 4).contiguous()
+ii = torch.from_numpy(w["ii1"]).to(dev); jj = torch.from_numpy(w["jj1"]).to(dev)
+flush = torch.empty(512 << 20, dtype=torch.uint8, device=dev)
+def t(fm, co, n=10):
+    ts = []
+    for i in range(n + 3):
+        flush.fill_(1)
+        a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
+        a.record(); cc.forward(g, fm, co, ii, jj, 3); b.record(); torch.cuda.synchronize()
+        if i >= 3: ts.append(a.elapsed_time(b))
+    return np.median(ts)
+for dbg in sys.argv[1:]:
+    os.environ["WVB200_CORR_DBG"] = dbg
+    print("dbg", dbg, "L0 %.3f ms  L1 %.3f ms" % (t(f0, c0), t(f1, c1)), flush=True)

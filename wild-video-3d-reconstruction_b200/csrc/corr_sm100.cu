@@ -38,7 +38,8 @@ namespace {
 
 constexpr int kC = 128, kP = 3, kPP = 9, kR = 3, kD = 8, kT = 7;
 constexpr int kConsumers = 8;
-constexpr int kThreads = 32 * (kConsumers + 1);
+constexpr int kProducers = 2;                              // each feeds kConsumers / kProducers consumer warps through its own stages
+constexpr int kThreads = 32 * (kConsumers + kProducers);
 constexpr int kStages = 6;
 constexpr int kBoxSmall = 10, kBoxLarge = 12, kBoxLargeRows = 6;  // tile shapes: 10x10, or 12x12 as two 12x6 halves
 constexpr int kMaxPix = kBoxLarge * kBoxLarge;             // 144 columns of D at most
@@ -49,7 +50,7 @@ constexpr int kStageBytes = 29 * 1024;                     // 29 696
 constexpr int kRawStride = 152;                            // floats per patch-pixel row of D (bank-conflict-free stores)
 constexpr int kRawBytes = kPP * kRawStride * 4;            // 5 472
 constexpr int kRecBytes = 96;                              // per-edge record (below)
-constexpr int kRecRing = 2 * 32 * kRecBytes;               // two producer batches of 32 records
+constexpr int kRecRing = 2 * 32 * kRecBytes;               // per producer: two batches of 16 records
 constexpr int kBarBytes = (kStages + 2 * kConsumers) * 8 + kConsumers * 4 + 32;
 constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kConsumers * kRawBytes + kRecRing + kBarBytes;
 constexpr int kClamp = 1 << 20;
@@ -219,7 +220,7 @@ __device__ __forceinline__ void bulk_copy_g2s(uint32_t dst, const void* src, uin
                : "memory");
 }
 
-// NT (<= 4) pixel tiles of 8 px: D[16 x 8*NT] = A[16 x 128] . tile^T, B fragments double-buffered one 32-channel step ahead.
+// NT pixel tiles of 8 px: D[16 x 8*NT] = A[16 x 128] . tile^T, B fragments double-buffered one 32-channel step ahead.
 // a0 / a1: this lane's ldmatrix address in tile 0 for chunks 0..3 / 4..7 of the 128-B rows (swizzle folded in).
 template <int NT>
 __device__ __forceinline__ void mma_group(uint32_t a0, uint32_t a1, const uint32_t (&A)[8][4], float* d0, float* d8, bool has8) {
@@ -279,10 +280,15 @@ corr_tiled_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_co
   const int nt = (int)(hi - lo);
   const int per = (nt + kConsumers - 1) / kConsumers;  // edges per consumer warp (contiguous runs: consecutive edges share patches)
 
-  if (warp == kConsumers) {
-    // ================================================================= producer
-    const int pw = lane >> 2, pj = lane & 3;             // this lane prepares AND issues edge 4*batch + pj of consumer warp pw
-    const int cntw = max(0, min(per, nt - pw * per));
+  if (warp >= kConsumers) {
+    // ================================================================= producers
+    // producer pi serves consumer warps [pi*WPP, (pi+1)*WPP) through stages [pi*SPP, (pi+1)*SPP); lanes 0 .. 4*WPP-1 work
+    constexpr int WPP = kConsumers / kProducers, SPP = kStages / kProducers;
+    static_assert(kConsumers % kProducers == 0 && kStages % kProducers == 0 && 4 * WPP <= 32, "producer split");
+    const int pi = warp - kConsumers;
+    const bool plane = lane < 4 * WPP;
+    const int pw = pi * WPP + ((lane >> 2) % WPP), pj = lane & 3;  // this lane prepares AND issues edge 4*batch + pj of consumer warp pw
+    const int cntw = plane ? max(0, min(per, nt - pw * per)) : 0;
     long long carry_pid = -1;                            // patch of warp pw's last edge of the previous batch
     int m_mine = 0;                                      // slots issued so far to consumer warp pw (same in its four lanes)
     int seq = 0;                                         // slots issued so far by the whole warp (uniform)
@@ -293,7 +299,8 @@ corr_tiled_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_co
       const bool valid = k < cntw;
       int kind = 3, x0 = 0, y0 = 0, slot = 0, has_patch = 0;
       long long pid = -1;
-      EdgeRec* myrec = reinterpret_cast<EdgeRec*>(recring + ((bt & 1) * 32 + lane) * kRecBytes);
+      const int recidx = (pi * 2 + (bt & 1)) * (4 * WPP) + lane;
+      EdgeRec* myrec = reinterpret_cast<EdgeRec*>(recring + recidx * kRecBytes);
       if (valid) {
         const long long be = lo + (long long)pw * per + k;
         const int b = (int)(be / P.E), e = (int)(be % P.E);
@@ -343,12 +350,12 @@ corr_tiled_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_co
         while (sub) {
           const int bit = __ffs(sub) - 1;
           sub &= sub - 1;
-          const int w = bit >> 2, src = bit + j;
-          const int stage = seq % kStages;
+          const int w = pi * WPP + (bit >> 2), src = bit + j;
+          const int stage = pi * SPP + seq % SPP;
           if (lane == src) {
-            mbar_wait(empty0 + 8 * stage, ((seq / kStages) & 1) ^ 1);
+            mbar_wait(empty0 + 8 * stage, ((seq / SPP) & 1) ^ 1);
             if (m_mine > 0) mbar_wait(taken0 + 8 * w, (m_mine - 1) & 1);
-            mailbox[w] = stage | (((bt & 1) * 32 + lane) << 8) | (part << 16);
+            mailbox[w] = stage | (recidx << 8) | (part << 16);
             const uint32_t bar = full0 + 8 * w, dst = smem_u32(stages + (size_t)stage * kStageBytes);
             const bool patch_now = has_patch && part == 0;
             const int npix = kind == 0 ? kBoxSmall * kBoxSmall : kBoxLarge * kBoxLargeRows;
@@ -415,15 +422,12 @@ corr_tiled_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_co
       // -------------------------------------------------------------- tensor-core contraction from the TMA tile
       const uint32_t a0 = st + lds_off0, a1 = st + lds_off1;
       if (kind == 0) {  // 100 px -> 13 pixel tiles (the last one half used)
-        mma_group<4>(a0, a1, A, d0, d8, has8);
-        mma_group<4>(a0 + 4 * 1024, a1 + 4 * 1024, A, d0 + 32, d8 + 32, has8);
-        mma_group<4>(a0 + 8 * 1024, a1 + 8 * 1024, A, d0 + 64, d8 + 64, has8);
-        mma_group<1>(a0 + 12 * 1024, a1 + 12 * 1024, A, d0 + 96, d8 + 96, has8);
+        mma_group<7>(a0, a1, A, d0, d8, has8);  // 7 + 6 tiles: two dependent chains of 8 MMAs instead of four
+        mma_group<6>(a0 + 7 * 1024, a1 + 7 * 1024, A, d0 + 56, d8 + 56, has8);
       } else {          // half of a 12x12 window: 72 px -> 9 pixel tiles, D columns 72*part ..
         const int c0 = part * (kBoxLarge * kBoxLargeRows);
-        mma_group<4>(a0, a1, A, d0 + c0, d8 + c0, has8);
-        mma_group<4>(a0 + 4 * 1024, a1 + 4 * 1024, A, d0 + c0 + 32, d8 + c0 + 32, has8);
-        mma_group<1>(a0 + 8 * 1024, a1 + 8 * 1024, A, d0 + c0 + 64, d8 + c0 + 64, has8);
+        mma_group<5>(a0, a1, A, d0 + c0, d8 + c0, has8);
+        mma_group<4>(a0 + 5 * 1024, a1 + 5 * 1024, A, d0 + c0 + 40, d8 + c0 + 40, has8);
       }
     } else if (kind == 2) {
       // -------------------------------------------------------------- direct gather (windows too far apart for a tile)
