@@ -34,6 +34,8 @@ for p in (ROOT,):
 # indices + output):  s*C*P^2 + s*C*F + 4*2*P^2 + 2*8 + s*49*P^2,  F0 = 100 px, F1 = 81 px
 CORR_BYTES_L0 = 2 * 128 * 9 + 2 * 128 * 100 + 72 + 16 + 2 * 49 * 9   # 28 874
 CORR_BYTES_L1 = 2 * 128 * 9 + 2 * 128 * 81 + 72 + 16 + 2 * 49 * 9    # 24 010
+# dram__bytes_read.sum + dram__bytes_write.sum per level-0 call (restage 121.2 + 73.4 MB, tiled 278.9 + 37.4 MB), ncu --set full
+NCU_TRAFFIC_L0 = 510.9e6
 WORKLOAD = ("configs[1]: 512x384 -> fmaps 96x128 + 24x32, C=128 fp16, pmem=36, M=96, tracker edge list E=45312, "
             "radius 3; one update(): corr x2 levels + neighbors + BA(10 free poses, 2 GN iterations)")
 
@@ -46,9 +48,13 @@ def measured_peak_gbs():
         return 6650.0, "fallback"
 
 
-def make_inputs(seed_offset=0):
-    """numpy inputs of one step (seeded; rank r uses its own clip)"""
+def make_inputs(seed_offset=0, small=False):
+    """numpy inputs of one step (seeded; rank r uses its own clip).  small=True: a reduced copy for the CPU tests."""
     syn = importlib.import_module(PKG + ".synthetic")
+    if small:
+        w = syn.make_corr_workload(seed=1 + 1000 * seed_offset, M=4, pmem=8, n_frames=10, ht=24, wd=32, lifetime=4, removal=6)
+        s = syn.make_ba_scene(seed=2 + 1000 * seed_offset, n=10, M=4, edges="tracker", lifetime=4, removal=6)
+        return w, s
     w = syn.make_corr_workload(seed=1 + 1000 * seed_offset)
     s = syn.make_ba_scene(seed=2 + 1000 * seed_offset, n=40, M=96, edges="tracker")
     assert w["E"] == len(s["kk"]) == 45312
@@ -288,32 +294,31 @@ def run_b200(args):
     t_max = float(tt.item())
 
     # ---- end to end through the C ABI with HOST buffers (pinned), copies inside the timed region -----------------
+    # the call a non-torch embedder makes: hostapi.Session.update == wv_session_update_host (include/wvb200.h)
     T = 7
     out0 = torch.empty((1, E, T, T, 3, 3), dtype=torch.half).pin_memory()
     out1 = torch.empty_like(out0).pin_memory()
     hp, hq = H["poses"].clone().pin_memory(), H["patches"].clone().pin_memory()
-    vp = lambda t: ctypes.c_void_p(t.data_ptr())  # noqa: E731
-    fb = lib.wv_ba_forward_host
-    fb.argtypes = [ctypes.c_void_p] * 9 + [ctypes.c_int64] * 3 + [ctypes.c_int] * 4 + [ctypes.c_void_p, ctypes.c_float, ctypes.c_void_p, ctypes.c_void_p]
-    fc = lib.wv_corr_forward_host
-    fc.argtypes = [ctypes.c_void_p] * 6 + [ctypes.c_int] * 11 + [ctypes.c_void_p]
-    st = ctypes.c_int(0)
-    n1, n2 = H["gmap"].shape[1], H["f0"].shape[1]
+    nbx, nbj = torch.empty(E, dtype=torch.long).pin_memory(), torch.empty(E, dtype=torch.long).pin_memory()
+    sess = pkg.hostapi.Session()
+    ba = dict(poses=hp, patches=hq, intrinsics=H["intr"], target=H["target"], weight=H["weight"], lmbda=H["lmbda"],
+              ii=H["ii"], jj=H["jj"], kk=H["kk"], t0=t0, t1=t1, nb_ix=nbx, nb_jx=nbj)
+    uargs = sess.make_args(H["gmap"], [H["f0"], H["f1"]], H["c0"], H["ii1"], H["jj1"], [out0, out1], radius=3, ba=ba, iterations=2)
 
     def e2e_step():
         hp.copy_(H["poses"]); hq.copy_(H["patches"])
-        rc = fc(vp(H["gmap"]), vp(H["f0"]), vp(H["c0"]), vp(H["ii1"]), vp(H["jj1"]), vp(out0), 0, 1, E, 128, 3, 3, n1, n2, 96, 128, 3, None)
-        rc |= fc(vp(H["gmap"]), vp(H["f1"]), vp(H["c1"]), vp(H["ii1"]), vp(H["jj1"]), vp(out1), 0, 1, E, 128, 3, 3, n1, n2, 24, 32, 3, None)
-        rc |= fb(vp(hp), vp(hq), vp(H["intr"]), vp(H["target"]), vp(H["weight"]), vp(H["lmbda"]), vp(H["ii"]), vp(H["jj"]), vp(H["kk"]),
-                 E, hp.shape[0], hq.shape[0], 3, t0, t1, 2, None, 2.0, ctypes.byref(st), None)
-        assert rc == 0 and st.value == 0, (rc, st.value)
+        sess.run(uargs)
 
     nb = lambda *ks: sum(H[k].numel() * H[k].element_size() for k in ks)  # noqa: E731
-    h2d = nb("gmap", "f0", "c0", "ii1", "jj1") + nb("gmap", "f1", "c1", "ii1", "jj1") + \
-        nb("poses", "patches", "intr", "target", "weight", "lmbda", "ii", "jj", "kk")
-    d2h = 2 * out0.numel() * 2 + nb("poses", "patches") + 4
+    h2d = nb("gmap", "f0", "f1", "c0", "ii1", "jj1", "poses", "patches", "intr", "target", "weight", "lmbda", "ii", "jj", "kk")
+    d2h = 2 * out0.numel() * 2 + nb("poses", "patches") + 2 * E * 8 + 4
     for _ in range(3):
         e2e_step()
+    # the e2e result is the product's result: check it once against the device-resident path of the timed loop above
+    c0d, c1d, ixd = step(False)
+    torch.cuda.synchronize()
+    assert torch.equal(out0, c0d.cpu()) and torch.equal(out1, c1d.cpu()) and torch.equal(nbx, ixd.cpu()), "e2e != device path"
+    assert torch.equal(hp, poses.cpu()), "e2e BA != device path"
     barrier()
     te = time.perf_counter()
     for _ in range(args.steps):
@@ -324,6 +329,7 @@ def run_b200(args):
     if world > 1:
         dist.all_reduce(tte, op=dist.ReduceOp.MAX)
     te = float(tte.item())
+    sess.close()
 
     if rank == 0:
         K = args.steps
@@ -342,12 +348,13 @@ def run_b200(args):
             "ba_iters_per_s": 2.0 / (float(seg[:, 3].mean()) * 1e-3),
             "wall_ms_per_step_incl_flush": 1e3 * wall / K,
             "roofline": {"kernel": "corr forward, level 0 (fp16 maps)", "bound": "hbm", "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": NCU_TRAFFIC_L0, "peak_source": peak_src,
+                         "traffic_source": "dram__bytes_read+write of restage_kernel + corr_tiled_kernel, ncu --set full, profiles/r1_corr_tiled_final_ncu_summary.txt",
                          "algorithmic_bytes_per_launch": CORR_BYTES_L0 * E},
             "e2e": {"value": world * K / te, "unit": "frames/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                    "api": "wv_corr_forward_host x2 + wv_ba_forward_host (C ABI, pinned host buffers)"},
-            "gpu_launches": 5 * K,
-            "gpu_launches_per_step": "corr x2, plan (neighbors), plan + window kernel (BA)",
+                    "api": "hostapi.Session.update -> wv_session_update_host (C ABI, pinned host buffers, 3 streams)"},
+            "gpu_launches": 7 * K,
+            "gpu_launches_per_step": "corr: (restage + tiled kernel) x2 levels; plan (neighbors); plan + window kernel (BA)",
             "clocks": clocks,
         }
         if world == 1 and not args.no_cpu:

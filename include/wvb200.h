@@ -146,6 +146,44 @@ int wv_ba_forward_host(float* poses, float* patches, const float* intrinsics, co
                        int t1, int iterations, const float* patches_est, float mu, int* status_out,
                        wv_stream_t stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * host-buffer session: one tracker update() per call -- altcorr.corr on every pyramid level
+ * (dpvo/dpvo.py:326-333: the same coords divided by 1, 4, ...), fastba.neighbors and fastba.BA on the
+ * same edge list (dpvo/dpvo.py:711-749) -- with HOST buffers in and out.  The session keeps its
+ * device buffers and three streams between calls; uploads, kernels and downloads of the different
+ * pieces overlap (small inputs and the coarse level first, the big level-0 ring last, each result
+ * downloaded while the next piece is still being uploaded).  Pinned host memory makes the copies
+ * asynchronous; pageable memory works and serialises them.  The call returns when everything has
+ * landed in the caller's buffers.
+ * ------------------------------------------------------------------------------------------- */
+typedef struct wv_session wv_session;
+
+typedef struct {
+  /* correlation */
+  int dtype, B, E, C, P, radius, n1, n2, nlevels; /* nlevels <= 4 */
+  const void* fmap1;                              /* [B][n1][C][P][P] */
+  const void* fmap2[4];                           /* level l: [B][n2][C][H2[l]][W2[l]] */
+  int H2[4], W2[4];
+  float coord_scale[4];                           /* level l correlates at coords * coord_scale[l] (1, 0.25, ...) */
+  const float* coords;                            /* [B][E][2][P][P] at level-0 resolution */
+  const int64_t* ii1;                             /* [E] patch slot in fmap1, jj1: frame slot in fmap2 */
+  const int64_t* jj1;
+  void* corr_out[4];                              /* level l: [B][E][2r+1][2r+1][P][P] (dtype) */
+  /* bundle adjustment + neighbors on the same E edges; iterations == 0 skips both */
+  float* poses; float* patches;                   /* in/out */
+  const float* intrinsics; const float* target; const float* weight; const float* lmbda;
+  const int64_t* ii; const int64_t* jj; const int64_t* kk;
+  int64_t n_poses, n_patches;
+  int t0, t1, iterations;
+  const float* patches_est; float mu;             /* nullable prior (see wv_ba_forward) */
+  int64_t* nb_ix; int64_t* nb_jx;                 /* nullable: neighbors(kk, jj) */
+  int status;                                     /* out: WV_STATUS_* bits */
+} wv_update_args;
+
+wv_session* wv_session_create(void);              /* on the current device; NULL on failure */
+void wv_session_destroy(wv_session* s);
+int wv_session_update_host(wv_session* s, wv_update_args* a);
+
 #ifdef __cplusplus
 }
 #endif

@@ -362,3 +362,35 @@ def test_corr_tiled_bad_index_and_nonfinite(golden):
                 cc.forward(g, f, dev(co), torch.tensor([0, 9, 2], device="cuda"), torch.tensor([0, 1, 1], device="cuda"), 3)
     finally:
         del os.environ["WVB200_CHECK_INDICES"]
+
+
+def test_host_session_update_matches_device_path(syn):
+    """hostapi.Session (wv_session_update_host): host buffers in/out, three streams; same bits as the tensor path"""
+    w = syn.make_corr_workload(seed=3, M=8, pmem=12, n_frames=14, ht=24, wd=32, C=128, lifetime=6, removal=9, oob_frac=0.1)
+    s = syn.make_ba_scene(seed=2, n=14, M=8, edges="tracker", lifetime=6, removal=9)
+    E = w["E"]
+    assert E == len(s["kk"])
+    g16 = torch.from_numpy(w["gmap"]).half(); f0 = torch.from_numpy(w["fmap0"]).half(); f1 = torch.from_numpy(w["fmap1"]).half()
+    co = torch.from_numpy(w["coords"]); ii1 = torch.from_numpy(w["ii1"]); jj1 = torch.from_numpy(w["jj1"])
+    out0 = torch.empty((1, E, 7, 7, 3, 3), dtype=torch.half); out1 = torch.empty_like(out0)
+    T = lambda k: torch.from_numpy(s[k].copy())  # noqa: E731
+    t0, t1 = int(s["t1"]) - 6, int(s["t1"])
+    ba = dict(poses=T("poses"), patches=T("patches"), intrinsics=T("intrinsics"), target=T("target"), weight=T("weight"),
+              lmbda=T("lmbda"), ii=T("ii"), jj=T("jj"), kk=T("kk"), t0=t0, t1=t1,
+              nb_ix=torch.empty(E, dtype=torch.long), nb_jx=torch.empty(E, dtype=torch.long))
+    sess = pkg().hostapi.Session()
+    for forced in ("1", "0"):  # tiled and generic corr
+        os.environ["WVB200_CORR_TILED"] = forced
+        try:
+            ba["poses"].copy_(T("poses")); ba["patches"].copy_(T("patches"))
+            sess.update(g16, [f0, f1], co, ii1, jj1, [out0, out1], ba=ba, iterations=2)
+            c0 = run_corr(g16.float().numpy(), f0.float().numpy(), w["coords"], w["ii1"], w["jj1"], 3, torch.float16)
+            c1 = run_corr(g16.float().numpy(), f1.float().numpy(), (w["coords"] * 0.25).astype(np.float32), w["ii1"], w["jj1"], 3, torch.float16)
+        finally:
+            del os.environ["WVB200_CORR_TILED"]
+        assert np.array_equal(out0.float().numpy(), c0) and np.array_equal(out1.float().numpy(), c1)
+        poses, patches = run_ba(s, t0, t1, 2)
+        assert np.array_equal(ba["poses"].numpy(), poses) and np.array_equal(ba["patches"].numpy(), patches)
+        oi, oj = oracle.neighbors(s["kk"], s["jj"])
+        assert np.array_equal(ba["nb_ix"].numpy(), oi) and np.array_equal(ba["nb_jx"].numpy(), oj)
+    sess.close()

@@ -42,6 +42,6 @@ def capi():
 
 
 def __getattr__(name):
-    if name in ("altcorr", "fastba", "synthetic", "hostapi"):
+    if name in ("altcorr", "fastba", "synthetic", "hostapi", "dist"):
         return importlib.import_module(f"{__name__}.{name}")
     raise AttributeError(name)

@@ -176,3 +176,158 @@ done:
 }
 
 }  // extern "C"
+
+// ---- host-buffer session ---------------------------------------------------------------------------
+struct wv_session {
+  int dev = 0;
+  char* arena = nullptr;
+  size_t cap = 0;
+  cudaStream_t s_in = nullptr, s_cmp = nullptr, s_out = nullptr;
+  cudaEvent_t ev_small = nullptr, ev_ba = nullptr, ev_f[4] = {}, ev_c[4] = {};
+};
+
+namespace {
+__global__ void scale_coords_kernel(const float* __restrict__ in, float* __restrict__ out, float s, size_t n) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) out[i] = in[i] * s;
+}
+}  // namespace
+
+extern "C" {
+
+wv_session* wv_session_create(void) {
+  wv_session* s = new wv_session();
+  bool ok = cudaGetDevice(&s->dev) == cudaSuccess;
+  ok = ok && cudaStreamCreateWithFlags(&s->s_in, cudaStreamNonBlocking) == cudaSuccess;
+  ok = ok && cudaStreamCreateWithFlags(&s->s_cmp, cudaStreamNonBlocking) == cudaSuccess;
+  ok = ok && cudaStreamCreateWithFlags(&s->s_out, cudaStreamNonBlocking) == cudaSuccess;
+  ok = ok && cudaEventCreateWithFlags(&s->ev_small, cudaEventDisableTiming) == cudaSuccess;
+  ok = ok && cudaEventCreateWithFlags(&s->ev_ba, cudaEventDisableTiming) == cudaSuccess;
+  for (int l = 0; l < 4 && ok; l++)
+    ok = cudaEventCreateWithFlags(&s->ev_f[l], cudaEventDisableTiming) == cudaSuccess &&
+         cudaEventCreateWithFlags(&s->ev_c[l], cudaEventDisableTiming) == cudaSuccess;
+  if (!ok) { wv_session_destroy(s); return nullptr; }
+  return s;
+}
+
+void wv_session_destroy(wv_session* s) {
+  if (!s) return;
+  if (s->arena) cudaFree(s->arena);
+  if (s->s_in) cudaStreamDestroy(s->s_in);
+  if (s->s_cmp) cudaStreamDestroy(s->s_cmp);
+  if (s->s_out) cudaStreamDestroy(s->s_out);
+  if (s->ev_small) cudaEventDestroy(s->ev_small);
+  if (s->ev_ba) cudaEventDestroy(s->ev_ba);
+  for (int l = 0; l < 4; l++) { if (s->ev_f[l]) cudaEventDestroy(s->ev_f[l]); if (s->ev_c[l]) cudaEventDestroy(s->ev_c[l]); }
+  delete s;
+}
+
+int wv_session_update_host(wv_session* s, wv_update_args* a) {
+  if (!s || !a) return WV_EINVAL;
+  a->status = 0;
+  if ((a->dtype != WV_F16 && a->dtype != WV_F32) || a->nlevels < 0 || a->nlevels > 4 || a->B <= 0 || a->E < 0) return WV_EINVAL;
+  if (a->E == 0) return WV_OK;
+  const bool do_ba = a->iterations > 0;
+  const size_t es = a->dtype == WV_F16 ? 2 : 4, T = 2 * a->radius + 1, PP = (size_t)a->P * a->P;
+  auto al = [](size_t x) { return (x + 1023) & ~(size_t)1023; };
+  // ---- arena layout
+  size_t o = 0;
+  auto take = [&](size_t bytes) { size_t r = o; o += al(bytes); return r; };
+  const size_t b1 = (size_t)a->B * a->n1 * a->C * PP * es, bc = (size_t)a->B * a->E * 2 * PP * 4, bi = (size_t)a->E * 8;
+  const size_t bo = (size_t)a->B * a->E * T * T * PP * es;
+  const size_t o1 = take(b1), oc = take(bc), oii = take(bi), ojj = take(bi), ost = take(256);
+  size_t of[4], ocs[4], oo[4], ow[4], bw[4], b2[4];
+  for (int l = 0; l < a->nlevels; l++) {
+    b2[l] = (size_t)a->B * a->n2 * a->C * a->H2[l] * a->W2[l] * es;
+    bw[l] = wv_corr_workspace_bytes(a->dtype, a->B, a->E, a->C, a->P, a->P, a->n1, a->n2, a->H2[l], a->W2[l], a->radius);
+    of[l] = take(b2[l]); ocs[l] = take(bc); oo[l] = take(bo); ow[l] = take(bw[l] + 1024);
+  }
+  const size_t bp = (size_t)a->n_poses * 7 * 4, bq = (size_t)a->n_patches * 3 * PP * 4, bn = (size_t)a->n_poses * 4 * 4, bt = (size_t)a->E * 2 * 4;
+  const size_t bwb = do_ba ? std::max(wv_ba_workspace_bytes(a->E, a->n_patches, a->t1 - a->t0), wv_ba_workspace_bytes(a->E, (int64_t)1 << 22, 0)) : 0;
+  size_t op = 0, oq = 0, oe = 0, on = 0, otg = 0, owt = 0, ol = 0, oi = 0, oj = 0, ok = 0, owb = 0, onx = 0, onj = 0;
+  if (do_ba) {
+    op = take(bp); oq = take(bq); oe = a->patches_est ? take(bq) : 0; on = take(bn); otg = take(bt); owt = take(bt); ol = take(256);
+    oi = take(bi); oj = take(bi); ok = take(bi); owb = take(bwb + 1024); onx = take(bi); onj = take(bi);
+  }
+  int rc = WV_OK;
+  if (o > s->cap) {
+    if (s->arena) { cudaDeviceSynchronize(); cudaFree(s->arena); s->arena = nullptr; s->cap = 0; }
+    const size_t want = o + (o >> 3);
+    if (cudaMalloc((void**)&s->arena, want) != cudaSuccess) return ::wv::cuda_fail(cudaGetLastError());
+    s->cap = want;
+  }
+  char* d = s->arena;
+  int* dstatus = (int*)(d + ost);
+#define SS_TRY(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) { rc = ::wv::cuda_fail(_e); goto fail; } } while (0)
+  // ---- uploads: small pieces first, then the maps from the coarsest level to level 0
+  SS_TRY(cudaMemsetAsync(dstatus, 0, 4, s->s_in));
+  SS_TRY(cudaMemcpyAsync(d + oc, a->coords, bc, cudaMemcpyHostToDevice, s->s_in));
+  SS_TRY(cudaMemcpyAsync(d + oii, a->ii1, bi, cudaMemcpyHostToDevice, s->s_in));
+  SS_TRY(cudaMemcpyAsync(d + ojj, a->jj1, bi, cudaMemcpyHostToDevice, s->s_in));
+  if (do_ba) {
+    SS_TRY(cudaMemcpyAsync(d + op, a->poses, bp, cudaMemcpyHostToDevice, s->s_in));
+    SS_TRY(cudaMemcpyAsync(d + oq, a->patches, bq, cudaMemcpyHostToDevice, s->s_in));
+    if (a->patches_est) SS_TRY(cudaMemcpyAsync(d + oe, a->patches_est, bq, cudaMemcpyHostToDevice, s->s_in));
+    SS_TRY(cudaMemcpyAsync(d + on, a->intrinsics, bn, cudaMemcpyHostToDevice, s->s_in));
+    SS_TRY(cudaMemcpyAsync(d + otg, a->target, bt, cudaMemcpyHostToDevice, s->s_in));
+    SS_TRY(cudaMemcpyAsync(d + owt, a->weight, bt, cudaMemcpyHostToDevice, s->s_in));
+    SS_TRY(cudaMemcpyAsync(d + ol, a->lmbda, 4, cudaMemcpyHostToDevice, s->s_in));
+    SS_TRY(cudaMemcpyAsync(d + oi, a->ii, bi, cudaMemcpyHostToDevice, s->s_in));
+    SS_TRY(cudaMemcpyAsync(d + oj, a->jj, bi, cudaMemcpyHostToDevice, s->s_in));
+    SS_TRY(cudaMemcpyAsync(d + ok, a->kk, bi, cudaMemcpyHostToDevice, s->s_in));
+  }
+  if (a->nlevels > 0) SS_TRY(cudaMemcpyAsync(d + o1, a->fmap1, b1, cudaMemcpyHostToDevice, s->s_in));
+  SS_TRY(cudaEventRecord(s->ev_small, s->s_in));
+  for (int l = a->nlevels - 1; l >= 0; l--) {
+    SS_TRY(cudaMemcpyAsync(d + of[l], a->fmap2[l], b2[l], cudaMemcpyHostToDevice, s->s_in));
+    SS_TRY(cudaEventRecord(s->ev_f[l], s->s_in));
+  }
+  // ---- compute: BA first (its inputs are there first), then the levels as their maps arrive
+  SS_TRY(cudaStreamWaitEvent(s->s_cmp, s->ev_small, 0));
+  if (do_ba) {
+    if (a->nb_ix && a->nb_jx) {
+      rc = wv_neighbors((const int64_t*)(d + ok), (const int64_t*)(d + oj), a->E, (int64_t)1 << 22, (int64_t*)(d + onx), (int64_t*)(d + onj),
+                        d + owb, bwb, dstatus, (wv_stream_t)s->s_cmp);
+      if (rc != WV_OK) goto fail;
+    }
+    rc = wv_ba_forward((float*)(d + op), (float*)(d + oq), (const float*)(d + on), (const float*)(d + otg), (const float*)(d + owt),
+                       (const float*)(d + ol), (const int64_t*)(d + oi), (const int64_t*)(d + oj), (const int64_t*)(d + ok), a->E,
+                       a->n_poses, a->n_patches, a->P, a->t0, a->t1, a->iterations, a->patches_est ? (const float*)(d + oe) : nullptr,
+                       a->mu, d + owb, bwb, dstatus, (wv_stream_t)s->s_cmp);
+    if (rc != WV_OK) goto fail;
+    SS_TRY(cudaEventRecord(s->ev_ba, s->s_cmp));
+    SS_TRY(cudaStreamWaitEvent(s->s_out, s->ev_ba, 0));
+    SS_TRY(cudaMemcpyAsync(a->poses, d + op, bp, cudaMemcpyDeviceToHost, s->s_out));
+    SS_TRY(cudaMemcpyAsync(a->patches, d + oq, bq, cudaMemcpyDeviceToHost, s->s_out));
+    if (a->nb_ix && a->nb_jx) {
+      SS_TRY(cudaMemcpyAsync(a->nb_ix, d + onx, bi, cudaMemcpyDeviceToHost, s->s_out));
+      SS_TRY(cudaMemcpyAsync(a->nb_jx, d + onj, bi, cudaMemcpyDeviceToHost, s->s_out));
+    }
+  }
+  for (int l = a->nlevels - 1; l >= 0; l--) {
+    SS_TRY(cudaStreamWaitEvent(s->s_cmp, s->ev_f[l], 0));
+    const float* cl = (const float*)(d + oc);
+    if (a->coord_scale[l] != 1.0f) {
+      const size_t n = bc / 4;
+      scale_coords_kernel<<<(unsigned)std::min<size_t>((n + 255) / 256, 1184), 256, 0, s->s_cmp>>>((const float*)(d + oc), (float*)(d + ocs[l]), a->coord_scale[l], n);
+      cl = (const float*)(d + ocs[l]);
+    }
+    char* wsp = (char*)(((uintptr_t)(d + ow[l]) + 1023) & ~(uintptr_t)1023);
+    rc = wv_corr_forward(d + o1, d + of[l], cl, (const int64_t*)(d + oii), (const int64_t*)(d + ojj), d + oo[l], a->dtype, a->B, a->E, a->C,
+                         a->P, a->P, a->n1, a->n2, a->H2[l], a->W2[l], a->radius, bw[l] ? wsp : nullptr, bw[l], dstatus, (wv_stream_t)s->s_cmp);
+    if (rc != WV_OK) goto fail;
+    SS_TRY(cudaEventRecord(s->ev_c[l], s->s_cmp));
+    SS_TRY(cudaStreamWaitEvent(s->s_out, s->ev_c[l], 0));
+    SS_TRY(cudaMemcpyAsync(a->corr_out[l], d + oo[l], bo, cudaMemcpyDeviceToHost, s->s_out));
+  }
+  SS_TRY(cudaStreamSynchronize(s->s_cmp));
+  SS_TRY(cudaMemcpyAsync(&a->status, dstatus, 4, cudaMemcpyDeviceToHost, s->s_out));
+  SS_TRY(cudaStreamSynchronize(s->s_out));
+  if (a->status & WV_STATUS_BAD_INDEX) return WV_EINVAL;
+  return WV_OK;
+fail:
+  cudaStreamSynchronize(s->s_in); cudaStreamSynchronize(s->s_cmp); cudaStreamSynchronize(s->s_out);
+  return rc;
+#undef SS_TRY
+}
+
+}  // extern "C"
