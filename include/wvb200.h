@@ -111,6 +111,16 @@ int wv_ba_forward(float* poses, float* patches, const float* intrinsics, const f
                   int iterations, const float* patches_est, float mu, void* workspace,
                   size_t workspace_bytes, int* status, wv_stream_t stream);
 
+/* wv_ba_forward when `workspace` already holds the edge plan that wv_neighbors(kk, jj, E, n_groups = plan_groups, ...)
+ * built for the SAME kk / jj (the tracker calls neighbors and BA on one edge list per update(), dpvo/net.py:81 then
+ * dpvo/dpvo.py:733): skips the second plan build.  workspace_bytes >= wv_ba_workspace_bytes(E, plan_groups, t1 - t0);
+ * kk values must be < plan_groups.  ii / jj are range-checked by the BA kernel itself. */
+int wv_ba_forward_planned(float* poses, float* patches, const float* intrinsics, const float* target,
+                          const float* weight, const float* lmbda, const int64_t* ii, const int64_t* jj,
+                          const int64_t* kk, int64_t E, int64_t n_poses, int64_t n_patches, int P, int t0,
+                          int t1, int iterations, const float* patches_est, float mu, void* workspace,
+                          size_t workspace_bytes, int64_t plan_groups, int* status, wv_stream_t stream);
+
 /* cuda_ba.reproject (ba_cuda.cu:368-418, 543-575): coords [E][2][P][P], no depth clamp. */
 int wv_ba_reproject(const float* poses, const float* patches, const float* intrinsics, const int64_t* ii,
                     const int64_t* jj, const int64_t* kk, int64_t E, int64_t n_poses, int64_t n_patches,

@@ -394,3 +394,36 @@ def test_host_session_update_matches_device_path(syn):
         oi, oj = oracle.neighbors(s["kk"], s["jj"])
         assert np.array_equal(ba["nb_ix"].numpy(), oi) and np.array_equal(ba["nb_jx"].numpy(), oj)
     sess.close()
+
+
+def test_ba_reuses_the_plan_of_neighbors(syn):
+    """neighbors(kk, jj) then BA(..., ii, jj, kk) on the same tensors (one tracker update()): BA runs on the cached plan,
+    with the same bits as a BA that builds its own; an in-place edit of kk in between invalidates the cache"""
+    _, cb = pkg().native_modules()
+    s = syn.make_ba_scene(seed=2, n=40, M=32, edges="tracker")
+    t0, t1 = int(s["t1"]) - 10, int(s["t1"])
+    D = {k: dev(s[k]) for k in ("intrinsics", "target", "weight", "lmbda", "ii", "jj", "kk")}
+
+    def run(cache, edit=False):
+        poses, patches = dev(s["poses"].copy()), dev(s["patches"].copy())
+        if not cache:
+            os.environ["WVB200_NO_PLAN_CACHE"] = "1"
+        try:
+            ix, jx = cb.neighbors(D["kk"], D["jj"])
+            if edit:
+                D["kk"].add_(0)  # bumps the version counter: the cached plan must not be trusted
+            cb.forward(poses, patches, D["intrinsics"], D["target"], D["weight"], D["lmbda"], D["ii"], D["jj"], D["kk"], t0, t1, 2)
+        finally:
+            os.environ.pop("WVB200_NO_PLAN_CACHE", None)
+        torch.cuda.synchronize()
+        return poses.cpu().numpy(), patches.cpu().numpy(), ix.cpu().numpy()
+
+    a, b, c = run(True), run(False), run(True, edit=True)
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2])
+    assert np.array_equal(a[0], c[0]) and np.array_equal(a[1], c[1])
+    # an out-of-range frame index is caught by the BA kernel itself on the cached-plan path
+    bad = D["jj"].clone(); bad[5] = 10 ** 6
+    cb.neighbors(D["kk"], bad)
+    with pytest.raises(IndexError):
+        cb.forward(dev(s["poses"].copy()), dev(s["patches"].copy()), D["intrinsics"], D["target"], D["weight"], D["lmbda"], D["ii"], bad,
+                   D["kk"], t0, t1, 2)

@@ -37,7 +37,7 @@ int corr_forward_tiled(const void*, const void*, const float*, const int64_t*, c
 size_t ba_workspace_bytes(int64_t E, int64_t n_patches, int N);
 int ba_forward_window(float*, float*, const float*, const float*, const float*, const float*, const int64_t*,
                       const int64_t*, const int64_t*, int64_t, int64_t, int64_t, int, int, int, int, const float*, float,
-                      void*, size_t, int*, cudaStream_t);
+                      void*, size_t, int*, cudaStream_t, int64_t);
 int ba_reproject(const float*, const float*, const float*, const int64_t*, const int64_t*, const int64_t*, int64_t,
                  int64_t, int64_t, int, float*, int*, cudaStream_t);
 int ba_neighbors(const int64_t*, const int64_t*, int64_t, int64_t, int64_t*, int64_t*, void*, size_t, int*, cudaStream_t);
@@ -139,7 +139,20 @@ int wv_ba_forward(float* poses, float* patches, const float* intrinsics, const f
   if (E == 0 || iterations <= 0) return WV_OK;
   if (!poses || !patches || !intrinsics || !target || !weight || !lmbda || !ii || !jj || !kk || !workspace) return WV_EINVAL;
   return ba_forward_window(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk, E, n_poses, n_patches, P, t0, t1,
-                           iterations, patches_est, mu, workspace, workspace_bytes, status, as_stream(stream));
+                           iterations, patches_est, mu, workspace, workspace_bytes, status, as_stream(stream), 0);
+}
+
+int wv_ba_forward_planned(float* poses, float* patches, const float* intrinsics, const float* target, const float* weight,
+                          const float* lmbda, const int64_t* ii, const int64_t* jj, const int64_t* kk, int64_t E,
+                          int64_t n_poses, int64_t n_patches, int P, int t0, int t1, int iterations, const float* patches_est,
+                          float mu, void* workspace, size_t workspace_bytes, int64_t plan_groups, int* status,
+                          wv_stream_t stream) {
+  if (E < 0 || n_poses <= 0 || n_patches <= 0 || P <= 0 || t0 < 0 || t1 < t0 || t1 > n_poses || plan_groups <= 0) return WV_EINVAL;
+  if (E >= (int64_t)1 << 31 || n_patches > plan_groups) return WV_EUNSUPPORTED;
+  if (E == 0 || iterations <= 0) return WV_OK;
+  if (!poses || !patches || !intrinsics || !target || !weight || !lmbda || !ii || !jj || !kk || !workspace) return WV_EINVAL;
+  return ba_forward_window(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk, E, n_poses, n_patches, P, t0, t1,
+                           iterations, patches_est, mu, workspace, workspace_bytes, status, as_stream(stream), plan_groups);
 }
 
 int wv_ba_reproject(const float* poses, const float* patches, const float* intrinsics, const int64_t* ii, const int64_t* jj,

@@ -18,6 +18,8 @@
 // (the reference's atomics are not).  fp32 throughout, like the reference.
 #include <cooperative_groups.h>
 
+#include <algorithm>
+
 #include "ba_plan.cuh"
 #include "se3.cuh"
 
@@ -34,6 +36,7 @@ struct BAArgs {
   const int64_t* ii; const int64_t* jj;
   const float* patches_est; float mu;
   int P, t0, N, iterations;
+  int n_poses;
   Plan p;
   float* partial;  // [grid][nS]
   float* Sfull;    // [nS]
@@ -156,9 +159,14 @@ __global__ void __launch_bounds__(kBaThreads, 1) ba_window_kernel(BAArgs a) {
       __syncwarp();
       float Csum = 0.f, usum = 0.f;
       for (int base = 0; base < n; base += 32) {
-        const bool act = base + lane < n;
+        bool act = base + lane < n;
         const int e = act ? a.p.eperm[off + base + lane] : 0;
-        const int ix = act ? (int)a.ii[e] : -1, jx = act ? (int)a.jj[e] : -2 - lane;
+        int ix = -1, jx = -2 - lane;
+        if (act) {  // a plan built by neighbors() has not looked at ii / jj: range-check them here
+          const int64_t iv = a.ii[e], jv = a.jj[e];
+          if (iv < 0 || iv >= a.n_poses || jv < 0 || jv >= a.n_poses) { set_status(a.status, WV_STATUS_BAD_INDEX); act = false; }
+          else { ix = (int)iv; jx = (int)jv; }
+        }
         const int fi = ix - a.t0, fj = jx - a.t0;
         const bool free_i = act && fi >= 0 && fi < N, free_j = act && fj >= 0 && fj < N;
         EdgeTerms T;
@@ -274,55 +282,63 @@ __global__ void __launch_bounds__(kBaThreads, 1) ba_window_kernel(BAArgs a) {
       }
       grid.sync();
       for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < nS; t += gridDim.x * blockDim.x) {
-        float s = 0.f;
-        for (int c = 0; c < (int)gridDim.x; c++) s += a.partial[(size_t)c * nS + t];
-        a.Sfull[t] = s;
+        // fixed order, four independent chains (loads in flight together), combined in a fixed order
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+        int c = 0;
+        for (; c + 4 <= (int)gridDim.x; c += 4) {
+          s0 += a.partial[(size_t)c * nS + t]; s1 += a.partial[(size_t)(c + 1) * nS + t];
+          s2 += a.partial[(size_t)(c + 2) * nS + t]; s3 += a.partial[(size_t)(c + 3) * nS + t];
+        }
+        for (; c < (int)gridDim.x; c++) s0 += a.partial[(size_t)c * nS + t];
+        a.Sfull[t] = (s0 + s1) + (s2 + s3);
       }
       grid.sync();
       // ---------------------------------------------------------------- phase C: damped Cholesky (every CTA)
+      // Right-looking LL^T on the (n6+1) x n6 trapezoid [S ; y^T] in shared memory: carrying the right-hand side as an
+      // extra row makes the forward substitution L z = y fall out of the factorisation.  Step j reads column j (left
+      // UNSCALED for the whole step, so one barrier per step suffices), updates the columns to its right, and files the
+      // scaled column L_ij in the unused upper triangle A[j][i] for the back substitution.  Four threads per row.
       const int ld = n6 + 1;
-      float* A = sm;            // [n6][ld]
-      float* dg = A + n6 * ld;  // [n6]
-      float* bx = dg + n6;      // [n6] rhs -> solution
+      float* A = sm;                   // [n6 + 1][ld]
+      float* dg = A + (n6 + 1) * ld;   // [n6]  diagonal of L
+      float* bx = dg + n6;             // [n6]  z, then the solution
       for (int t = threadIdx.x; t < n6 * n6; t += blockDim.x) {
-        const int rr = t / n6, cc = t % n6;
-        float s = a.Sfull[rr >= cc ? tri(rr, cc) : tri(cc, rr)];
-        if (rr == cc) s = s + (s * 1e-4f + 1.0f);  // S += I * (1e-4 * S + 1.0), ba_cuda.cu:517-518
-        A[rr * ld + cc] = s;
+        const int rr = t / n6, cc = t - rr * n6;
+        if (cc <= rr) {
+          float s = a.Sfull[tri(rr, cc)];
+          if (rr == cc) s = s + (s * 1e-4f + 1.0f);  // S += I * (1e-4 * S + 1.0), ba_cuda.cu:517-518
+          A[rr * ld + cc] = s;
+        }
       }
-      for (int t = threadIdx.x; t < n6; t += blockDim.x) bx[t] = a.Sfull[nT + t];
+      for (int t = threadIdx.x; t < n6; t += blockDim.x) A[n6 * ld + t] = a.Sfull[nT + t];
+      const int q4 = threadIdx.x & 3, r4 = threadIdx.x >> 2;
       for (int j = 0; j < n6; j++) {
         __syncthreads();
         const float d = A[j * ld + j];
         if (!(d > 0.f)) { failed = true; break; }  // same value in every thread of every CTA
-        const float dj = sqrtf(d);
-        if (threadIdx.x == 0) dg[j] = dj;
-        for (int i = j + 1 + threadIdx.x; i < n6; i += blockDim.x) A[i * ld + j] = A[i * ld + j] / dj;
-        __syncthreads();
-        const int m = n6 - j - 1;
-        for (int t = threadIdx.x; t < m * m; t += blockDim.x) {
-          const int i = j + 1 + t / m, k = j + 1 + t % m;
-          if (k <= i) A[i * ld + k] -= A[i * ld + j] * A[k * ld + j];
+        const float dj = sqrtf(d), rd = 1.f / d;
+        for (int i = j + 1 + r4; i <= n6; i += kBaThreads / 4) {
+          const float aij = A[i * ld + j], f = aij * rd;
+          const int kend = i < n6 ? i : n6 - 1;
+          for (int k = j + 1 + q4; k <= kend; k += 4) A[i * ld + k] = fmaf(-f, A[k * ld + j], A[i * ld + k]);
+          if (q4 == 0) {
+            if (i < n6) A[j * ld + i] = aij / dj;  // L_ij, filed in the upper triangle
+            else bx[j] = aij / dj;                 // z_j
+          }
         }
+        if (threadIdx.x == 0) dg[j] = dj;
       }
       __syncthreads();
       if (failed) {
         if (blockIdx.x == 0 && threadIdx.x == 0) set_status(a.status, WV_STATUS_NOT_SPD);
         break;
       }
-      if (warp == 0) {  // L z = y, L^T x = z (column-oriented, one warp)
-        for (int i = 0; i < n6; i++) {
-          const float z = bx[i] / dg[i];
-          __syncwarp();
-          if (lane == 0) bx[i] = z;
-          for (int k = i + 1 + lane; k < n6; k += 32) bx[k] -= A[k * ld + i] * z;
-          __syncwarp();
-        }
+      if (warp == 0) {  // L^T x = z, column-oriented, one warp; L_ik (k < i) is at A[k][i]
         for (int i = n6 - 1; i >= 0; i--) {
           const float x = bx[i] / dg[i];
           __syncwarp();
           if (lane == 0) bx[i] = x;
-          for (int k = lane; k < i; k += 32) bx[k] -= A[i * ld + k] * x;
+          for (int k = lane; k < i; k += 32) bx[k] = fmaf(-A[k * ld + i], x, bx[k]);
           __syncwarp();
         }
       }
@@ -422,16 +438,19 @@ size_t ba_workspace_bytes(int64_t E, int64_t n_patches, int N) {
 int ba_forward_window(float* poses, float* patches, const float* intr, const float* target, const float* weight,
                       const float* lmbda, const int64_t* ii, const int64_t* jj, const int64_t* kk, int64_t E,
                       int64_t n_poses, int64_t n_patches, int P, int t0, int t1, int iterations,
-                      const float* patches_est, float mu, void* ws, size_t ws_bytes, int* status, cudaStream_t st) {
+                      const float* patches_est, float mu, void* ws, size_t ws_bytes, int* status, cudaStream_t st,
+                      int64_t plan_groups) {
+  // plan_groups > 0: `ws` already holds the plan wv_neighbors built for these (kk, jj) with n_groups == plan_groups
   const int N = t1 - t0;
   if (N > kMaxFree) return WV_EUNSUPPORTED;
   if (E == 0 || iterations <= 0) return WV_OK;
-  if (ws_bytes < ba_workspace_bytes(E, n_patches, N)) return WV_EWORKSPACE;
+  const int64_t groups = plan_groups > 0 ? plan_groups : n_patches;
+  if (ws_bytes < ba_workspace_bytes(E, groups, N)) return WV_EWORKSPACE;
   const int G = plan_grid();
   const int n6 = 6 * N, nS = n6 * (n6 + 1) / 2 + n6;
   BAArgs a{};
   char* b = (char*)ws;
-  size_t o = plan_carve(&a.p, ws, E, n_patches, G);
+  size_t o = plan_carve(&a.p, ws, E, groups, G);
   auto take = [&](size_t bytes) { void* r = b + o; o += al256(bytes); return r; };
   a.partial = (float*)take(sizeof(float) * (size_t)(G * nS + 1));
   a.Sfull = (float*)take(sizeof(float) * (size_t)(nS + 1));
@@ -440,10 +459,12 @@ int ba_forward_window(float* poses, float* patches, const float* intr, const flo
   a.uk = (float*)take(sizeof(float) * (size_t)(a.p.Mp_cap + 1));
   a.poses = poses; a.patches = patches; a.intr = intr; a.target = target; a.weight = weight; a.lmbda = lmbda;
   a.ii = ii; a.jj = jj; a.patches_est = patches_est; a.mu = mu; a.P = P; a.t0 = t0; a.N = N; a.iterations = iterations;
-  a.status = status;
-  int rc = plan_build(a.p, kk, jj, ii, n_poses, nullptr, nullptr, status, st);
-  if (rc != WV_OK) return rc;
-  const size_t smem = sizeof(float) * (size_t)(kBaWarps * nS + kBaWarps * n6 + 64);
+  a.status = status; a.n_poses = (int)n_poses;
+  if (plan_groups <= 0) {
+    int rc = plan_build(a.p, kk, jj, ii, n_poses, nullptr, nullptr, status, st);
+    if (rc != WV_OK) return rc;
+  }
+  const size_t smem = sizeof(float) * std::max((size_t)(kBaWarps * nS + kBaWarps * n6 + 64), (size_t)((n6 + 1) * (n6 + 1) + 2 * n6 + 64));
   if (smem > 48 * 1024)
     WV_CUDA_TRY(cudaFuncSetAttribute(ba_window_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   void* args[] = {&a};

@@ -20,6 +20,19 @@ torch::Tensor workspace(const torch::Device& dev, size_t bytes) {
   return it->second;
 }
 
+// The tracker calls neighbors(kk, jj) and then BA(..., ii, jj, kk, ...) on the same edge tensors inside one update()
+// (dpvo/net.py:81, dpvo/dpvo.py:733).  neighbors leaves its edge plan in the per-device workspace; if BA then sees the same
+// storage (pointer, length, version counter), workspace and stream, it reuses the plan instead of rebuilding it.
+constexpr int64_t kPlanGroups = (int64_t)1 << 22;  // ids (patch indices) must lie below 4M for the shared plan
+struct PlanNote {
+  const void* kk = nullptr; const void* jj = nullptr; int64_t E = -1; uint32_t vkk = 0, vjj = 0;
+  const void* ws = nullptr; void* stream = nullptr;
+};
+PlanNote& plan_note(int dev) {
+  static std::map<int, PlanNote> notes;
+  return notes[dev];
+}
+
 void check_f32c(const torch::Tensor& t, const char* name) {
   check_cuda(t, name);
   TORCH_CHECK(t.scalar_type() == torch::kFloat, "cuda_ba: ", name, " must be float32");
@@ -56,13 +69,27 @@ std::vector<torch::Tensor> ba_forward(torch::Tensor poses, torch::Tensor patches
     est = estc.data_ptr<float>();
   }
   if (E == 0 || iterations <= 0) return {};
-  const size_t wsb = wv_ba_workspace_bytes(E, n_patches, t1 - t0);
-  torch::Tensor ws = workspace(poses.device(), wsb);
-  check_rc(wv_ba_forward(poses.data_ptr<float>(), patches.data_ptr<float>(), intrinsics.data_ptr<float>(), tg.data_ptr<float>(),
-                         wt.data_ptr<float>(), lm.data_ptr<float>(), iic.data_ptr<int64_t>(), jjc.data_ptr<int64_t>(),
-                         kkc.data_ptr<int64_t>(), E, n_poses, n_patches, P, t0, t1, iterations, est, (float)mu, ws.data_ptr(),
-                         (size_t)ws.numel(), status_word(poses.device()).data_ptr<int>(), current_stream()),
-           "cuda_ba.forward");
+  PlanNote& note = plan_note(poses.device().index());
+  const size_t wsb_shared = wv_ba_workspace_bytes(E, kPlanGroups, t1 - t0);
+  torch::Tensor ws = workspace(poses.device(), std::max(wv_ba_workspace_bytes(E, n_patches, t1 - t0), note.E == E ? wsb_shared : (size_t)0));
+  const bool planned = !env_flag("WVB200_NO_PLAN_CACHE") && note.E == E && note.kk == kkc.data_ptr() && note.jj == jjc.data_ptr() &&
+                       note.vkk == kkc._version() && note.vjj == jjc._version() && note.ws == ws.data_ptr() &&
+                       note.stream == (void*)current_stream() && n_patches <= kPlanGroups && (size_t)ws.numel() >= wsb_shared;
+  if (planned) {
+    check_rc(wv_ba_forward_planned(poses.data_ptr<float>(), patches.data_ptr<float>(), intrinsics.data_ptr<float>(),
+                                   tg.data_ptr<float>(), wt.data_ptr<float>(), lm.data_ptr<float>(), iic.data_ptr<int64_t>(),
+                                   jjc.data_ptr<int64_t>(), kkc.data_ptr<int64_t>(), E, n_poses, n_patches, P, t0, t1, iterations, est,
+                                   (float)mu, ws.data_ptr(), (size_t)ws.numel(), kPlanGroups, status_word(poses.device()).data_ptr<int>(),
+                                   current_stream()),
+             "cuda_ba.forward");
+  } else {
+    note = PlanNote();  // this call rebuilds the plan with its own layout
+    check_rc(wv_ba_forward(poses.data_ptr<float>(), patches.data_ptr<float>(), intrinsics.data_ptr<float>(), tg.data_ptr<float>(),
+                           wt.data_ptr<float>(), lm.data_ptr<float>(), iic.data_ptr<int64_t>(), jjc.data_ptr<int64_t>(),
+                           kkc.data_ptr<int64_t>(), E, n_poses, n_patches, P, t0, t1, iterations, est, (float)mu, ws.data_ptr(),
+                           (size_t)ws.numel(), status_word(poses.device()).data_ptr<int>(), current_stream()),
+             "cuda_ba.forward");
+  }
   // The reference raises from torch::linalg::cholesky inside this call (dpvo/dpvo.py:733 lets it propagate);
   // reading the status word costs one host sync.  WVB200_ASYNC=1 skips it (capture-safe, errors stay sticky).
   if (!env_flag("WVB200_ASYNC")) raise_on_status(poses.device(), "cuda_ba.forward");
@@ -76,13 +103,17 @@ std::vector<torch::Tensor> neighbors(torch::Tensor ii, torch::Tensor jj) {
   const int64_t E = iic.numel();
   torch::Tensor ix = torch::empty({E}, iic.options()), jx = torch::empty({E}, iic.options());
   if (E == 0) return {ix, jx};
-  const int64_t n_groups = (int64_t)1 << 22;  // ids (patch indices) must lie in a window of 4M values
-  const size_t wsb = wv_ba_workspace_bytes(E, n_groups, 0);
+  const int64_t n_groups = kPlanGroups;
+  const size_t wsb = wv_ba_workspace_bytes(E, n_groups, 16);  // room for a following BA on the same plan (<= 16 free poses)
   torch::Tensor ws = workspace(iic.device(), wsb);
+  PlanNote& note = plan_note(iic.device().index());
+  note = PlanNote();
   check_rc(wv_neighbors(iic.data_ptr<int64_t>(), jjc.data_ptr<int64_t>(), E, n_groups, ix.data_ptr<int64_t>(),
                         jx.data_ptr<int64_t>(), ws.data_ptr(), (size_t)ws.numel(), status_word(iic.device()).data_ptr<int>(),
                         current_stream()),
            "cuda_ba.neighbors");
+  note.kk = iic.data_ptr(); note.jj = jjc.data_ptr(); note.E = E; note.vkk = iic._version(); note.vjj = jjc._version();
+  note.ws = ws.data_ptr(); note.stream = (void*)current_stream();
   if (env_flag("WVB200_CHECK_INDICES")) raise_on_status(iic.device(), "cuda_ba.neighbors");
   return {ix, jx};
 }

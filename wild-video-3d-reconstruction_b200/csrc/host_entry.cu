@@ -242,7 +242,7 @@ int wv_session_update_host(wv_session* s, wv_update_args* a) {
     of[l] = take(b2[l]); ocs[l] = take(bc); oo[l] = take(bo); ow[l] = take(bw[l] + 1024);
   }
   const size_t bp = (size_t)a->n_poses * 7 * 4, bq = (size_t)a->n_patches * 3 * PP * 4, bn = (size_t)a->n_poses * 4 * 4, bt = (size_t)a->E * 2 * 4;
-  const size_t bwb = do_ba ? std::max(wv_ba_workspace_bytes(a->E, a->n_patches, a->t1 - a->t0), wv_ba_workspace_bytes(a->E, (int64_t)1 << 22, 0)) : 0;
+  const size_t bwb = do_ba ? std::max(wv_ba_workspace_bytes(a->E, a->n_patches, a->t1 - a->t0), wv_ba_workspace_bytes(a->E, (int64_t)1 << 22, a->t1 - a->t0)) : 0;
   size_t op = 0, oq = 0, oe = 0, on = 0, otg = 0, owt = 0, ol = 0, oi = 0, oj = 0, ok = 0, owb = 0, onx = 0, onj = 0;
   if (do_ba) {
     op = take(bp); oq = take(bq); oe = a->patches_est ? take(bq) : 0; on = take(bn); otg = take(bt); owt = take(bt); ol = take(256);
@@ -289,10 +289,17 @@ int wv_session_update_host(wv_session* s, wv_update_args* a) {
                         d + owb, bwb, dstatus, (wv_stream_t)s->s_cmp);
       if (rc != WV_OK) goto fail;
     }
-    rc = wv_ba_forward((float*)(d + op), (float*)(d + oq), (const float*)(d + on), (const float*)(d + otg), (const float*)(d + owt),
-                       (const float*)(d + ol), (const int64_t*)(d + oi), (const int64_t*)(d + oj), (const int64_t*)(d + ok), a->E,
-                       a->n_poses, a->n_patches, a->P, a->t0, a->t1, a->iterations, a->patches_est ? (const float*)(d + oe) : nullptr,
-                       a->mu, d + owb, bwb, dstatus, (wv_stream_t)s->s_cmp);
+    if (a->nb_ix && a->nb_jx && a->n_patches <= ((int64_t)1 << 22))  // one edge plan serves both calls
+      rc = wv_ba_forward_planned((float*)(d + op), (float*)(d + oq), (const float*)(d + on), (const float*)(d + otg),
+                                 (const float*)(d + owt), (const float*)(d + ol), (const int64_t*)(d + oi), (const int64_t*)(d + oj),
+                                 (const int64_t*)(d + ok), a->E, a->n_poses, a->n_patches, a->P, a->t0, a->t1, a->iterations,
+                                 a->patches_est ? (const float*)(d + oe) : nullptr, a->mu, d + owb, bwb, (int64_t)1 << 22, dstatus,
+                                 (wv_stream_t)s->s_cmp);
+    else
+      rc = wv_ba_forward((float*)(d + op), (float*)(d + oq), (const float*)(d + on), (const float*)(d + otg), (const float*)(d + owt),
+                         (const float*)(d + ol), (const int64_t*)(d + oi), (const int64_t*)(d + oj), (const int64_t*)(d + ok), a->E,
+                         a->n_poses, a->n_patches, a->P, a->t0, a->t1, a->iterations, a->patches_est ? (const float*)(d + oe) : nullptr,
+                         a->mu, d + owb, bwb, dstatus, (wv_stream_t)s->s_cmp);
     if (rc != WV_OK) goto fail;
     SS_TRY(cudaEventRecord(s->ev_ba, s->s_cmp));
     SS_TRY(cudaStreamWaitEvent(s->s_out, s->ev_ba, 0));
