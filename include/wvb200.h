@@ -42,7 +42,8 @@ enum {
 /* bits of the device status word */
 enum {
   WV_STATUS_BAD_INDEX = 1, /* an ii/jj/kk entry was outside its tensor; that edge was skipped */
-  WV_STATUS_NOT_SPD = 2    /* Cholesky met a non-positive pivot (reference: torch::linalg::cholesky throws, ba_cuda.cu:521) */
+  WV_STATUS_NOT_SPD = 2,   /* Cholesky met a non-positive pivot (reference: torch::linalg::cholesky throws, ba_cuda.cu:521) */
+  WV_STATUS_TOO_DENSE = 4  /* global BA: one patch had more than 128 free-pose observations; the excess was dropped */
 };
 
 const char* wv_strerror(int code);
@@ -120,6 +121,37 @@ int wv_ba_forward_planned(float* poses, float* patches, const float* intrinsics,
                           const int64_t* kk, int64_t E, int64_t n_poses, int64_t n_patches, int P, int t0,
                           int t1, int iterations, const float* patches_est, float mu, void* workspace,
                           size_t workspace_bytes, int64_t plan_groups, int* status, wv_stream_t stream);
+
+/* ---- BA with more than 16 free poses (the loop-closure / end-of-run global BA, dpvo/dpvo.py:436-505) ----------
+ * The same cuda_ba() (dpvo/fastba/ba_cuda.cu:422-540), split at its two natural seams so that (a) the dense
+ * 6N x 6N solve can be done by the caller's solver (the torch binding uses the reference's own
+ * torch::linalg::cholesky + cholesky_solve, ba_cuda.cu:521-523) and (b) the patches can be sharded over GPUs:
+ * rank `shard` of `nshards` accumulates only its contiguous run of the sorted unique patch ids, the caller sums
+ * [S | y] over ranks (one allreduce per iteration), solves, and sums dZ over ranks.  One iteration is
+ *     wv_ba_global_build -> (allreduce S, y) -> wv_ba_global_damp -> dX = S^-1 y (caller) ->
+ *     wv_ba_global_dz -> (allreduce dZ) -> wv_ba_global_retract.
+ * The dense 6N x Mp matrix E of the reference (:443-444) is never formed.
+ *   S [6N][6N] row-major: only the LOWER triangle is written (the upper is left zero); y [6N]; N = t1 - t0.
+ *   dX [N][6]; dZ [min(E, n_patches)] indexed by the rank of the patch id among the sorted unique kk.
+ *   build_plan != 0 rebuilds the edge plan in `workspace` (needed once per edge list, not per iteration).
+ *   workspace_bytes >= wv_ba_global_workspace_bytes(E, n_patches); the same workspace goes to all four calls. */
+size_t wv_ba_global_workspace_bytes(int64_t E, int64_t n_patches);
+int wv_ba_global_build(float* poses, float* patches, const float* intrinsics, const float* target,
+                       const float* weight, const float* lmbda, const int64_t* ii, const int64_t* jj,
+                       const int64_t* kk, int64_t E, int64_t n_poses, int64_t n_patches, int P, int t0, int t1,
+                       const float* patches_est, float mu, int shard, int nshards, int build_plan, float* S,
+                       float* y, void* workspace, size_t workspace_bytes, int* status, wv_stream_t stream);
+/* S_dd <- S_dd * (1 + 1e-4) + 1 (ba_cuda.cu:517-518); n6 = 6 * (t1 - t0) */
+int wv_ba_global_damp(float* S, int n6, wv_stream_t stream);
+int wv_ba_global_dz(float* poses, float* patches, const float* intrinsics, const float* target,
+                    const float* weight, const float* lmbda, const int64_t* ii, const int64_t* jj, int64_t E,
+                    int64_t n_poses, int64_t n_patches, int P, int t0, int t1, const float* patches_est,
+                    float mu, int shard, int nshards, const float* dX, float* dZ, void* workspace,
+                    size_t workspace_bytes, int* status, wv_stream_t stream);
+/* pose_retr_kernel + patch_retr_kernel (ba_cuda.cu:160-211) for poses t0..t1-1 and every patch of the plan */
+int wv_ba_global_retract(float* poses, float* patches, int64_t E, int64_t n_poses, int64_t n_patches, int P,
+                         int t0, int t1, const float* dX, const float* dZ, void* workspace,
+                         size_t workspace_bytes, wv_stream_t stream);
 
 /* cuda_ba.reproject (ba_cuda.cu:368-418, 543-575): coords [E][2][P][P], no depth clamp. */
 int wv_ba_reproject(const float* poses, const float* patches, const float* intrinsics, const int64_t* ii,

@@ -36,8 +36,14 @@ def run_ba(s, t0, t1, iters, patches_est=None, mu=2.0):
 
 
 def quat_angle(qa, qb):
-    d = np.abs((qa * qb).sum(-1)) / (np.linalg.norm(qa, axis=-1) * np.linalg.norm(qb, axis=-1))
-    return 2 * np.arccos(np.clip(d, 0, 1))
+    """rotation angle between unit quaternions (x, y, z, w), in fp64 via the vector part of conj(a) * b (an arccos of the dot
+    product quantises to 0 or 6.9e-4 rad in fp32)"""
+    a = np.asarray(qa, np.float64); b = np.asarray(qb, np.float64)
+    a = a / np.linalg.norm(a, axis=-1, keepdims=True); b = b / np.linalg.norm(b, axis=-1, keepdims=True)
+    av, aw, bv, bw = a[..., :3], a[..., 3:], b[..., :3], b[..., 3:]
+    v = aw * bv - bw * av - np.cross(av, bv)
+    w = aw[..., 0] * bw[..., 0] + (av * bv).sum(-1)
+    return 2 * np.arctan2(np.linalg.norm(v, axis=-1), np.abs(w))
 
 
 def vp(a):

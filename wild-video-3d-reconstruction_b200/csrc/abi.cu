@@ -43,6 +43,16 @@ int ba_reproject(const float*, const float*, const float*, const int64_t*, const
 int ba_neighbors(const int64_t*, const int64_t*, int64_t, int64_t, int64_t*, int64_t*, void*, size_t, int*, cudaStream_t);
 size_t plan_bytes(int64_t E, int64_t n_groups, int max_ctas);
 int plan_grid();
+size_t ba_global_workspace_bytes(int64_t E, int64_t n_patches);
+int ba_global_build(float*, float*, const float*, const float*, const float*, const float*, const int64_t*, const int64_t*,
+                    const int64_t*, int64_t, int64_t, int64_t, int, int, int, const float*, float, int, int, int, float*, float*,
+                    void*, size_t, int*, cudaStream_t);
+int ba_global_damp(float*, int, cudaStream_t);
+int ba_global_dz(float*, float*, const float*, const float*, const float*, const float*, const int64_t*, const int64_t*, int64_t,
+                 int64_t, int64_t, int, int, int, const float*, float, int, int, const float*, float*, void*, size_t, int*,
+                 cudaStream_t);
+int ba_global_retract(float*, float*, int64_t, int64_t, int64_t, int, int, int, const float*, const float*, void*, size_t,
+                      cudaStream_t);
 }  // namespace wv
 
 using namespace wv;
@@ -153,6 +163,57 @@ int wv_ba_forward_planned(float* poses, float* patches, const float* intrinsics,
   if (!poses || !patches || !intrinsics || !target || !weight || !lmbda || !ii || !jj || !kk || !workspace) return WV_EINVAL;
   return ba_forward_window(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk, E, n_poses, n_patches, P, t0, t1,
                            iterations, patches_est, mu, workspace, workspace_bytes, status, as_stream(stream), plan_groups);
+}
+
+size_t wv_ba_global_workspace_bytes(int64_t E, int64_t n_patches) {
+  if (E < 0 || n_patches < 0) return 0;
+  return ba_global_workspace_bytes(E, n_patches);
+}
+
+static int global_args_ok(int64_t E, int64_t n_poses, int64_t n_patches, int P, int t0, int t1, int shard, int nshards) {
+  if (E < 0 || n_poses <= 0 || n_patches <= 0 || P <= 0 || t0 < 0 || t1 < t0 || t1 > n_poses || nshards <= 0 || shard < 0 ||
+      shard >= nshards)
+    return WV_EINVAL;
+  if (E >= (int64_t)1 << 31 || n_patches >= (int64_t)1 << 31 || (int64_t)(t1 - t0) * 6 >= 46340) return WV_EUNSUPPORTED;
+  return WV_OK;
+}
+
+int wv_ba_global_build(float* poses, float* patches, const float* intrinsics, const float* target, const float* weight,
+                       const float* lmbda, const int64_t* ii, const int64_t* jj, const int64_t* kk, int64_t E, int64_t n_poses,
+                       int64_t n_patches, int P, int t0, int t1, const float* patches_est, float mu, int shard, int nshards,
+                       int build_plan, float* S, float* y, void* workspace, size_t workspace_bytes, int* status,
+                       wv_stream_t stream) {
+  const int rc = global_args_ok(E, n_poses, n_patches, P, t0, t1, shard, nshards);
+  if (rc != WV_OK) return rc;
+  if (!poses || !patches || !intrinsics || !target || !weight || !lmbda || !ii || !jj || !kk || !workspace) return WV_EINVAL;
+  if (t1 > t0 && (!S || !y)) return WV_EINVAL;
+  return ba_global_build(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk, E, n_poses, n_patches, P, t0, t1,
+                         patches_est, mu, shard, nshards, build_plan, S, y, workspace, workspace_bytes, status, as_stream(stream));
+}
+
+int wv_ba_global_damp(float* S, int n6, wv_stream_t stream) {
+  if (n6 < 0 || (n6 > 0 && !S)) return WV_EINVAL;
+  return ba_global_damp(S, n6, as_stream(stream));
+}
+
+int wv_ba_global_dz(float* poses, float* patches, const float* intrinsics, const float* target, const float* weight,
+                    const float* lmbda, const int64_t* ii, const int64_t* jj, int64_t E, int64_t n_poses, int64_t n_patches, int P,
+                    int t0, int t1, const float* patches_est, float mu, int shard, int nshards, const float* dX, float* dZ,
+                    void* workspace, size_t workspace_bytes, int* status, wv_stream_t stream) {
+  const int rc = global_args_ok(E, n_poses, n_patches, P, t0, t1, shard, nshards);
+  if (rc != WV_OK) return rc;
+  if (!poses || !patches || !intrinsics || !target || !weight || !lmbda || !ii || !jj || !dZ || !workspace) return WV_EINVAL;
+  if (t1 > t0 && !dX) return WV_EINVAL;
+  return ba_global_dz(poses, patches, intrinsics, target, weight, lmbda, ii, jj, E, n_poses, n_patches, P, t0, t1, patches_est, mu,
+                      shard, nshards, dX, dZ, workspace, workspace_bytes, status, as_stream(stream));
+}
+
+int wv_ba_global_retract(float* poses, float* patches, int64_t E, int64_t n_poses, int64_t n_patches, int P, int t0, int t1,
+                         const float* dX, const float* dZ, void* workspace, size_t workspace_bytes, wv_stream_t stream) {
+  const int rc = global_args_ok(E, n_poses, n_patches, P, t0, t1, 0, 1);
+  if (rc != WV_OK) return rc;
+  if (!poses || !patches || !dZ || !workspace || (t1 > t0 && !dX)) return WV_EINVAL;
+  return ba_global_retract(poses, patches, E, n_poses, n_patches, P, t0, t1, dX, dZ, workspace, workspace_bytes, as_stream(stream));
 }
 
 int wv_ba_reproject(const float* poses, const float* patches, const float* intrinsics, const int64_t* ii, const int64_t* jj,

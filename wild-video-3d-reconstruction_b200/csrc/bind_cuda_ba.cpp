@@ -45,6 +45,111 @@ torch::Tensor idx(const torch::Tensor& t, const char* name) {
   return t.contiguous().view({-1});
 }
 
+// ---- BA with more than 16 free poses (global BA): build / solve / dz / retract pieces over the C ABI's wv_ba_global_* -------
+struct BAIn {
+  torch::Tensor tg, wt, lm, ii, jj, kk, est;
+  const float* estp = nullptr;
+  int P = 0; int64_t E = 0, n_poses = 0, n_patches = 0;
+};
+
+BAIn ba_inputs(const torch::Tensor& poses, const torch::Tensor& patches, const torch::Tensor& intrinsics, const torch::Tensor& target,
+               const torch::Tensor& weight, const torch::Tensor& lmbda, const torch::Tensor& ii, const torch::Tensor& jj,
+               const torch::Tensor& kk, int t0, int t1, const c10::optional<torch::Tensor>& patches_est) {
+  check_f32c(poses, "poses"); check_f32c(patches, "patches"); check_f32c(intrinsics, "intrinsics");
+  TORCH_CHECK(patches.dim() >= 4, "cuda_ba: patches must be [..., 3, P, P]");
+  BAIn in;
+  in.P = patches.size(-1);
+  in.n_poses = poses.numel() / 7; in.n_patches = patches.numel() / (3 * in.P * in.P);
+  in.tg = target.to(torch::kFloat).contiguous().view({-1, 2}); in.wt = weight.to(torch::kFloat).contiguous().view({-1, 2});
+  in.lm = lmbda.to(torch::kFloat).contiguous().view({-1});
+  check_cuda(in.tg, "target"); check_cuda(in.wt, "weight"); check_cuda(in.lm, "lmbda");
+  in.ii = idx(ii, "ii"); in.jj = idx(jj, "jj"); in.kk = idx(kk, "kk");
+  in.E = in.ii.numel();
+  TORCH_CHECK(in.jj.numel() == in.E && in.kk.numel() == in.E && in.tg.size(0) == in.E && in.wt.size(0) == in.E,
+              "cuda_ba: inconsistent edge count");
+  TORCH_CHECK(t0 >= 0 && t1 >= t0 && t1 <= in.n_poses, "cuda_ba: bad pose window [t0, t1)");
+  if (patches_est.has_value() && patches_est->defined()) {
+    in.est = patches_est->to(torch::kFloat).contiguous();
+    TORCH_CHECK(in.est.numel() == patches.numel() && in.est.is_cuda(), "cuda_ba: patches_est must match patches");
+    in.estp = in.est.data_ptr<float>();
+  }
+  return in;
+}
+
+torch::Tensor global_ws(const torch::Device& dev, const BAIn& in) {
+  plan_note(dev.index()) = PlanNote();  // the shared workspace now holds this call's plan
+  return workspace(dev, wv_ba_global_workspace_bytes(in.E, in.n_patches));
+}
+
+// partial reduced system of this shard: returns one flat buffer [6N*6N + 6N] = [S (row-major, lower triangle) | y], so that a
+// multi-GPU caller sums it with ONE allreduce
+torch::Tensor global_build(torch::Tensor poses, torch::Tensor patches, torch::Tensor intrinsics, torch::Tensor target,
+                           torch::Tensor weight, torch::Tensor lmbda, torch::Tensor ii, torch::Tensor jj, torch::Tensor kk, int t0,
+                           int t1, int shard, int nshards, bool build_plan, c10::optional<torch::Tensor> patches_est, double mu) {
+  c10::cuda::CUDAGuard guard(poses.device());
+  BAIn in = ba_inputs(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk, t0, t1, patches_est);
+  const int64_t n6 = 6 * (int64_t)(t1 - t0);
+  torch::Tensor Sy = torch::empty({n6 * n6 + n6}, poses.options());
+  if (in.E == 0) return Sy.zero_();
+  torch::Tensor ws = build_plan ? global_ws(poses.device(), in) : workspace(poses.device(), wv_ba_global_workspace_bytes(in.E, in.n_patches));
+  check_rc(wv_ba_global_build(poses.data_ptr<float>(), patches.data_ptr<float>(), intrinsics.data_ptr<float>(), in.tg.data_ptr<float>(),
+                              in.wt.data_ptr<float>(), in.lm.data_ptr<float>(), in.ii.data_ptr<int64_t>(), in.jj.data_ptr<int64_t>(),
+                              in.kk.data_ptr<int64_t>(), in.E, in.n_poses, in.n_patches, in.P, t0, t1, in.estp, (float)mu, shard,
+                              nshards, build_plan ? 1 : 0, Sy.data_ptr<float>(), Sy.data_ptr<float>() + n6 * n6, ws.data_ptr(),
+                              (size_t)ws.numel(), status_word(poses.device()).data_ptr<int>(), current_stream()),
+           "cuda_ba.global_build");
+  return Sy;
+}
+
+// damping + the reference's own dense solve (ba_cuda.cu:517-523): returns dX [N, 6]
+torch::Tensor global_solve(torch::Tensor Sy, int n_free) {
+  c10::cuda::CUDAGuard guard(Sy.device());
+  const int64_t n6 = 6 * (int64_t)n_free;
+  TORCH_CHECK(Sy.is_cuda() && Sy.scalar_type() == torch::kFloat && Sy.is_contiguous() && Sy.numel() == n6 * n6 + n6,
+              "cuda_ba.global_solve: expected the flat [S | y] buffer of global_build");
+  if (n6 == 0) return torch::zeros({0, 6}, Sy.options());
+  check_rc(wv_ba_global_damp(Sy.data_ptr<float>(), (int)n6, current_stream()), "cuda_ba.global_solve");
+  torch::Tensor S = Sy.narrow(0, 0, n6 * n6).view({n6, n6}), y = Sy.narrow(0, n6 * n6, n6).view({n6, 1});
+  auto [L, info] = at::linalg_cholesky_ex(S, /*upper=*/false, /*check_errors=*/false);
+  TORCH_CHECK(info.item<int>() == 0, "cuda_ba.forward: linalg.cholesky: the reduced camera system is not positive-definite");
+  return at::cholesky_solve(y, L, /*upper=*/false).view({n_free, 6}).contiguous();
+}
+
+// this shard's depth updates (zeros elsewhere; a multi-GPU caller sums over ranks): dZ [min(E, n_patches)]
+torch::Tensor global_dz(torch::Tensor poses, torch::Tensor patches, torch::Tensor intrinsics, torch::Tensor target,
+                        torch::Tensor weight, torch::Tensor lmbda, torch::Tensor ii, torch::Tensor jj, torch::Tensor kk, int t0, int t1,
+                        int shard, int nshards, torch::Tensor dX, c10::optional<torch::Tensor> patches_est, double mu) {
+  c10::cuda::CUDAGuard guard(poses.device());
+  BAIn in = ba_inputs(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk, t0, t1, patches_est);
+  TORCH_CHECK(dX.is_cuda() && dX.scalar_type() == torch::kFloat && dX.is_contiguous() && dX.numel() == 6 * (int64_t)(t1 - t0),
+              "cuda_ba.global_dz: dX must be float32 [t1 - t0, 6]");
+  torch::Tensor dZ = torch::empty({std::min(in.E, in.n_patches)}, poses.options());
+  if (in.E == 0) return dZ;
+  torch::Tensor ws = workspace(poses.device(), wv_ba_global_workspace_bytes(in.E, in.n_patches));
+  check_rc(wv_ba_global_dz(poses.data_ptr<float>(), patches.data_ptr<float>(), intrinsics.data_ptr<float>(), in.tg.data_ptr<float>(),
+                           in.wt.data_ptr<float>(), in.lm.data_ptr<float>(), in.ii.data_ptr<int64_t>(), in.jj.data_ptr<int64_t>(), in.E,
+                           in.n_poses, in.n_patches, in.P, t0, t1, in.estp, (float)mu, shard, nshards, dX.data_ptr<float>(),
+                           dZ.data_ptr<float>(), ws.data_ptr(), (size_t)ws.numel(), status_word(poses.device()).data_ptr<int>(),
+                           current_stream()),
+           "cuda_ba.global_dz");
+  return dZ;
+}
+
+void global_retract(torch::Tensor poses, torch::Tensor patches, int64_t E, int t0, int t1, torch::Tensor dX, torch::Tensor dZ) {
+  check_f32c(poses, "poses"); check_f32c(patches, "patches");
+  c10::cuda::CUDAGuard guard(poses.device());
+  const int P = patches.size(-1);
+  const int64_t n_poses = poses.numel() / 7, n_patches = patches.numel() / (3 * P * P);
+  TORCH_CHECK(dX.is_cuda() && dX.scalar_type() == torch::kFloat && dX.is_contiguous() && dX.numel() == 6 * (int64_t)(t1 - t0) &&
+                  dZ.is_cuda() && dZ.scalar_type() == torch::kFloat && dZ.is_contiguous() && dZ.numel() == std::min(E, n_patches),
+              "cuda_ba.global_retract: dX / dZ do not match this problem");
+  if (E == 0) return;
+  torch::Tensor ws = workspace(poses.device(), wv_ba_global_workspace_bytes(E, n_patches));
+  check_rc(wv_ba_global_retract(poses.data_ptr<float>(), patches.data_ptr<float>(), E, n_poses, n_patches, P, t0, t1,
+                                dX.data_ptr<float>(), dZ.data_ptr<float>(), ws.data_ptr(), (size_t)ws.numel(), current_stream()),
+           "cuda_ba.global_retract");
+}
+
 std::vector<torch::Tensor> ba_forward(torch::Tensor poses, torch::Tensor patches, torch::Tensor intrinsics, torch::Tensor target,
                                       torch::Tensor weight, torch::Tensor lmbda, torch::Tensor ii, torch::Tensor jj,
                                       torch::Tensor kk, int t0, int t1, int iterations,
@@ -69,6 +174,17 @@ std::vector<torch::Tensor> ba_forward(torch::Tensor poses, torch::Tensor patches
     est = estc.data_ptr<float>();
   }
   if (E == 0 || iterations <= 0) return {};
+  if (t1 - t0 > 16) {  // global BA: dense reduced system in HBM, the reference's own dense solver
+    for (int it = 0; it < iterations; it++) {
+      torch::Tensor Sy = global_build(poses, patches, intrinsics, tg, wt, lm, iic, jjc, kkc, t0, t1, 0, 1, it == 0, patches_est, mu);
+      torch::Tensor dX = global_solve(Sy, t1 - t0);
+      Sy = torch::Tensor();
+      torch::Tensor dZ = global_dz(poses, patches, intrinsics, tg, wt, lm, iic, jjc, kkc, t0, t1, 0, 1, dX, patches_est, mu);
+      global_retract(poses, patches, E, t0, t1, dX, dZ);
+    }
+    raise_on_status(poses.device(), "cuda_ba.forward");
+    return {};
+  }
   PlanNote& note = plan_note(poses.device().index());
   const size_t wsb_shared = wv_ba_workspace_bytes(E, kPlanGroups, t1 - t0);
   torch::Tensor ws = workspace(poses.device(), std::max(wv_ba_workspace_bytes(E, n_patches, t1 - t0), note.E == E ? wsb_shared : (size_t)0));
@@ -160,6 +276,15 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.def("forward", &ba_forward, "BA forward operator", py::arg("poses"), py::arg("patches"), py::arg("intrinsics"),
         py::arg("target"), py::arg("weight"), py::arg("lmbda"), py::arg("ii"), py::arg("jj"), py::arg("kk"), py::arg("t0"),
         py::arg("t1"), py::arg("iterations"), py::arg("patches_est") = py::none(), py::arg("mu") = 2.0);
+  m.def("global_build", &global_build, "global BA: this shard's partial [S | y]", py::arg("poses"), py::arg("patches"),
+        py::arg("intrinsics"), py::arg("target"), py::arg("weight"), py::arg("lmbda"), py::arg("ii"), py::arg("jj"), py::arg("kk"),
+        py::arg("t0"), py::arg("t1"), py::arg("shard") = 0, py::arg("nshards") = 1, py::arg("build_plan") = true,
+        py::arg("patches_est") = py::none(), py::arg("mu") = 2.0);
+  m.def("global_solve", &global_solve, "global BA: damping + dense Cholesky solve -> dX");
+  m.def("global_dz", &global_dz, "global BA: this shard's depth updates", py::arg("poses"), py::arg("patches"), py::arg("intrinsics"),
+        py::arg("target"), py::arg("weight"), py::arg("lmbda"), py::arg("ii"), py::arg("jj"), py::arg("kk"), py::arg("t0"),
+        py::arg("t1"), py::arg("shard"), py::arg("nshards"), py::arg("dX"), py::arg("patches_est") = py::none(), py::arg("mu") = 2.0);
+  m.def("global_retract", &global_retract, "global BA: pose + patch retraction");
   m.def("neighbors", &neighbors, "temporal neighboor indicies");
   m.def("reproject", &reproject, "fused reprojection of all patch pixels");
   m.def("solve_system", &solve_system, "solve system");

@@ -1,1 +1,1 @@
-from .ba import BA, neighbors, reproject, solve_system  # noqa: F401
+from .ba import BA, BA_sharded, neighbors, reproject, solve_system  # noqa: F401

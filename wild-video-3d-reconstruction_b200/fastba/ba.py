@@ -13,3 +13,35 @@ def BA(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk, t0, t1, it
     dpvo/ba.py:151-159; leaving them out is the reference's 12-argument behaviour."""
     return cuda_ba.forward(poses.data, patches, intrinsics, target, weight, lmbda, ii, jj, kk, t0, t1, iterations,
                            patches_est, mu)
+
+
+def BA_sharded(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk, t0, t1, iterations=2, patches_est=None, mu=2.0,
+               group=None):
+    """fastba.BA for the global problem, patch-sharded over the ranks of `group`.
+
+    Every rank holds the full state (poses, patches, edge list) and calls this collectively.  Per Gauss-Newton iteration rank r
+    accumulates the partial reduced system [S | y] of ITS contiguous run of patches (cuda_ba.global_build), ONE all_reduce sums
+    the flat buffer, every rank runs the same dense solve (cuda_ba.global_solve: damping + Cholesky, ba_cuda.cu:517-523), rank r
+    back-substitutes its patches' depth updates (cuda_ba.global_dz), a second all_reduce sums the dZ vector, and every rank
+    applies the same retraction -- so the replicas of the state stay identical without a broadcast.
+    Without an initialised process group this is the single-GPU global path."""
+    import torch.distributed as dist
+
+    world, rank = 1, 0
+    if dist.is_available() and dist.is_initialized():
+        world, rank = dist.get_world_size(group), dist.get_rank(group)
+    poses = poses.data
+    E = ii.numel()
+    if E == 0 or iterations <= 0:
+        return
+    for it in range(iterations):
+        Sy = cuda_ba.global_build(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk, t0, t1, rank, world, it == 0,
+                                  patches_est, mu)
+        if world > 1:
+            dist.all_reduce(Sy, group=group)
+        dX = cuda_ba.global_solve(Sy, t1 - t0)
+        del Sy
+        dZ = cuda_ba.global_dz(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk, t0, t1, rank, world, dX, patches_est, mu)
+        if world > 1:
+            dist.all_reduce(dZ, group=group)
+        cuda_ba.global_retract(poses, patches, E, t0, t1, dX, dZ)

@@ -80,6 +80,21 @@ def all_pairs_edges(n, M):
     return kk // M, jj, kk
 
 
+def global_edges(n, M):
+    """Edge list of the reference's global BA in its fixed-pattern form (dpvo/dpvo.py:448-471): frame pairs (i, i+1) for all i,
+    plus (i, j) for every 5th i and j in [i+10, i+20); each pair carries all M patches of frame i, pair-major."""
+    fi = [np.arange(n - 1, dtype=np.int64)]
+    fj = [np.arange(1, n, dtype=np.int64)]
+    for i in range(0, n, 5):
+        j = np.arange(i + 10, min(i + 20, n), dtype=np.int64)
+        fi.append(np.full_like(j, i)); fj.append(j)
+    fi, fj = np.concatenate(fi), np.concatenate(fj)
+    ii = np.repeat(fi, M)
+    jj = np.repeat(fj, M)
+    kk = (fi[:, None] * M + np.arange(M, dtype=np.int64)[None]).reshape(-1)
+    return ii, jj, kk
+
+
 # ----------------------------------------------------------------------------- BA scene
 def make_ba_scene(seed=0, n=10, M=96, edges="all", ht=96, wd=128, fx=110.0, n_buffer=None,
                   pose_noise=0.02, depth_noise=0.1, pix_noise=0.5, first_frame=0, lifetime=13, removal=22):
@@ -112,6 +127,8 @@ def make_ba_scene(seed=0, n=10, M=96, edges="all", ht=96, wd=128, fx=110.0, n_bu
     patches_gt = patches.copy()
     if edges == "all":
         ii, jj, kk = all_pairs_edges(n, M)
+    elif edges == "global":
+        ii, jj, kk = global_edges(n, M)
     else:
         ii, jj, kk = tracker_edges(n, M, lifetime, removal)
     # true projections of the patch centres
