@@ -62,52 +62,92 @@ def make_inputs(seed_offset=0, small=False):
 
 
 class ClockSampler:
-    """nvidia-smi clocks/throttle reasons DURING the timed region (B200_PROFILING.md recipe)"""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock + clock-event (throttle) reasons sampled DURING the timed region.
 
-    def __init__(self, index):
-        self.index = index
-        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
-        self.p = None
+    The timed region of this workload is a few tens of milliseconds, shorter than one `nvidia-smi` start-up, so the samples come
+    from NVML in a thread (the same counters `nvidia-smi --query-gpu=clocks.sm,clocks_event_reasons.*` prints, B200_PROFILING.md),
+    one every ~1 ms; `nvidia-smi -lms` is only the fallback when NVML cannot be loaded."""
+    BITS = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20, "sw_power_cap": 0x4}
+
+    def __init__(self, torch_index):
+        import threading
+        self.sm, self.mx, self.reasons = [], None, set()
+        self.stop_flag = threading.Event()
+        self.thread = None
+        self.h = None
+        self.smi = None
+        try:
+            import pynvml
+            import torch
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            pr = torch.cuda.get_device_properties(torch_index)
+            try:
+                bus = "%08x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+                self.h = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+            except Exception:
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(torch_index)
+            self.mx = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self.h = None
+        self.index = torch_index
+
+    def _loop(self):
+        nv = self.nv
+        while not self.stop_flag.is_set():
+            try:
+                self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                r = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+                for name, bit in self.BITS.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self.stop_flag.wait(0.001)
 
     def start(self):
-        try:
-            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                       "-lms", "100"], stdout=self.f, stderr=subprocess.DEVNULL)
+        import threading
+        if self.h is not None:
+            self.thread = threading.Thread(target=self._loop, daemon=True)
+            self.thread.start()
+            return
+        try:  # fallback
+            self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+            q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+                 "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+            self.smi = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={q}", "--format=csv,noheader,nounits",
+                                         "-lms", "20"], stdout=self.f, stderr=subprocess.DEVNULL)
         except Exception:
-            self.p = None
+            self.smi = None
 
     def stop(self):
-        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
-        if self.p is None:
-            return out
-        self.p.terminate()
-        try:
-            self.p.wait(timeout=5)
-        except Exception:
-            self.p.kill()
-        self.f.flush()
-        self.f.seek(0)
-        sm, mx, reasons = [], [], set()
-        for line in self.f.read().splitlines():
-            c = [x.strip() for x in line.split(",")]
-            if len(c) < 9:
-                continue
+        out = {"sm_mhz": None, "sm_max_mhz": self.mx, "reasons": [], "source": "nvml thread, 1 ms period"}
+        if self.thread is not None:
+            self.stop_flag.set()
+            self.thread.join(timeout=2)
+        elif self.smi is not None:
+            out["source"] = "nvidia-smi -lms 20"
+            self.smi.terminate()
             try:
-                sm.append(float(c[1])); mx.append(float(c[2]))
-            except ValueError:
-                continue
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), c[5:9]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
-        os.unlink(self.f.name)
-        if sm:
-            # under load = the upper half of the samples (the sampler also sees the gaps between steps)
-            out["sm_mhz"] = float(np.median(sorted(sm)[len(sm) // 2:]))
-            out["sm_max_mhz"] = float(max(mx))
-        out["reasons"] = sorted(reasons)
-        out["samples"] = len(sm)
+                self.smi.wait(timeout=5)
+            except Exception:
+                self.smi.kill()
+            self.f.flush(); self.f.seek(0)
+            for line in self.f.read().splitlines():
+                c = [x.strip() for x in line.split(",")]
+                try:
+                    self.sm.append(float(c[0])); self.mx = max(self.mx or 0.0, float(c[1]))
+                except (ValueError, IndexError):
+                    continue
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), c[2:6]):
+                    if v.lower().startswith("active"):
+                        self.reasons.add(name)
+            os.unlink(self.f.name)
+            out["sm_max_mhz"] = self.mx
+        if self.sm:
+            out["sm_mhz"] = float(np.median(self.sm))
+        out["reasons"] = sorted(self.reasons)
+        out["samples"] = len(self.sm)
         return out
 
 
