@@ -29,13 +29,14 @@ def main():
     ap.add_argument("--reps", type=int, default=5)
     ap.add_argument("--check", action="store_true")
     ap.add_argument("--edges", default="global", help="global (dpvo.py:448-471 pattern) | tracker | all")
+    ap.add_argument("--loop-frac", type=float, default=0.02, help="config4: share of extra edges to random frames")
     a = ap.parse_args()
     rank, world, local = pkg.dist.init()
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     _, cb = pkg.native_modules()
     fb = importlib.import_module(pkg.__name__ + ".fastba")
-    s = pkg.synthetic.make_ba_scene(seed=5, n=a.frames, M=a.M, edges=a.edges, pose_noise=0.005)
+    s = pkg.synthetic.make_ba_scene(seed=5, n=a.frames, M=a.M, edges=a.edges, pose_noise=0.005, loop_frac=a.loop_frac)
     D = {k: torch.from_numpy(np.ascontiguousarray(s[k])).to(dev) for k in
          ("poses", "patches", "intrinsics", "target", "weight", "lmbda", "ii", "jj", "kk")}
     t0, t1 = 1, a.frames
@@ -63,14 +64,16 @@ def main():
     # per-piece device times of one iteration on this rank's shard
     wp, wq = D["poses"].clone(), D["patches"].clone()
     args = (wp, wq, D["intrinsics"], D["target"], D["weight"], D["lmbda"], D["ii"], D["jj"], D["kk"], t0, t1)
-    ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(6)]
     cb.global_build(*args, rank, world, True); torch.cuda.synchronize()
     ev[0].record(); Sy = cb.global_build(*args, rank, world, True)
     ev[1].record(); dX = cb.global_solve(Sy, t1 - t0)
     ev[2].record(); dZ = cb.global_dz(*args, rank, world, dX)
     ev[3].record(); cb.global_retract(wp, wq, E, t0, t1, dX, dZ)
-    ev[4].record(); torch.cuda.synchronize()
-    out["pieces_ms"] = {k: round(ev[i].elapsed_time(ev[i + 1]), 4) for i, k in enumerate(("plan+build", "damp+cholesky+solve", "dz", "retract"))}
+    ev[4].record(); Sy = cb.global_build(*args, rank, world, False)
+    ev[5].record(); torch.cuda.synchronize()
+    out["pieces_ms"] = {k: round(ev[i].elapsed_time(ev[i + 1]), 4)
+                        for i, k in enumerate(("plan+build", "damp+cholesky+solve", "dz", "retract", "build (plan reused)"))}
     del Sy
     if a.check:
         _, p1, q1 = run(False)

@@ -42,14 +42,39 @@ struct GArgs {
   int* status;
 };
 
-// block (fa, fb), fa > fb: all 36 entries; fa == fb: lower triangle of the diagonal block.  val(r, c) = s * A[r] * B[c]
-__device__ __forceinline__ void add_block(float* S, int n6, int fa, int fb, const float* A, const float* B, float s) {
+// A CTA works on a chunk of kChunk consecutive patches (consecutive ids = the same or neighbouring source frames, which observe
+// nearly the same set of frames), 8 consecutive patches per warp.
+//   * The Schur update of the chunk, sum_k q_k e_k e_k^T restricted to the diagonal window of frames [wb, wb + kWinFrames) that
+//     (almost) all of its entries fall into, is a small SYRK: the window parts of the columns e_k are laid out densely in shared
+//     memory (Ecol [kChunk][192]) and every thread accumulates 8x8 register tiles of the window's lower triangle over the 64
+//     columns -- no atomics -- and adds its tiles to S in HBM once per chunk.  Pairs with an entry outside the window
+//     (loop-closure edges) go to HBM as atomics directly.
+//   * The pose-block terms of an edge ((j,j), (i,j) and v_j: 63 values) are run-length accumulated in the lane's registers while
+//     consecutive patches of the warp keep the same (i, j) in that lane, and flushed with RED atomics when the key changes;
+//     the source-frame terms ((i,i), v_i) likewise per warp.
+static constexpr int kChunk = 64;
+static constexpr int kPerWarp = kChunk / kGWarps;  // 8 consecutive patches per warp
+static constexpr int kWinFrames = 32;
+static constexpr int kWinDim = 6 * kWinFrames;  // 192
+static constexpr int kTile = 8;
+static constexpr int kTilesPerDim = kWinDim / kTile;                    // 24
+static constexpr int kTiles = kTilesPerDim * (kTilesPerDim + 1) / 2;    // 300 lower tiles
+static constexpr size_t kBuildSmem = sizeof(float) * (kChunk * kWinDim + 2 * kChunk);
+
+// 8-byte vector RED (sm_90+): rows of a 6x6 block start at an even float offset (n6 and 6*fb are even), S is 256-B aligned
+__device__ __forceinline__ void red2(float* p, float x, float y) { atomicAdd(reinterpret_cast<float2*>(p), make_float2(x, y)); }
+
+// block (fa, fb) of S with fa >= fb += s A B^T, straight to HBM (fa == fb: lower triangle of the block only)
+__device__ __forceinline__ void red_block(float* S, int n6, int fa, int fb, const float* A, const float* B, float s) {
   float* base = S + (size_t)(6 * fa) * n6 + 6 * fb;
-  if (fa > fb) {
+  if (fa != fb) {
 #pragma unroll
-    for (int r = 0; r < 6; r++)
-#pragma unroll
-      for (int c = 0; c < 6; c++) atomicAdd(base + (size_t)r * n6 + c, s * A[r] * B[c]);
+    for (int r = 0; r < 6; r++) {
+      const float ar = s * A[r];
+      red2(base + (size_t)r * n6, ar * B[0], ar * B[1]);
+      red2(base + (size_t)r * n6 + 2, ar * B[2], ar * B[3]);
+      red2(base + (size_t)r * n6 + 4, ar * B[4], ar * B[5]);
+    }
   } else {
 #pragma unroll
     for (int r = 0; r < 6; r++)
@@ -58,10 +83,63 @@ __device__ __forceinline__ void add_block(float* S, int n6, int fa, int fb, cons
   }
 }
 
+struct LaneAcc {  // run-length accumulators of one lane: pose-block terms of edges (fi -> fj)
+  int fi, fj;     // free-pose indices of the current key (may be out of [0, N): fixed pose)
+  float JJ[21], IJ[36], vj[6];
+};
+
+__device__ __forceinline__ void lane_acc_reset(LaneAcc& A, int fi, int fj) {
+  A.fi = fi; A.fj = fj;
+#pragma unroll
+  for (int t = 0; t < 21; t++) A.JJ[t] = 0.f;
+#pragma unroll
+  for (int t = 0; t < 36; t++) A.IJ[t] = 0.f;
+#pragma unroll
+  for (int t = 0; t < 6; t++) A.vj[t] = 0.f;
+}
+
+__device__ __forceinline__ void lane_acc_flush(const LaneAcc& A, float* S, float* y, int N, int n6) {
+  const bool free_i = A.fi >= 0 && A.fi < N, free_j = A.fj >= 0 && A.fj < N;
+  if (!free_j) return;
+  {
+    float* b = S + (size_t)(6 * A.fj) * n6 + 6 * A.fj;
+    int t = 0;
+#pragma unroll
+    for (int p = 0; p < 6; p++) {
+#pragma unroll
+      for (int c = 0; c <= p; c++) atomicAdd(b + (size_t)p * n6 + c, A.JJ[t++]);
+      atomicAdd(y + 6 * A.fj + p, A.vj[p]);
+    }
+  }
+  if (!free_i) return;
+  if (A.fi > A.fj) {
+    float* b = S + (size_t)(6 * A.fi) * n6 + 6 * A.fj;
+#pragma unroll
+    for (int p = 0; p < 6; p++)
+#pragma unroll
+      for (int c = 0; c < 6; c += 2) red2(b + (size_t)p * n6 + c, -A.IJ[6 * p + c], -A.IJ[6 * p + c + 1]);
+  } else if (A.fi < A.fj) {
+    float* b = S + (size_t)(6 * A.fj) * n6 + 6 * A.fi;
+#pragma unroll
+    for (int c = 0; c < 6; c++)
+#pragma unroll
+      for (int p = 0; p < 6; p += 2) red2(b + (size_t)c * n6 + p, -A.IJ[6 * p + c], -A.IJ[6 * (p + 1) + c]);
+  } else {
+    float* b = S + (size_t)(6 * A.fi) * n6 + 6 * A.fi;
+#pragma unroll
+    for (int p = 0; p < 6; p++)
+#pragma unroll
+      for (int c = 0; c <= p; c++) atomicAdd(b + (size_t)p * n6 + c, -(A.IJ[6 * p + c] + A.IJ[6 * c + p]));
+  }
+}
+
 template <bool BUILD>
 __global__ void __launch_bounds__(kGThreads) ba_global_kernel(GArgs a) {
+  extern __shared__ float dyn_mem[];  // BUILD: Ecol [kChunk][kWinDim], q [kChunk], qu [kChunk]
   __shared__ float ent_v[kGWarps][kMaxEntries][6];
   __shared__ int ent_f[kGWarps][kMaxEntries];
+  __shared__ int s_wb;
+  __shared__ int perm[kGWarps][32];
   const int N = a.N, n6 = 6 * N;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int PP = a.P * a.P, ctr = (a.P / 2) * a.P + a.P / 2;
@@ -69,179 +147,301 @@ __global__ void __launch_bounds__(kGThreads) ba_global_kernel(GArgs a) {
   const float lambda = a.lmbda[0];
   const int Mp = a.p.hdr->Mp;
   const int r_lo = (int)((long long)Mp * a.shard / a.nshards), r_hi = (int)((long long)Mp * (a.shard + 1) / a.nshards);
-  const int gw = blockIdx.x * kGWarps + warp, nw = gridDim.x * kGWarps;
   const unsigned FULL = 0xffffffffu;
   float(*ev)[6] = ent_v[warp];
   int* ef = ent_f[warp];
+  float* Ecol = dyn_mem;
+  float* qs = dyn_mem + kChunk * kWinDim;
+  float* qus = qs + kChunk;
+  const int nchunks = (r_hi - r_lo + kChunk - 1) / kChunk;
 
-  for (int r = r_lo + gw; r < r_hi; r += nw) {
-    const int id = a.p.kx[r], off = a.p.seg_off[r], n = a.p.seg_off[r + 1] - off;
-    const float* pc = a.patches + (size_t)id * 3 * PP;
-    const float px = pc[ctr], py = pc[PP + ctr], pd = pc[2 * PP + ctr];
-    float Csum = 0.f, usum = 0.f;
-    int L = 0;  // entries so far (warp-uniform)
-    bool overflow = false;
-    for (int base = 0; base < n; base += 32) {
-      bool act = base + lane < n;
-      const int e = act ? a.p.eperm[off + base + lane] : 0;
-      int ix = -1, jx = -1;
-      if (act) {
-        const int64_t iv = a.ii[e], jv = a.jj[e];
-        if (iv < 0 || iv >= a.n_poses || jv < 0 || jv >= a.n_poses) { set_status(a.status, WV_STATUS_BAD_INDEX); act = false; }
-        else { ix = (int)iv; jx = (int)jv; }
+  for (int ch = blockIdx.x; ch < nchunks; ch += gridDim.x) {
+    const int c_lo = r_lo + ch * kChunk, c_hi = min(c_lo + kChunk, r_hi);
+    int wb = 0;
+    if (BUILD) {
+      // window base: the lowest free frame the chunk's first patch touches (its segment is ordered by target frame)
+      if (threadIdx.x == 0) {
+        const int e0 = a.p.eperm[a.p.seg_off[c_lo]];
+        long long f = min(a.jj[e0], a.ii[e0]) - a.t0;
+        s_wb = (int)max(0ll, min(f, (long long)max(N - kWinFrames, 0)));
       }
-      const int fi = ix - a.t0, fj = jx - a.t0;
-      const bool free_i = act && fi >= 0 && fi < N, free_j = act && fj >= 0 && fj < N;
-      EdgeTerms T;
-      float Ej[6], Ei[6];
+      for (int t = threadIdx.x; t < kChunk * kWinDim + 2 * kChunk; t += kGThreads) dyn_mem[t] = 0.f;
+      __syncthreads();
+      wb = s_wb;
+    }
+    LaneAcc acc;
+    float II[21], vi[6];
+    int acc_f0 = -1;  // free index of the source frame the II / vi accumulators belong to (warp-uniform), -1: none
+    if (BUILD) {
+      lane_acc_reset(acc, -1, -1);
 #pragma unroll
-      for (int c = 0; c < 6; c++) { Ej[c] = 0.f; Ei[c] = 0.f; }
-      if (act) {
-        edge_terms(a, e, ix, jx, px, py, pd, fx, fy, cx, cy, T);
-        Csum += T.w[0] * T.Jz[0] * T.Jz[0] + T.w[1] * T.Jz[1] * T.Jz[1];
-        usum += T.w[0] * T.r[0] * T.Jz[0] + T.w[1] * T.r[1] * T.Jz[1];
+      for (int t = 0; t < 21; t++) II[t] = 0.f;
 #pragma unroll
-        for (int c = 0; c < 6; c++) {
-          Ej[c] = T.w[0] * T.Jz[0] * T.Jj[0][c] + T.w[1] * T.Jz[1] * T.Jj[1][c];
-          Ei[c] = -(T.w[0] * T.Jz[0] * T.Ji[0][c] + T.w[1] * T.Jz[1] * T.Ji[1][c]);
-        }
-      }
-      // source frame shared by the whole chunk (the tracker's edge lists): its block / entry are reduced in the warp first
-      const int ix0 = __shfl_sync(FULL, ix, 0);
-      const bool uni = __all_sync(FULL, !act || ix == ix0);
-      const int f0 = ix0 - a.t0;
-      const bool free0 = uni && f0 >= 0 && f0 < N;
-      if (BUILD) {
+      for (int t = 0; t < 6; t++) vi[t] = 0.f;
+    }
+    for (int pi = 0; pi < kPerWarp; pi++) {
+      const int r = c_lo + warp * kPerWarp + pi;
+      if (r >= c_hi) break;
+      const int id = a.p.kx[r], off = a.p.seg_off[r], n = a.p.seg_off[r + 1] - off;
+      const float* pc = a.patches + (size_t)id * 3 * PP;
+      const float px = pc[ctr], py = pc[PP + ctr], pd = pc[2 * PP + ctr];
+      float Csum = 0.f, usum = 0.f;
+      int L = 0;  // entries so far (warp-uniform)
+      bool overflow = false;
+      for (int base = 0; base < n; base += 32) {
+        bool act = base + lane < n;
+        int e = act ? a.p.eperm[off + base + lane] : 0;
+        int ix = -1, jx = -1;
         if (act) {
-          if (free_j) {  // (j, j) block and v_j: both residual rows combined, one set of atomics per edge
-            float* base_jj = a.S + (size_t)(6 * fj) * n6 + 6 * fj;
+          const int64_t iv = a.ii[e], jv = a.jj[e];
+          if (iv < 0 || iv >= a.n_poses || jv < 0 || jv >= a.n_poses) { set_status(a.status, WV_STATUS_BAD_INDEX); act = false; }
+          else { ix = (int)iv; jx = (int)jv; }
+        }
+        if (BUILD) {
+          // lane assignment: edges into the window first, in target-frame order, then the others (loop closures).  Patches of one
+          // source frame then present the same (i, j) to the same lane, whatever loop edges they carry, and the run-length
+          // accumulators below survive from patch to patch.
+          const int fj0 = jx - a.t0;
+          const bool inw = act && fj0 >= wb && fj0 < wb + kWinFrames;
+          const unsigned m_in = __ballot_sync(FULL, inw), m_out = __ballot_sync(FULL, act && !inw);
+          const unsigned below = (1u << lane) - 1u;
+          const int np = inw ? __popc(m_in & below)
+                             : (act ? __popc(m_in) + __popc(m_out & below) : __popc(m_in) + __popc(m_out) + __popc(~(m_in | m_out) & below));
+          perm[warp][np] = lane;
+          __syncwarp();
+          const int src = perm[warp][lane];
+          __syncwarp();
+          e = __shfl_sync(FULL, e, src); ix = __shfl_sync(FULL, ix, src); jx = __shfl_sync(FULL, jx, src);
+          act = __shfl_sync(FULL, (int)act, src) != 0;
+        }
+        const int fi = ix - a.t0, fj = jx - a.t0;
+        const bool free_i = act && fi >= 0 && fi < N, free_j = act && fj >= 0 && fj < N;
+        EdgeTerms T;
+        float Ej[6], Ei[6];
+#pragma unroll
+        for (int c = 0; c < 6; c++) { Ej[c] = 0.f; Ei[c] = 0.f; }
+        if (act) {
+          edge_terms(a, e, ix, jx, px, py, pd, fx, fy, cx, cy, T);
+          Csum += T.w[0] * T.Jz[0] * T.Jz[0] + T.w[1] * T.Jz[1] * T.Jz[1];
+          usum += T.w[0] * T.r[0] * T.Jz[0] + T.w[1] * T.r[1] * T.Jz[1];
+#pragma unroll
+          for (int c = 0; c < 6; c++) {
+            Ej[c] = T.w[0] * T.Jz[0] * T.Jj[0][c] + T.w[1] * T.Jz[1] * T.Jj[1][c];
+            Ei[c] = -(T.w[0] * T.Jz[0] * T.Ji[0][c] + T.w[1] * T.Jz[1] * T.Ji[1][c]);
+          }
+        }
+        // source frame shared by all lanes of the chunk (the tracker's edge lists): its terms are reduced in the warp
+        const int ix0 = __shfl_sync(FULL, ix, 0);
+        const bool uni = __all_sync(FULL, !act || ix == ix0);
+        const int f0 = ix0 - a.t0;
+        const bool free0 = uni && f0 >= 0 && f0 < N;
+        if (BUILD) {
+          // ---- (j,j), (i,j), v_j: run-length accumulation in this lane
+          if (act && (free_j || free_i)) {
+            if (acc.fi != fi || acc.fj != fj) { lane_acc_flush(acc, a.S, a.y, N, n6); lane_acc_reset(acc, fi, fj); }
+            int t = 0;
 #pragma unroll
             for (int p = 0; p < 6; p++) {
 #pragma unroll
-              for (int c = 0; c <= p; c++)
-                atomicAdd(base_jj + (size_t)p * n6 + c, T.w[0] * T.Jj[0][p] * T.Jj[0][c] + T.w[1] * T.Jj[1][p] * T.Jj[1][c]);
-              atomicAdd(a.y + 6 * fj + p, T.w[0] * T.r[0] * T.Jj[0][p] + T.w[1] * T.r[1] * T.Jj[1][p]);
+              for (int c = 0; c <= p; c++) acc.JJ[t++] += T.w[0] * T.Jj[0][p] * T.Jj[0][c] + T.w[1] * T.Jj[1][p] * T.Jj[1][c];
+#pragma unroll
+              for (int c = 0; c < 6; c++) acc.IJ[6 * p + c] += T.w[0] * T.Ji[0][p] * T.Jj[0][c] + T.w[1] * T.Ji[1][p] * T.Jj[1][c];
+              acc.vj[p] += T.w[0] * T.r[0] * T.Jj[0][p] + T.w[1] * T.r[1] * T.Jj[1][p];
             }
           }
-          if (free_i && free_j) {  // (i, j) cross block: -w Ji Jj^T
-            if (fi > fj) {
-              float* b2 = a.S + (size_t)(6 * fi) * n6 + 6 * fj;
+          // ---- (i,i), v_i
+          const int want = free0 ? f0 : -1;
+          if (acc_f0 != want && acc_f0 >= 0) {  // warp-uniform: reduce + flush the previous source frame
+            int t = 0;
 #pragma unroll
-              for (int p = 0; p < 6; p++)
+            for (int p = 0; p < 6; p++) {
 #pragma unroll
-                for (int c = 0; c < 6; c++)
-                  atomicAdd(b2 + (size_t)p * n6 + c, -(T.w[0] * T.Ji[0][p] * T.Jj[0][c] + T.w[1] * T.Ji[1][p] * T.Jj[1][c]));
-            } else if (fi < fj) {
-              float* b2 = a.S + (size_t)(6 * fj) * n6 + 6 * fi;
-#pragma unroll
-              for (int p = 0; p < 6; p++)
-#pragma unroll
-                for (int c = 0; c < 6; c++)
-                  atomicAdd(b2 + (size_t)c * n6 + p, -(T.w[0] * T.Ji[0][p] * T.Jj[0][c] + T.w[1] * T.Ji[1][p] * T.Jj[1][c]));
-            } else {
-              float* b2 = a.S + (size_t)(6 * fi) * n6 + 6 * fi;
-#pragma unroll
-              for (int p = 0; p < 6; p++)
-#pragma unroll
-                for (int c = 0; c <= p; c++)
-                  atomicAdd(b2 + (size_t)p * n6 + c, -(T.w[0] * (T.Ji[0][p] * T.Jj[0][c] + T.Jj[0][p] * T.Ji[0][c]) +
-                                                       T.w[1] * (T.Ji[1][p] * T.Jj[1][c] + T.Jj[1][p] * T.Ji[1][c])));
-            }
-          }
-        }
-        // (i, i) block and v_i
-        if (free0) {
-          int t = 0;
-#pragma unroll
-          for (int p = 0; p < 6; p++) {
-#pragma unroll
-            for (int c = 0; c <= p; c++) {
-              float v = act ? T.w[0] * T.Ji[0][p] * T.Ji[0][c] + T.w[1] * T.Ji[1][p] * T.Ji[1][c] : 0.f;
-              v = warp_sum(v);
-              if (lane == t) atomicAdd(a.S + (size_t)(6 * f0 + p) * n6 + 6 * f0 + c, v);
-              t++;
-            }
-            float w = act ? T.w[0] * T.r[0] * T.Ji[0][p] + T.w[1] * T.r[1] * T.Ji[1][p] : 0.f;
-            w = warp_sum(w);
-            if (lane == 21 + p) atomicAdd(a.y + 6 * f0 + p, -w);
-          }
-        } else if (free_i) {  // mixed source frames: per-edge atomics
-          float* b2 = a.S + (size_t)(6 * fi) * n6 + 6 * fi;
-#pragma unroll
-          for (int p = 0; p < 6; p++) {
-#pragma unroll
-            for (int c = 0; c <= p; c++)
-              atomicAdd(b2 + (size_t)p * n6 + c, T.w[0] * T.Ji[0][p] * T.Ji[0][c] + T.w[1] * T.Ji[1][p] * T.Ji[1][c]);
-            atomicAdd(a.y + 6 * fi + p, -(T.w[0] * T.r[0] * T.Ji[0][p] + T.w[1] * T.r[1] * T.Ji[1][p]));
-          }
-        }
-      }
-      // ---- entries of the patch's column of E
-      {
-        const unsigned mj = __ballot_sync(FULL, free_j);
-        const int nj = __popc(mj);
-        if (L + nj <= kMaxEntries) {
-          if (free_j) {
-            const int s = L + __popc(mj & ((1u << lane) - 1u));
-            ef[s] = fj;
-#pragma unroll
-            for (int c = 0; c < 6; c++) ev[s][c] = Ej[c];
-          }
-          L += nj;
-        } else overflow = true;
-        if (uni) {
-          float Es[6];
-#pragma unroll
-          for (int c = 0; c < 6; c++) Es[c] = warp_sum(Ei[c]);
-          if (free0) {
-            if (L + 1 <= kMaxEntries) {
-              if (lane == 0) {
-                ef[L] = f0;
-#pragma unroll
-                for (int c = 0; c < 6; c++) ev[L][c] = Es[c];
+              for (int c = 0; c <= p; c++) {
+                const float v = warp_sum(II[t]);
+                if (lane == t) atomicAdd(a.S + (size_t)(6 * acc_f0 + p) * n6 + 6 * acc_f0 + c, v);
+                II[t] = 0.f;
+                t++;
               }
-              L += 1;
+              const float wv = warp_sum(vi[p]);
+              if (lane == 21 + p) atomicAdd(a.y + 6 * acc_f0 + p, -wv);
+              vi[p] = 0.f;
+            }
+          }
+          acc_f0 = want;
+          if (free0) {
+            if (act) {
+              int t = 0;
+#pragma unroll
+              for (int p = 0; p < 6; p++) {
+#pragma unroll
+                for (int c = 0; c <= p; c++) II[t++] += T.w[0] * T.Ji[0][p] * T.Ji[0][c] + T.w[1] * T.Ji[1][p] * T.Ji[1][c];
+                vi[p] += T.w[0] * T.r[0] * T.Ji[0][p] + T.w[1] * T.r[1] * T.Ji[1][p];
+              }
+            }
+          } else if (free_i) {  // mixed source frames inside one chunk of lanes: per-edge atomics
+            red_block(a.S, n6, fi, fi, T.Ji[0], T.Ji[0], T.w[0]);
+            red_block(a.S, n6, fi, fi, T.Ji[1], T.Ji[1], T.w[1]);
+#pragma unroll
+            for (int p = 0; p < 6; p++) atomicAdd(a.y + 6 * fi + p, -(T.w[0] * T.r[0] * T.Ji[0][p] + T.w[1] * T.r[1] * T.Ji[1][p]));
+          }
+        }
+        // ---- entries of the patch's column of E
+        {
+          const unsigned mj = __ballot_sync(FULL, free_j);
+          const int nj = __popc(mj);
+          if (L + nj <= kMaxEntries) {
+            if (free_j) {
+              const int s = L + __popc(mj & ((1u << lane) - 1u));
+              ef[s] = fj;
+#pragma unroll
+              for (int c = 0; c < 6; c++) ev[s][c] = Ej[c];
+            }
+            L += nj;
+          } else overflow = true;
+          if (uni) {
+            float Es[6];
+#pragma unroll
+            for (int c = 0; c < 6; c++) Es[c] = warp_sum(Ei[c]);
+            if (free0) {
+              if (L + 1 <= kMaxEntries) {
+                if (lane == 0) {
+                  ef[L] = f0;
+#pragma unroll
+                  for (int c = 0; c < 6; c++) ev[L][c] = Es[c];
+                }
+                L += 1;
+              } else overflow = true;
+            }
+          } else {
+            const unsigned mi = __ballot_sync(FULL, free_i);
+            const int ni = __popc(mi);
+            if (L + ni <= kMaxEntries) {
+              if (free_i) {
+                const int s = L + __popc(mi & ((1u << lane) - 1u));
+                ef[s] = fi;
+#pragma unroll
+                for (int c = 0; c < 6; c++) ev[s][c] = Ei[c];
+              }
+              L += ni;
             } else overflow = true;
           }
-        } else {
-          const unsigned mi = __ballot_sync(FULL, free_i);
-          const int ni = __popc(mi);
-          if (L + ni <= kMaxEntries) {
-            if (free_i) {
-              const int s = L + __popc(mi & ((1u << lane) - 1u));
-              ef[s] = fi;
-#pragma unroll
-              for (int c = 0; c < 6; c++) ev[s][c] = Ei[c];
-            }
-            L += ni;
-          } else overflow = true;
         }
+        __syncwarp();
+      }
+      if (overflow && lane == 0) set_status(a.status, WV_STATUS_TOO_DENSE);
+      float C = warp_sum(Csum), u = warp_sum(usum);
+      if (a.patches_est) {  // depth prior (dpvo/ba.py:151-159)
+        const float dest = a.patches_est[(size_t)id * 3 * PP + 2 * PP + ctr];
+        if (dest > 0.f) { C += a.mu; u -= a.mu * (pd - dest); }
+      }
+      const float q = 1.f / (C + lambda);
+      if (BUILD) {
+        if (N > 0) {
+          // window part of the column -> Ecol (entries of one patch may repeat a frame: add), the rest -> HBM atomics
+          const int col = r - c_lo;
+          float* mycol = Ecol + col * kWinDim;
+          for (int t = lane; t < L * 6; t += 32) {
+            const int en = t / 6, c = t - 6 * en, f = ef[en];
+            if (f >= wb && f < wb + kWinFrames) atomicAdd(mycol + 6 * (f - wb) + c, ev[en][c]);
+            else atomicAdd(a.y + 6 * f + c, -q * u * ev[en][c]);
+          }
+          if (lane == 0) { qs[col] = q; qus[col] = q * u; }
+          // pairs with an entry outside the window (loop-closure edges): one block per lane, straight to HBM
+          bool any_out = false;
+          for (int t = lane; t < L; t += 32) any_out |= ef[t] < wb || ef[t] >= wb + kWinFrames;
+          if (__any_sync(FULL, any_out)) {
+            for (int ea = 0; ea < L; ea++) {
+              const int fa = ef[ea];
+              if (fa >= wb && fa < wb + kWinFrames) continue;  // warp-uniform
+              for (int eb = lane; eb < L; eb += 32) {
+                const int fb = ef[eb];
+                const bool in_b = fb >= wb && fb < wb + kWinFrames;
+                if (fa > fb) red_block(a.S, n6, fa, fb, ev[ea], ev[eb], -q);
+                else if (fa < fb) { if (in_b) red_block(a.S, n6, fb, fa, ev[eb], ev[ea], -q); }  // (out, out) is visited from the other side
+                else red_block(a.S, n6, fa, fa, ev[ea], ev[eb], -q);
+              }
+            }
+          }
+        }
+      } else {
+        float sdot = 0.f;
+        for (int t = lane; t < L * 6; t += 32) sdot += ev[t / 6][t % 6] * a.dX[6 * ef[t / 6] + t % 6];
+        sdot = warp_sum(sdot);
+        if (lane == 0) a.dZ[r] = q * (u - sdot);
       }
       __syncwarp();
     }
-    if (overflow && lane == 0) set_status(a.status, WV_STATUS_TOO_DENSE);
-    float C = warp_sum(Csum), u = warp_sum(usum);
-    if (a.patches_est) {  // depth prior (dpvo/ba.py:151-159)
-      const float dest = a.patches_est[(size_t)id * 3 * PP + 2 * PP + ctr];
-      if (dest > 0.f) { C += a.mu; u -= a.mu * (pd - dest); }
-    }
-    const float q = 1.f / (C + lambda);
     if (BUILD) {
-      if (N > 0) {
-        for (int t = lane; t < L * L; t += 32) {
-          const int ea = t / L, eb = t - ea * L;
-          const int fa = ef[ea], fb = ef[eb];
-          if (fa >= fb) add_block(a.S, n6, fa, fb, ev[ea], ev[eb], -q);
+      // flush the run-length accumulators
+      lane_acc_flush(acc, a.S, a.y, N, n6);
+      if (acc_f0 >= 0) {
+        int t = 0;
+#pragma unroll
+        for (int p = 0; p < 6; p++) {
+#pragma unroll
+          for (int c = 0; c <= p; c++) {
+            const float v = warp_sum(II[t]);
+            if (lane == t) atomicAdd(a.S + (size_t)(6 * acc_f0 + p) * n6 + 6 * acc_f0 + c, v);
+            t++;
+          }
+          const float wv = warp_sum(vi[p]);
+          if (lane == 21 + p) atomicAdd(a.y + 6 * acc_f0 + p, -wv);
         }
-        for (int t = lane; t < L * 6; t += 32) atomicAdd(a.y + 6 * ef[t / 6] + t % 6, -q * u * ev[t / 6][t % 6]);
       }
-    } else {
-      float sdot = 0.f;
-      for (int t = lane; t < L * 6; t += 32) sdot += ev[t / 6][t % 6] * a.dX[6 * ef[t / 6] + t % 6];
-      sdot = warp_sum(sdot);
-      if (lane == 0) a.dZ[r] = q * (u - sdot);
+      __syncthreads();
+      // ---- window SYRK: W -= sum_k q_k e_k e_k^T over the chunk's columns, 8x8 register tiles of the lower triangle
+      const int wb6 = 6 * wb;
+      const int ncol = c_hi - c_lo;
+      for (int tile = threadIdx.x; tile < kTiles; tile += kGThreads) {
+        int tr = (int)((sqrtf(8.f * tile + 1.f) - 1.f) * 0.5f);
+        while ((tr + 1) * (tr + 2) / 2 <= tile) tr++;
+        while (tr * (tr + 1) / 2 > tile) tr--;
+        const int tc = tile - tr * (tr + 1) / 2;
+        if (wb6 + tr * kTile >= n6) continue;
+        float accT[kTile][kTile];
+#pragma unroll
+        for (int i = 0; i < kTile; i++)
+#pragma unroll
+          for (int j = 0; j < kTile; j++) accT[i][j] = 0.f;
+        for (int k = 0; k < ncol; k++) {
+          const float4* ra = reinterpret_cast<const float4*>(Ecol + k * kWinDim + tr * kTile);
+          const float4* rb = reinterpret_cast<const float4*>(Ecol + k * kWinDim + tc * kTile);
+          const float4 a0 = ra[0], a1 = ra[1], b0 = rb[0], b1 = rb[1];
+          const float nq = -qs[k];
+          const float av[8] = {a0.x * nq, a0.y * nq, a0.z * nq, a0.w * nq, a1.x * nq, a1.y * nq, a1.z * nq, a1.w * nq};
+          const float bv[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+          for (int i = 0; i < kTile; i++)
+#pragma unroll
+            for (int j = 0; j < kTile; j++) accT[i][j] = fmaf(av[i], bv[j], accT[i][j]);
+        }
+#pragma unroll
+        for (int i = 0; i < kTile; i++) {
+          const int R = wb6 + tr * kTile + i;
+          if (R >= n6) break;
+          float* grow = a.S + (size_t)R * n6 + wb6 + tc * kTile;
+          if (tr != tc && ((wb6 + tc * kTile) & 3) == 0 && (n6 & 3) == 0) {  // 16-B aligned rows: two vector REDs
+            if (accT[i][0] != 0.f || accT[i][1] != 0.f || accT[i][2] != 0.f || accT[i][3] != 0.f)
+              atomicAdd(reinterpret_cast<float4*>(grow), make_float4(accT[i][0], accT[i][1], accT[i][2], accT[i][3]));
+            if (accT[i][4] != 0.f || accT[i][5] != 0.f || accT[i][6] != 0.f || accT[i][7] != 0.f)
+              atomicAdd(reinterpret_cast<float4*>(grow + 4), make_float4(accT[i][4], accT[i][5], accT[i][6], accT[i][7]));
+          } else {
+#pragma unroll
+            for (int j = 0; j < kTile; j++) {
+              // lower triangle of S only (like every other writer)
+              if (wb6 + tc * kTile + j <= R && accT[i][j] != 0.f) atomicAdd(grow + j, accT[i][j]);
+            }
+          }
+        }
+      }
+      for (int t = threadIdx.x; t < kWinDim; t += kGThreads) {
+        if (wb6 + t >= n6) break;
+        float s = 0.f;
+        for (int k = 0; k < ncol; k++) s = fmaf(-qus[k], Ecol[k * kWinDim + t], s);
+        if (s != 0.f) atomicAdd(a.y + wb6 + t, s);
+      }
+      __syncthreads();
     }
-    __syncwarp();
   }
 }
 
@@ -288,8 +488,8 @@ static GArgs make_gargs(float* poses, float* patches, const float* intr, const f
 }
 
 static int global_grid(int64_t n_patches_guess) {
-  const int64_t want = (n_patches_guess + kGWarps - 1) / kGWarps;
-  const int64_t cap = (int64_t)sm_count() * 8;
+  const int64_t want = (n_patches_guess + kChunk - 1) / kChunk;
+  const int64_t cap = (int64_t)sm_count() * 2;
   return (int)std::max<int64_t>(1, std::min(want, cap));
 }
 
@@ -310,7 +510,8 @@ int ba_global_build(float* poses, float* patches, const float* intr, const float
     WV_CUDA_TRY(cudaMemsetAsync(S, 0, n6 * n6 * sizeof(float), st));
     WV_CUDA_TRY(cudaMemsetAsync(y, 0, n6 * sizeof(float), st));
   }
-  ba_global_kernel<true><<<global_grid(std::min(E, n_patches)), kGThreads, 0, st>>>(a);
+  WV_CUDA_TRY(cudaFuncSetAttribute(ba_global_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBuildSmem));
+  ba_global_kernel<true><<<global_grid(std::min(E, n_patches)), kGThreads, kBuildSmem, st>>>(a);
   WV_LAUNCH_CHECK();
   return WV_OK;
 }

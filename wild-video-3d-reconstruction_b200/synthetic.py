@@ -95,9 +95,26 @@ def global_edges(n, M):
     return ii, jj, kk
 
 
+def config4_edges(n, M, span=12, loop_frac=0.02, seed=3):
+    """every patch -> the frames within +-span of its source frame (25 per patch away from the ends),
+    plus loop_frac extra edges to frames drawn uniformly from [0, n).  Patch-major."""
+    rng = np.random.default_rng(seed)
+    src = np.repeat(np.arange(n, dtype=np.int64), M)                      # source frame of every patch
+    off = np.arange(-span, span + 1, dtype=np.int64)
+    jj = src[:, None] + off[None]
+    kk = np.broadcast_to(np.arange(n * M, dtype=np.int64)[:, None], jj.shape)
+    ok = (jj >= 0) & (jj < n)
+    jj, kk = jj[ok], kk[ok]
+    nl = int(loop_frac * len(kk))
+    kl = rng.integers(0, n * M, nl).astype(np.int64)
+    jl = rng.integers(0, n, nl).astype(np.int64)
+    kk = np.concatenate([kk, kl]); jj = np.concatenate([jj, jl])
+    return kk // M, jj, kk
+
+
 # ----------------------------------------------------------------------------- BA scene
 def make_ba_scene(seed=0, n=10, M=96, edges="all", ht=96, wd=128, fx=110.0, n_buffer=None,
-                  pose_noise=0.02, depth_noise=0.1, pix_noise=0.5, first_frame=0, lifetime=13, removal=22):
+                  pose_noise=0.02, depth_noise=0.1, pix_noise=0.5, first_frame=0, lifetime=13, removal=22, loop_frac=0.02):
     """Synthetic window: forward motion 0.1 m/frame + 1 deg/frame yaw, points at depth U(2,8) m.
 
     Returns a dict of float32/int64 numpy arrays with the layouts cuda_ba.forward takes:
@@ -129,6 +146,8 @@ def make_ba_scene(seed=0, n=10, M=96, edges="all", ht=96, wd=128, fx=110.0, n_bu
         ii, jj, kk = all_pairs_edges(n, M)
     elif edges == "global":
         ii, jj, kk = global_edges(n, M)
+    elif edges == "config4":
+        ii, jj, kk = config4_edges(n, M, loop_frac=loop_frac)
     else:
         ii, jj, kk = tracker_edges(n, M, lifetime, removal)
     # true projections of the patch centres
