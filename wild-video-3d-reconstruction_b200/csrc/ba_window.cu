@@ -94,6 +94,7 @@ __device__ __forceinline__ void scatter_row(float* S, float* y, int fi, int fj, 
 }
 
 __global__ void __launch_bounds__(kBaThreads, 1) ba_window_kernel(BAArgs a) {
+  __shared__ int fail_s;
   extern __shared__ float sm[];
   cg::grid_group grid = cg::this_grid();
   const int N = a.N, n6 = 6 * N, nT = (n6 * (n6 + 1)) >> 1, nS = nT + n6;
@@ -258,14 +259,13 @@ __global__ void __launch_bounds__(kBaThreads, 1) ba_window_kernel(BAArgs a) {
       }
       grid.sync();
       // ---------------------------------------------------------------- phase C: damped Cholesky (every CTA)
-      // Right-looking LL^T on the (n6+1) x n6 trapezoid [S ; y^T] in shared memory: carrying the right-hand side as an
-      // extra row makes the forward substitution L z = y fall out of the factorisation.  Step j reads column j (left
-      // UNSCALED for the whole step, so one barrier per step suffices), updates the columns to its right, and files the
-      // scaled column L_ij in the unused upper triangle A[j][i] for the back substitution.  Four threads per row.
-      const int ld = n6 + 1;
+      // Blocked right-looking LL^T on the (n6+1) x n6 trapezoid [S ; y^T] in shared memory, one 6-column pose block per step
+      // (N steps of 3 barriers instead of 6N column steps): carrying the right-hand side as an extra row makes the forward
+      // substitution L z = y fall out of the factorisation.  L overwrites the lower triangle; dg holds 1 / L_cc.
+      const int ld = n6 + 1;           // odd: column walks are bank-conflict free
       float* A = sm;                   // [n6 + 1][ld]
-      float* dg = A + (n6 + 1) * ld;   // [n6]  diagonal of L
-      float* bx = dg + n6;             // [n6]  z, then the solution
+      float* dg = A + (n6 + 1) * ld;   // [n6]  reciprocal diagonal of L
+      float* bx = dg + n6;             // [n6]  the solution dX
       for (int t = threadIdx.x; t < n6 * n6; t += blockDim.x) {
         const int rr = t / n6, cc = t - rr * n6;
         if (cc <= rr) {
@@ -275,35 +275,90 @@ __global__ void __launch_bounds__(kBaThreads, 1) ba_window_kernel(BAArgs a) {
         }
       }
       for (int t = threadIdx.x; t < n6; t += blockDim.x) A[n6 * ld + t] = a.Sfull[nT + t];
-      const int q4 = threadIdx.x & 3, r4 = threadIdx.x >> 2;
-      for (int j = 0; j < n6; j++) {
+      if (threadIdx.x == 0) fail_s = 0;
+      __syncthreads();
+      const int ti = threadIdx.x >> 4, tk = threadIdx.x & 15;  // 16 x 16 threads over (row, column) of the trailing update
+      for (int J = 0; J < N; J++) {
+        const int c0 = 6 * J;
+        if (threadIdx.x == 0) {  // (a) the 6x6 diagonal block, in registers
+          float Lb[6][6];
+#pragma unroll
+          for (int r = 0; r < 6; r++)
+#pragma unroll
+            for (int c = 0; c <= r; c++) Lb[r][c] = A[(c0 + r) * ld + c0 + c];
+          bool bad = false;
+#pragma unroll
+          for (int c = 0; c < 6; c++) {
+            float d = Lb[c][c];
+#pragma unroll
+            for (int m = 0; m < c; m++) d = fmaf(-Lb[c][m], Lb[c][m], d);
+            if (!(d > 0.f)) bad = true;
+            const float dj = sqrtf(d), inv = 1.f / dj;
+            Lb[c][c] = dj;
+            dg[c0 + c] = inv;
+#pragma unroll
+            for (int r = c + 1; r < 6; r++) {
+              float v = Lb[r][c];
+#pragma unroll
+              for (int m = 0; m < c; m++) v = fmaf(-Lb[r][m], Lb[c][m], v);
+              Lb[r][c] = v * inv;
+            }
+          }
+          if (bad) fail_s = 1;
+#pragma unroll
+          for (int r = 0; r < 6; r++)
+#pragma unroll
+            for (int c = 0; c <= r; c++) A[(c0 + r) * ld + c0 + c] = Lb[r][c];
+        }
         __syncthreads();
-        const float d = A[j * ld + j];
-        if (!(d > 0.f)) { failed = true; break; }  // same value in every thread of every CTA
-        const float dj = sqrtf(d), rd = 1.f / d;
-        for (int i = j + 1 + r4; i <= n6; i += kBaThreads / 4) {
-          const float aij = A[i * ld + j], f = aij * rd;
+        if (fail_s) break;  // same value in every thread of every CTA
+        // (b) panel: rows below the block (and the rhs row) x L_JJ^-T, one thread per row
+        for (int i = c0 + 6 + threadIdx.x; i <= n6; i += blockDim.x) {
+          float x[6];
+#pragma unroll
+          for (int c = 0; c < 6; c++) x[c] = A[i * ld + c0 + c];
+#pragma unroll
+          for (int c = 0; c < 6; c++) {
+#pragma unroll
+            for (int m = 0; m < c; m++) x[c] = fmaf(-x[m], A[(c0 + c) * ld + c0 + m], x[c]);
+            x[c] *= dg[c0 + c];
+          }
+#pragma unroll
+          for (int c = 0; c < 6; c++) A[i * ld + c0 + c] = x[c];
+        }
+        __syncthreads();
+        // (c) trailing update A_ik -= L_i,J . L_k,J for k > block, i >= k (i runs over the rhs row too)
+        const int first = c0 + 6;
+        for (int i = first + ti; i <= n6; i += 16) {
+          float li[6];
+#pragma unroll
+          for (int c = 0; c < 6; c++) li[c] = A[i * ld + c0 + c];
           const int kend = i < n6 ? i : n6 - 1;
-          for (int k = j + 1 + q4; k <= kend; k += 4) A[i * ld + k] = fmaf(-f, A[k * ld + j], A[i * ld + k]);
-          if (q4 == 0) {
-            if (i < n6) A[j * ld + i] = aij / dj;  // L_ij, filed in the upper triangle
-            else bx[j] = aij / dj;                 // z_j
+          for (int k = first + tk; k <= kend; k += 16) {
+            float acc = A[i * ld + k];
+#pragma unroll
+            for (int c = 0; c < 6; c++) acc = fmaf(-li[c], A[k * ld + c0 + c], acc);
+            A[i * ld + k] = acc;
           }
         }
-        if (threadIdx.x == 0) dg[j] = dj;
+        __syncthreads();
       }
-      __syncthreads();
+      failed = fail_s != 0;
       if (failed) {
         if (blockIdx.x == 0 && threadIdx.x == 0) set_status(a.status, WV_STATUS_NOT_SPD);
         break;
       }
-      if (warp == 0) {  // L^T x = z, column-oriented, one warp; L_ik (k < i) is at A[k][i]
+      if (warp == 0) {  // L^T x = z: z (row n6) lives in registers, lane l owns entries l, l+32, l+64; row i of L is read ahead
+        float z0 = lane < n6 ? A[n6 * ld + lane] : 0.f, z1 = lane + 32 < n6 ? A[n6 * ld + lane + 32] : 0.f,
+              z2 = lane + 64 < n6 ? A[n6 * ld + lane + 64] : 0.f;
+#pragma unroll 4
         for (int i = n6 - 1; i >= 0; i--) {
-          const float x = bx[i] / dg[i];
-          __syncwarp();
-          if (lane == 0) bx[i] = x;
-          for (int k = lane; k < i; k += 32) bx[k] = fmaf(-A[k * ld + i], x, bx[k]);
-          __syncwarp();
+          const float* Li = A + i * ld;
+          const float l0 = lane < i ? Li[lane] : 0.f, l1 = lane + 32 < i ? Li[lane + 32] : 0.f, l2 = lane + 64 < i ? Li[lane + 64] : 0.f;
+          const float zi = __shfl_sync(0xffffffffu, i < 32 ? z0 : (i < 64 ? z1 : z2), i & 31);
+          const float x = zi * dg[i];
+          if (lane == (i & 31)) bx[i] = x;
+          z0 = fmaf(-l0, x, z0); z1 = fmaf(-l1, x, z1); z2 = fmaf(-l2, x, z2);
         }
       }
       __syncthreads();
