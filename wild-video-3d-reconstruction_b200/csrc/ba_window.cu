@@ -94,7 +94,6 @@ __device__ __forceinline__ void scatter_row(float* S, float* y, int fi, int fj, 
 }
 
 __global__ void __launch_bounds__(kBaThreads, 1) ba_window_kernel(BAArgs a) {
-  __shared__ int fail_s;
   extern __shared__ float sm[];
   cg::grid_group grid = cg::this_grid();
   const int N = a.N, n6 = 6 * N, nT = (n6 * (n6 + 1)) >> 1, nS = nT + n6;
@@ -246,72 +245,70 @@ __global__ void __launch_bounds__(kBaThreads, 1) ba_window_kernel(BAArgs a) {
         a.partial[(size_t)blockIdx.x * nS + t] = s;
       }
       grid.sync();
-      for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < nS; t += gridDim.x * blockDim.x) {
-        // fixed order, four independent chains (loads in flight together), combined in a fixed order
-        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-        int c = 0;
-        for (; c + 4 <= (int)gridDim.x; c += 4) {
-          s0 += a.partial[(size_t)c * nS + t]; s1 += a.partial[(size_t)(c + 1) * nS + t];
-          s2 += a.partial[(size_t)(c + 2) * nS + t]; s3 += a.partial[(size_t)(c + 3) * nS + t];
+      {
+        // cross-CTA sum in a fixed order: 16 lanes per element, lane s adds partials s, s+16, ... in order, then a fixed
+        // xor-shuffle tree over the 16 lanes (bitwise reproducible; 37 888 threads share the 1 890 x 148 loads)
+        const int g = blockIdx.x * blockDim.x + threadIdx.x, grp = g >> 4, sub = g & 15;
+        const int ngrp = (gridDim.x * blockDim.x) >> 4;
+        for (int base = 0; base < nS; base += ngrp) {
+          const int t = base + grp;
+          float s = 0.f;
+          if (t < nS)
+            for (int c = sub; c < (int)gridDim.x; c += 16) s += a.partial[(size_t)c * nS + t];
+#pragma unroll
+          for (int o = 8; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+          if (t < nS && sub == 0) a.Sfull[t] = s;
         }
-        for (; c < (int)gridDim.x; c++) s0 += a.partial[(size_t)c * nS + t];
-        a.Sfull[t] = (s0 + s1) + (s2 + s3);
       }
       grid.sync();
       // ---------------------------------------------------------------- phase C: damped Cholesky (every CTA)
       // Blocked right-looking LL^T on the (n6+1) x n6 trapezoid [S ; y^T] in shared memory, one 6-column pose block per step
-      // (N steps of 3 barriers instead of 6N column steps): carrying the right-hand side as an extra row makes the forward
+      // (N steps of 2 barriers instead of 6N column steps): carrying the right-hand side as an extra row makes the forward
       // substitution L z = y fall out of the factorisation.  L overwrites the lower triangle; dg holds 1 / L_cc.
       const int ld = n6 + 1;           // odd: column walks are bank-conflict free
       float* A = sm;                   // [n6 + 1][ld]
       float* dg = A + (n6 + 1) * ld;   // [n6]  reciprocal diagonal of L
       float* bx = dg + n6;             // [n6]  the solution dX
-      for (int t = threadIdx.x; t < n6 * n6; t += blockDim.x) {
-        const int rr = t / n6, cc = t - rr * n6;
-        if (cc <= rr) {
-          float s = a.Sfull[tri(rr, cc)];
-          if (rr == cc) s = s + (s * 1e-4f + 1.0f);  // S += I * (1e-4 * S + 1.0), ba_cuda.cu:517-518
-          A[rr * ld + cc] = s;
-        }
+      for (int t = threadIdx.x; t < nT; t += blockDim.x) {  // packed lower triangle, coalesced
+        int rr = (int)((sqrtf(8.f * (float)t + 1.f) - 1.f) * 0.5f);
+        while (tri(rr + 1, 0) <= t) rr++;
+        while (tri(rr, 0) > t) rr--;
+        const int cc = t - tri(rr, 0);
+        float s = a.Sfull[t];
+        if (rr == cc) s = s + (s * 1e-4f + 1.0f);  // S += I * (1e-4 * S + 1.0), ba_cuda.cu:517-518
+        A[rr * ld + cc] = s;
       }
       for (int t = threadIdx.x; t < n6; t += blockDim.x) A[n6 * ld + t] = a.Sfull[nT + t];
-      if (threadIdx.x == 0) fail_s = 0;
       __syncthreads();
       const int ti = threadIdx.x >> 4, tk = threadIdx.x & 15;  // 16 x 16 threads over (row, column) of the trailing update
       for (int J = 0; J < N; J++) {
         const int c0 = 6 * J;
-        if (threadIdx.x == 0) {  // (a) the 6x6 diagonal block, in registers
-          float Lb[6][6];
+        // (a) the 6x6 diagonal block: EVERY thread factorises it in its own registers (same inputs, same arithmetic), so the
+        // panel solve below needs no barrier after it; thread 0 files the result once the panel no longer reads the original
+        float Lb[6][6], inv[6];
 #pragma unroll
-          for (int r = 0; r < 6; r++)
+        for (int r = 0; r < 6; r++)
 #pragma unroll
-            for (int c = 0; c <= r; c++) Lb[r][c] = A[(c0 + r) * ld + c0 + c];
-          bool bad = false;
+          for (int c = 0; c <= r; c++) Lb[r][c] = A[(c0 + r) * ld + c0 + c];
+        bool bad = false;
 #pragma unroll
-          for (int c = 0; c < 6; c++) {
-            float d = Lb[c][c];
+        for (int c = 0; c < 6; c++) {
+          float d = Lb[c][c];
 #pragma unroll
-            for (int m = 0; m < c; m++) d = fmaf(-Lb[c][m], Lb[c][m], d);
-            if (!(d > 0.f)) bad = true;
-            const float dj = sqrtf(d), inv = 1.f / dj;
-            Lb[c][c] = dj;
-            dg[c0 + c] = inv;
+          for (int m = 0; m < c; m++) d = fmaf(-Lb[c][m], Lb[c][m], d);
+          if (!(d > 0.f)) bad = true;
+          const float dj = sqrtf(d);
+          inv[c] = 1.f / dj;
+          Lb[c][c] = dj;
 #pragma unroll
-            for (int r = c + 1; r < 6; r++) {
-              float v = Lb[r][c];
+          for (int r = c + 1; r < 6; r++) {
+            float v = Lb[r][c];
 #pragma unroll
-              for (int m = 0; m < c; m++) v = fmaf(-Lb[r][m], Lb[c][m], v);
-              Lb[r][c] = v * inv;
-            }
+            for (int m = 0; m < c; m++) v = fmaf(-Lb[r][m], Lb[c][m], v);
+            Lb[r][c] = v * inv[c];
           }
-          if (bad) fail_s = 1;
-#pragma unroll
-          for (int r = 0; r < 6; r++)
-#pragma unroll
-            for (int c = 0; c <= r; c++) A[(c0 + r) * ld + c0 + c] = Lb[r][c];
         }
-        __syncthreads();
-        if (fail_s) break;  // same value in every thread of every CTA
+        if (bad) { failed = true; break; }  // same value in every thread of every CTA
         // (b) panel: rows below the block (and the rhs row) x L_JJ^-T, one thread per row
         for (int i = c0 + 6 + threadIdx.x; i <= n6; i += blockDim.x) {
           float x[6];
@@ -320,13 +317,21 @@ __global__ void __launch_bounds__(kBaThreads, 1) ba_window_kernel(BAArgs a) {
 #pragma unroll
           for (int c = 0; c < 6; c++) {
 #pragma unroll
-            for (int m = 0; m < c; m++) x[c] = fmaf(-x[m], A[(c0 + c) * ld + c0 + m], x[c]);
-            x[c] *= dg[c0 + c];
+            for (int m = 0; m < c; m++) x[c] = fmaf(-x[m], Lb[c][m], x[c]);
+            x[c] *= inv[c];
           }
 #pragma unroll
           for (int c = 0; c < 6; c++) A[i * ld + c0 + c] = x[c];
         }
         __syncthreads();
+        if (threadIdx.x == 0) {
+#pragma unroll
+          for (int r = 0; r < 6; r++) {
+#pragma unroll
+            for (int c = 0; c <= r; c++) A[(c0 + r) * ld + c0 + c] = Lb[r][c];
+            dg[c0 + r] = inv[r];
+          }
+        }
         // (c) trailing update A_ik -= L_i,J . L_k,J for k > block, i >= k (i runs over the rhs row too)
         const int first = c0 + 6;
         for (int i = first + ti; i <= n6; i += 16) {
@@ -343,7 +348,6 @@ __global__ void __launch_bounds__(kBaThreads, 1) ba_window_kernel(BAArgs a) {
         }
         __syncthreads();
       }
-      failed = fail_s != 0;
       if (failed) {
         if (blockIdx.x == 0 && threadIdx.x == 0) set_status(a.status, WV_STATUS_NOT_SPD);
         break;
