@@ -18,6 +18,7 @@ def t(fm, co, n=10):
         a.record(); cc.forward(g, fm, co, ii, jj, 3); b.record(); torch.cuda.synchronize()
         if i >= 3: ts.append(a.elapsed_time(b))
     return np.median(ts)
-for dbg in sys.argv[1:]:
-    os.environ["WVB200_CORR_DBG"] = dbg
-    print("dbg", dbg, "L0 %.3f ms  L1 %.3f ms" % (t(f0, c0), t(f1, c1)), flush=True)
+# usage: python tools/corrtime.py [generic]      (generic: force the any-shape kernel via WVB200_CORR_TILED=0)
+if len(sys.argv) > 1 and sys.argv[1] == "generic":
+    os.environ["WVB200_CORR_TILED"] = "0"
+print("L0 %.4f ms  L1 %.4f ms" % (t(f0, c0), t(f1, c1)), flush=True)
