@@ -533,3 +533,45 @@ def test_global_ba_not_spd_raises(syn):
         run_ba(s, 1, int(s["t1"]), 2)
     s2 = syn.make_ba_scene(seed=11, n=40, M=8, edges="tracker")
     run_ba(s2, 1, int(s2["t1"]), 1)  # the extension still works afterwards
+
+
+# ------------------------------------------------------------------------------------------------- corr at full size
+@pytest.mark.parametrize("M", [96, 384])
+def test_corr_full_size_properties(syn, M):
+    """BASELINE configs[1] size (M = 96, E = 45 312) and default.yaml's M = 384 (E = 181 248), both pyramid levels, fp16 maps:
+    tiled == generic kernel to one fp16 rounding; a 256-edge sample == fp64 oracle; and size-independent exact properties:
+    scaling the map by 2 doubles the output bit for bit (where the fp16 result is a normal number), permuting the edges permutes the output bit for bit, edges whose
+    window lies wholly outside the map give exact zeros."""
+    cc, _ = pkg().native_modules()
+    w = syn.make_corr_workload(seed=21, M=M)
+    rng = np.random.default_rng(5)
+    E = w["coords"].shape[1]
+    g = dev(w["gmap"], torch.float16)
+    ii, jj = dev(w["ii1"]), dev(w["jj1"])
+    perm = torch.from_numpy(rng.permutation(E)).cuda()
+    for lvl, (fm, div) in enumerate(((w["fmap0"], 1.0), (w["fmap1"], 4.0))):
+        f = dev(fm, torch.float16)
+        co = dev((w["coords"] / div).astype(np.float32))
+        H, W = fm.shape[3], fm.shape[4]
+        with _tiled(True):
+            out, = cc.forward(g, f, co, ii, jj, 3)
+            out2, = cc.forward(g, f * 2, co, ii, jj, 3)
+            outp, = cc.forward(g, f, co[:, perm].contiguous(), ii[perm].contiguous(), jj[perm].contiguous(), 3)
+        with _tiled(False):
+            gen, = cc.forward(g, f, co, ii, jj, 3)
+        torch.cuda.synchronize()
+        scale = max(1.0, out.float().abs().max().item())
+        assert (out.float() - gen.float()).abs().max().item() <= 2.0 ** -9 * scale, f"level {lvl}"
+        normal = out.abs() >= 2.0 ** -13  # fp16 results in the subnormal range round on a fixed grid: scaling is exact only above it
+        assert torch.equal(out2[normal], (out * 2)[normal]) and normal.float().mean().item() > 0.8, f"level {lvl}: linearity"
+        assert (out2.float() - 2 * out.float()).abs().max().item() <= 2.0 ** -23, f"level {lvl}: linearity (subnormal results)"
+        assert torch.equal(outp, out[:, perm]), f"level {lvl}: permutation"
+        c = co[0]  # [E,2,3,3]
+        outside = ((c[:, 0] < -5).all(-1).all(-1) | (c[:, 0] > W + 4).all(-1).all(-1) | (c[:, 1] < -5).all(-1).all(-1) | (c[:, 1] > H + 4).all(-1).all(-1))
+        assert outside.any() and out[0, outside].abs().max().item() == 0.0, f"level {lvl}: out-of-map edges"
+        pick = np.sort(rng.choice(E, 256, replace=False))
+        g16 = torch.from_numpy(w["gmap"]).half().float().numpy()
+        f16 = torch.from_numpy(fm).half().float().numpy()
+        truth = oracle.corr_forward(g16, f16, (w["coords"][:, pick] / div).astype(np.float32), w["ii1"][pick], w["jj1"][pick], 3, mode=oracle.F64)
+        got = out[:, torch.from_numpy(pick).cuda()].float().cpu().numpy()
+        assert np.abs(got - truth).max() <= 2.0 ** -10 * max(1.0, np.abs(truth).max()), f"level {lvl}: oracle sample"

@@ -112,3 +112,116 @@ def test_two_ranks_gloo_replicas():
     assert all(o[2] == 2.0 for o in out)                    # max over ranks
     assert out[0][3] != out[1][3]                           # different clips per rank
     assert out[0][4] + out[1][4] == list(range(5))          # shards partition the clips
+
+
+# ----------------------------------------------------------------------------------------------------------
+# fastba.BA_sharded host logic under gloo (world_size 2): the collective placement, shard arguments and iteration loop, with a
+# CPU stand-in for the four cuda_ba.global_* pieces (a linear toy problem with the same build -> solve -> dz -> retract algebra).
+# ----------------------------------------------------------------------------------------------------------
+class _ToyGlobalBA:
+    def __init__(self):
+        self.calls = []
+
+    @staticmethod
+    def _patch_terms(k, depth, n6):
+        import torch
+        g = torch.Generator().manual_seed(int(k) + 17)
+        e = torch.randn(n6, generator=g, dtype=torch.float64) * 0.3
+        b = torch.randn(n6, generator=g, dtype=torch.float64) * 0.1
+        C = 1.0 + 0.1 * float(depth)           # depends on the current state: iteration 2 sees iteration 1's update
+        u = 0.5 * float(depth) - 0.2
+        return e, b, C, u
+
+    def _shard(self, kk, shard, nshards):
+        import torch
+        kx = torch.unique(kk)                   # sorted
+        lo, hi = len(kx) * shard // nshards, len(kx) * (shard + 1) // nshards
+        return kx, lo, hi
+
+    def global_build(self, poses, patches, intr, target, weight, lmbda, ii, jj, kk, t0, t1, shard, nshards, build_plan, est, mu):
+        import torch
+        self.calls.append(("build", shard, nshards, bool(build_plan)))
+        n6 = 6 * (t1 - t0)
+        S = torch.zeros(n6, n6, dtype=torch.float64); y = torch.zeros(n6, dtype=torch.float64)
+        kx, lo, hi = self._shard(kk, shard, nshards)
+        for r in range(lo, hi):
+            e, b, C, u = self._patch_terms(kx[r], patches[kx[r], 2, 0, 0], n6)
+            q = 1.0 / (C + float(lmbda[0]))
+            S += torch.outer(b, b) + torch.outer(e, e) * (1.0 - q * 0.5)
+            y += b * 0.3 - q * u * e
+        return torch.cat([torch.tril(S).reshape(-1), y]).float()
+
+    def global_solve(self, Sy, n_free):
+        import torch
+        n6 = 6 * n_free
+        S = Sy[: n6 * n6].view(n6, n6).double(); y = Sy[n6 * n6:].double()
+        S = torch.tril(S) + torch.tril(S, -1).T
+        S = S + torch.diag(torch.diagonal(S) * 1e-4 + 1.0)
+        return torch.cholesky_solve(y[:, None], torch.linalg.cholesky(S)).view(n_free, 6).float()
+
+    def global_dz(self, poses, patches, intr, target, weight, lmbda, ii, jj, kk, t0, t1, shard, nshards, dX, est, mu):
+        import torch
+        self.calls.append(("dz", shard, nshards))
+        n6 = 6 * (t1 - t0)
+        kx, lo, hi = self._shard(kk, shard, nshards)
+        dZ = torch.zeros(min(ii.numel(), patches.shape[0]))
+        for r in range(lo, hi):
+            e, b, C, u = self._patch_terms(kx[r], patches[kx[r], 2, 0, 0], n6)
+            dZ[r] = float((u - (e * dX.double().view(-1)).sum()) / (C + float(lmbda[0])))
+        return dZ
+
+    def global_retract(self, poses, patches, E, t0, t1, dX, dZ):
+        import torch
+        kx = self._kx
+        poses[t0:t1, :6] += dX
+        patches[kx, 2] += dZ[: len(kx), None, None]
+
+
+def _sharded_worker(rank, world, port, q):
+    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    import sys
+    sys.path.insert(0, ROOT)
+    import torch
+    pkg = importlib.import_module(PKG)
+    if world > 1:
+        pkg.dist.init("gloo")
+    ba = importlib.import_module(PKG + ".fastba.ba")
+    toy = _ToyGlobalBA()
+    ba.cuda_ba = toy                                   # the CPU stand-in; the product path is the CUDA extension
+    n, M = 9, 5
+    ii, jj, kk = pkg.synthetic.global_edges(n, M)
+    ii, jj, kk = (torch.from_numpy(x) for x in (ii, jj, kk))
+    toy._kx = torch.unique(kk)
+    g = torch.Generator().manual_seed(3)
+    poses = torch.randn(n, 7, generator=g); patches = torch.rand(n * M, 3, 3, 3, generator=g) + 0.5
+    E = ii.numel()
+    ba.BA_sharded(poses, patches, torch.ones(n, 4), torch.zeros(E, 2), torch.ones(E, 2), torch.tensor([1e-4]), ii, jj, kk, 1, n, 2)
+    q.put((rank, poses.numpy().copy(), patches.numpy().copy(), toy.calls))
+    if world > 1:
+        pkg.dist.finalize()
+
+
+def test_ba_sharded_host_logic_gloo_two_ranks():
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    results = {}
+    for world in (1, 2):
+        with socket.socket() as s:
+            s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]
+        q = ctx.Queue()
+        ps = [ctx.Process(target=_sharded_worker, args=(r, world, port, q)) for r in range(world)]
+        [p.start() for p in ps]
+        results[world] = sorted((q.get(timeout=180) for _ in ps), key=lambda o: o[0])
+        [p.join(60) for p in ps]
+    one, (r0, r1) = results[1][0], results[2]
+    # both ranks end with the same state, bit for bit (same reduced system after the allreduce, same solve, same retraction)
+    assert np.array_equal(r0[1], r1[1]) and np.array_equal(r0[2], r1[2])
+    # and it is the one-process answer up to the summation order of the allreduce
+    np.testing.assert_allclose(r0[1], one[1], rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(r0[2], one[2], rtol=1e-5, atol=1e-6)
+    assert not np.array_equal(one[1], results[1][0][1] * 0)  # something moved
+    # shard arguments and the plan flag: (rank, world) on every call, plan built on the first iteration only
+    for rank, res in enumerate((r0, r1)):
+        builds = [c for c in res[3] if c[0] == "build"]
+        assert [b[1:3] for b in builds] == [(rank, 2), (rank, 2)] and [b[3] for b in builds] == [True, False]
+        assert [c[1:] for c in res[3] if c[0] == "dz"] == [(rank, 2), (rank, 2)]
