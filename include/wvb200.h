@@ -43,7 +43,8 @@ enum {
 enum {
   WV_STATUS_BAD_INDEX = 1, /* an ii/jj/kk entry was outside its tensor; that edge was skipped */
   WV_STATUS_NOT_SPD = 2,   /* Cholesky met a non-positive pivot (reference: torch::linalg::cholesky throws, ba_cuda.cu:521) */
-  WV_STATUS_TOO_DENSE = 4  /* global BA: one patch had more than 128 free-pose observations; the excess was dropped */
+  WV_STATUS_TOO_DENSE = 4, /* global BA: one patch had more than 128 free-pose observations; the excess was dropped */
+  WV_STATUS_STALE_PLAN = 8 /* wv_ba_forward_planned: the plan in the workspace was not built for this kk; the result is invalid */
 };
 
 const char* wv_strerror(int code);
@@ -115,7 +116,9 @@ int wv_ba_forward(float* poses, float* patches, const float* intrinsics, const f
 /* wv_ba_forward when `workspace` already holds the edge plan that wv_neighbors(kk, jj, E, n_groups = plan_groups, ...)
  * built for the SAME kk / jj (the tracker calls neighbors and BA on one edge list per update(), dpvo/net.py:81 then
  * dpvo/dpvo.py:733): skips the second plan build.  workspace_bytes >= wv_ba_workspace_bytes(E, plan_groups, t1 - t0);
- * kk values must be < plan_groups.  ii / jj are range-checked by the BA kernel itself. */
+ * kk values must be < plan_groups.  ii / jj are range-checked by the BA kernel itself, every edge's kk is verified against the
+ * plan (mismatch -> WV_STATUS_STALE_PLAN: the call's result is invalid), and patch ids >= n_patches are flagged
+ * (WV_STATUS_BAD_INDEX) and skipped. */
 int wv_ba_forward_planned(float* poses, float* patches, const float* intrinsics, const float* target,
                           const float* weight, const float* lmbda, const int64_t* ii, const int64_t* jj,
                           const int64_t* kk, int64_t E, int64_t n_poses, int64_t n_patches, int P, int t0,

@@ -575,3 +575,45 @@ def test_corr_full_size_properties(syn, M):
         truth = oracle.corr_forward(g16, f16, (w["coords"][:, pick] / div).astype(np.float32), w["ii1"][pick], w["jj1"][pick], 3, mode=oracle.F64)
         got = out[:, torch.from_numpy(pick).cuda()].float().cpu().numpy()
         assert np.abs(got - truth).max() <= 2.0 ** -10 * max(1.0, np.abs(truth).max()), f"level {lvl}: oracle sample"
+
+
+def test_planned_ba_detects_a_plan_built_for_other_edges(syn):
+    """C ABI: wv_ba_forward_planned on a workspace whose plan belongs to a different kk must say so (WV_STATUS_STALE_PLAN),
+    and kk values beyond the patch buffer on a reused plan must be flagged, not dereferenced"""
+    lib = pkg().capi()
+    s = syn.make_ba_scene(seed=2, n=20, M=16, edges="tracker")
+    t1 = int(s["t1"]); t0 = t1 - 10
+    D = {k: dev(s[k]) for k in ("poses", "patches", "intrinsics", "target", "weight", "lmbda", "ii", "jj", "kk")}
+    E, groups = D["kk"].numel(), 1 << 16
+    n_poses, n_patches = D["poses"].shape[0], D["patches"].shape[0]
+    lib.wv_ba_workspace_bytes.restype = ctypes.c_size_t
+    lib.wv_ba_workspace_bytes.argtypes = [ctypes.c_int64, ctypes.c_int64, ctypes.c_int]
+    wsb = lib.wv_ba_workspace_bytes(E, groups, t1 - t0)
+    ws = torch.empty(wsb, dtype=torch.uint8, device="cuda")
+    status = torch.zeros(1, dtype=torch.int32, device="cuda")
+    ix, jx = torch.empty_like(D["kk"]), torch.empty_like(D["kk"])
+    P = ctypes.c_void_p
+
+    def planned(kk_plan, kk_ba, n_patches_arg):
+        status.zero_()
+        rc = lib.wv_neighbors(P(kk_plan.data_ptr()), P(D["jj"].data_ptr()), ctypes.c_int64(E), ctypes.c_int64(groups), P(ix.data_ptr()),
+                              P(jx.data_ptr()), P(ws.data_ptr()), ctypes.c_size_t(wsb), P(status.data_ptr()), None)
+        assert rc == 0
+        poses, patches = D["poses"].clone(), D["patches"].clone()
+        rc = lib.wv_ba_forward_planned(P(poses.data_ptr()), P(patches.data_ptr()), P(D["intrinsics"].data_ptr()), P(D["target"].data_ptr()),
+                                       P(D["weight"].data_ptr()), P(D["lmbda"].data_ptr()), P(D["ii"].data_ptr()), P(D["jj"].data_ptr()),
+                                       P(kk_ba.data_ptr()), ctypes.c_int64(E), ctypes.c_int64(n_poses), ctypes.c_int64(n_patches_arg),
+                                       ctypes.c_int(3), ctypes.c_int(t0), ctypes.c_int(t1), ctypes.c_int(2), None, ctypes.c_float(2.0),
+                                       P(ws.data_ptr()), ctypes.c_size_t(wsb), ctypes.c_int64(groups), P(status.data_ptr()), None)
+        assert rc == 0
+        torch.cuda.synchronize()
+        return int(status.item()), poses, patches
+
+    st, poses, _ = planned(D["kk"], D["kk"], n_patches)
+    assert st == 0 and not torch.equal(poses, D["poses"])
+    other = D["kk"].clone(); other[::7] = (other[::7] + 3) % n_patches
+    st, _, _ = planned(D["kk"], other, n_patches)
+    assert st & 8                      # WV_STATUS_STALE_PLAN
+    st, _, patches = planned(D["kk"], D["kk"], n_patches // 2)   # half the patch buffer: ids beyond it are flagged ...
+    assert st & 1                      # WV_STATUS_BAD_INDEX
+    assert torch.equal(patches[n_patches // 2:], D["patches"][n_patches // 2:])  # ... and never touched

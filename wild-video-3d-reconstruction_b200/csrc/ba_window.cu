@@ -37,7 +37,8 @@ struct BAArgs {
   const int64_t* ii; const int64_t* jj;
   const float* patches_est; float mu;
   int P, t0, N, iterations;
-  int n_poses;
+  int n_poses, n_patches;
+  const int64_t* kk_check;  // non-null when the plan was built by an earlier call (wv_neighbors): every edge is verified against it
   Plan p;
   float* partial;  // [grid][nS]
   float* Sfull;    // [nS]
@@ -116,7 +117,13 @@ __global__ void __launch_bounds__(kBaThreads, 1) ba_window_kernel(BAArgs a) {
 
     // ------------------------------------------------------------------ phase A: edges -> tables
     for (int r = r_lo + warp; r < r_hi; r += kBaWarps) {
-      const int id = a.p.kx[r], off = a.p.seg_off[r], n = a.p.seg_off[r + 1] - off;
+      int id = a.p.kx[r];
+      const int off = a.p.seg_off[r];
+      int n = a.p.seg_off[r + 1] - off;
+      if (id >= a.n_patches) {  // only possible on a reused plan (its ids were checked against the plan's group count)
+        if (lane == 0) set_status(a.status, WV_STATUS_BAD_INDEX);
+        id = 0; n = 0;
+      }
       const float* pc = a.patches + (size_t)id * 3 * PP;
       const float px = pc[ctr], py = pc[PP + ctr], pd = pc[2 * PP + ctr];
       for (int c = lane; c < n6; c += 32) myE[c] = 0.f;
@@ -129,6 +136,7 @@ __global__ void __launch_bounds__(kBaThreads, 1) ba_window_kernel(BAArgs a) {
         if (act) {  // a plan built by neighbors() has not looked at ii / jj: range-check them here
           const int64_t iv = a.ii[e], jv = a.jj[e];
           if (iv < 0 || iv >= a.n_poses || jv < 0 || jv >= a.n_poses) { set_status(a.status, WV_STATUS_BAD_INDEX); act = false; }
+          else if (a.kk_check && a.kk_check[e] != (int64_t)id) { set_status(a.status, WV_STATUS_STALE_PLAN); act = false; }
           else { ix = (int)iv; jx = (int)jv; }
         }
         const int fi = ix - a.t0, fj = jx - a.t0;
@@ -372,6 +380,7 @@ __global__ void __launch_bounds__(kBaThreads, 1) ba_window_kernel(BAArgs a) {
         float s = 0.f;
         for (int c = 0; c < n6; c++) s += Ek[c] * bx[c];
         const float dz = a.qk[r] * (a.uk[r] - s);
+        if (a.p.kx[r] >= a.n_patches) continue;
         float* pdz = a.patches + (size_t)a.p.kx[r] * 3 * PP + 2 * PP;
         float dd = pdz[0] + dz;
         dd = (dd > 20.f) ? 1.0f : dd;  // patch_retr_kernel, ba_cuda.cu:200-203
@@ -388,6 +397,7 @@ __global__ void __launch_bounds__(kBaThreads, 1) ba_window_kernel(BAArgs a) {
       grid.sync();
     } else {  // structure-only (ba_cuda.cu:494-506): dZ = Q u
       for (int r = r_lo + threadIdx.x; r < r_hi; r += blockDim.x) {
+        if (a.p.kx[r] >= a.n_patches) continue;
         float* pdz = a.patches + (size_t)a.p.kx[r] * 3 * PP + 2 * PP;
         float dd = pdz[0] + a.qk[r] * a.uk[r];
         dd = (dd > 20.f) ? 1.0f : dd;
@@ -482,7 +492,8 @@ int ba_forward_window(float* poses, float* patches, const float* intr, const flo
   a.uk = (float*)take(sizeof(float) * (size_t)(a.p.Mp_cap + 1));
   a.poses = poses; a.patches = patches; a.intr = intr; a.target = target; a.weight = weight; a.lmbda = lmbda;
   a.ii = ii; a.jj = jj; a.patches_est = patches_est; a.mu = mu; a.P = P; a.t0 = t0; a.N = N; a.iterations = iterations;
-  a.status = status; a.n_poses = (int)n_poses;
+  a.status = status; a.n_poses = (int)n_poses; a.n_patches = (int)n_patches;
+  a.kk_check = plan_groups > 0 ? kk : nullptr;
   if (plan_groups <= 0) {
     int rc = plan_build(a.p, kk, jj, ii, n_poses, nullptr, nullptr, status, st);
     if (rc != WV_OK) return rc;

@@ -198,6 +198,7 @@ std::vector<torch::Tensor> ba_forward(torch::Tensor poses, torch::Tensor patches
                                    (float)mu, ws.data_ptr(), (size_t)ws.numel(), kPlanGroups, status_word(poses.device()).data_ptr<int>(),
                                    current_stream()),
              "cuda_ba.forward");
+    note = PlanNote();  // one-shot: the next BA without a neighbors() before it builds its own plan
   } else {
     note = PlanNote();  // this call rebuilds the plan with its own layout
     check_rc(wv_ba_forward(poses.data_ptr<float>(), patches.data_ptr<float>(), intrinsics.data_ptr<float>(), tg.data_ptr<float>(),
