@@ -161,6 +161,27 @@ int wv_ba_reproject(const float* poses, const float* patches, const float* intri
                     const int64_t* jj, const int64_t* kk, int64_t E, int64_t n_poses, int64_t n_patches,
                     int P, float* coords, int* status, wv_stream_t stream);
 
+/* ---- fused projective ops: what dpvo/projective_ops.py composes from lietorch group ops ----------
+ * Layouts as the reference's tensors: poses [n_poses][7], patches [n_patches][3][P][P], intrinsics [n_poses][4] -- PER-FRAME
+ * rows (intrinsics[ii] back-projects, intrinsics[jj] projects) and d = 1 / max(Z, 0.1), as projective_ops.py:19-49 does
+ * (wv_ba_reproject is the fastba flavour: row 0 only, no clamp).
+ * wv_pops_transform: transform(poses, patches, intrinsics, ii, jj, kk, depth, valid, jacobian=False, tonly)
+ *   (projective_ops.py:53-104): coords [E][P][P][depth ? 3 : 2]; valid (nullable) [E][P][P] = (Z > 0.2).
+ * wv_pops_flow_mag: flow_mag(..., beta) (projective_ops.py:111-121): out [E][P][P].
+ * wv_pops_point_cloud: point_cloud(poses, patches, intrinsics, ix) (projective_ops.py:106-108): out [n][P][P][4].
+ * wv_frame_distance: compute_keyframe_distance (dpvo/dpvo.py:383-408) for all pairs of the first n frames, patches of frame f
+ *   at rows [f*M, (f+1)*M): D [n][n] symmetric, zero diagonal. */
+int wv_pops_transform(const float* poses, const float* patches, const float* intrinsics, const int64_t* ii,
+                      const int64_t* jj, const int64_t* kk, int64_t E, int64_t n_poses, int64_t n_patches, int P,
+                      int tonly, int depth, float* coords, float* valid, int* status, wv_stream_t stream);
+int wv_pops_flow_mag(const float* poses, const float* patches, const float* intrinsics, const int64_t* ii,
+                     const int64_t* jj, const int64_t* kk, int64_t E, int64_t n_poses, int64_t n_patches, int P,
+                     float beta, float* out, int* status, wv_stream_t stream);
+int wv_pops_point_cloud(const float* poses, const float* patches, const float* intrinsics, const int64_t* ix,
+                        int64_t n, int64_t n_poses, int P, float* out, int* status, wv_stream_t stream);
+int wv_frame_distance(const float* poses, const float* patches, const float* intrinsics, int64_t n, int64_t n_poses,
+                      int64_t n_patches, int M, int P, float beta, float* D, wv_stream_t stream);
+
 /* cuda_ba.neighbors (dpvo/fastba/ba.cpp:106-151), on the device and without host synchronisation:
  * for every edge the index of the previous / next edge of the same group `ii` in (jj, original index)
  * order, -1 at the ends.  ii values must lie in [0, n_groups). */

@@ -143,12 +143,68 @@ def pyba_cases():
     return out
 
 
+def pops_cases():
+    """dpvo/projective_ops.py (transform / flow_mag / point_cloud) over the reference's own lietorch CPU ops, and the keyframe
+    distance + distance-based edge selection of dpvo/dpvo.py:383-429 restated with those same reference functions (the methods
+    themselves live on the CUDA-only DPVO class).  Per-frame intrinsics differ from frame to frame on purpose."""
+    _, pops, lie = import_reference_python()
+    out = {}
+    for name, kw in {"trk": dict(seed=31, n=14, M=6, edges="tracker", lifetime=5, removal=8), "glb": dict(seed=32, n=24, M=4, edges="global")}.items():
+        s = syn.make_ba_scene(**kw)
+        rng = np.random.default_rng(7)
+        intr = s["intrinsics"] * (1.0 + 0.05 * rng.standard_normal(s["intrinsics"].shape)).astype(np.float32)
+        poses = s["poses"].copy()
+        poses[:, 3:] *= (1.0 + 0.01 * rng.standard_normal((len(poses), 1))).astype(np.float32)  # not exactly unit: lietorch renormalises
+        patches = s["patches"].copy()
+        patches[::9, 2] = 0.01  # far points; a few behind-the-camera cases come from the pose noise
+        G = lie.SE3(T(poses)[None]); pt = T(patches)[None]; K = T(intr)[None]
+        ii, jj, kk = T(s["ii"]), T(s["jj"]), T(s["kk"])
+        out.update({f"{name}_poses": poses, f"{name}_patches": patches, f"{name}_intrinsics": intr,
+                    f"{name}_ii": s["ii"], f"{name}_jj": s["jj"], f"{name}_kk": s["kk"]})
+        out[f"{name}_transform"] = pops.transform(G, pt, K, ii, jj, kk)[0].numpy()
+        co, val = pops.transform(G, pt, K, ii, jj, kk, depth=True, valid=True)
+        out[f"{name}_transform_depth"] = co[0].numpy(); out[f"{name}_valid"] = val[0].numpy()
+        out[f"{name}_transform_tonly"] = pops.transform(G, pt, K, ii, jj, kk, tonly=True)[0].numpy()
+        for beta in (0.3, 0.5):
+            out[f"{name}_flow_mag_{beta}"] = pops.flow_mag(G, pt, K, ii, jj, kk, beta=beta)[0].numpy()
+        n, M = s["n"], s["M"]
+        ix = torch.arange(len(patches)) // M
+        ix = ix.clamp(max=len(poses) - 1)
+        out[f"{name}_ix"] = ix.numpy()
+        out[f"{name}_point_cloud"] = pops.point_cloud(G, pt, K, ix)[0].numpy()
+        # compute_keyframe_distance(i, j, beta=0.5), dpvo/dpvo.py:383-408, for all pairs; then get_distance_based_edges, :410-429
+        D = np.zeros((n, n), np.float32)
+        for i in range(n):
+            for j in range(i + 1, n):
+                a = torch.full((M,), i, dtype=torch.long); b = torch.full((M,), j, dtype=torch.long)
+                ki = torch.arange(M * i, M * (i + 1)); kj = torch.arange(M * j, M * (j + 1))
+                fij = pops.flow_mag(G, pt, K, a, b, ki, beta=0.5); fji = pops.flow_mag(G, pt, K, b, a, kj, beta=0.5)
+                D[i, j] = D[j, i] = (0.5 * (fij.mean() + fji.mean())).item()
+        out[f"{name}_frame_distance"] = D
+        # threshold in the widest gap of the middle third of the sorted distances, so that the selection does not hinge on rounding
+        dv = np.sort(D[np.triu_indices(n, 2)])
+        lo, hi = len(dv) // 3, 2 * len(dv) // 3
+        g = int(np.argmax(np.diff(dv[lo:hi]))) + lo
+        thresh = float(0.5 * (dv[g] + dv[g + 1]))
+        ei, ej = [], []
+        for i in range(n - 1):
+            ei.append(i); ej.append(i + 1)
+        for i in range(n):
+            for j in range(i + 2, n):
+                if D[i, j] < thresh:
+                    ei.append(i); ej.append(j)
+        out[f"{name}_thresh"] = np.float32(thresh)
+        out[f"{name}_edges_ii"] = np.array(ei, np.int64); out[f"{name}_edges_jj"] = np.array(ej, np.int64)
+    return out
+
+
 def main():
     build_ref.build()
     os.makedirs(OUT, exist_ok=True)
     np.savez_compressed(os.path.join(OUT, "corr_ref.npz"), **corr_cases(build_ref.load("ref_cuda_corr")))
     np.savez_compressed(os.path.join(OUT, "ba_ref.npz"), **ba_cases(build_ref.load("ref_cuda_ba")))
     np.savez_compressed(os.path.join(OUT, "pyba_ref.npz"), **pyba_cases())
+    np.savez_compressed(os.path.join(OUT, "pops_ref.npz"), **pops_cases())
     for f in sorted(os.listdir(OUT)):
         print(f, os.path.getsize(os.path.join(OUT, f)) // 1024, "KiB")
 

@@ -159,3 +159,117 @@ def solve_system(J_i, J_j, ii, jj, res, ep, lm, freen):
     if rc < 0:
         raise ValueError("solve_system: i == j or negative index")
     return delta, rc
+
+
+# ----------------------------------------------------------------------------------------------------------
+# projective ops (numpy restatement; byte/elementwise arithmetic, vectorised over edges)
+#   dpvo/projective_ops.py:19-30 iproj, :33-49 proj, :53-68 transform (jacobian=False), :106-108 point_cloud, :111-121 flow_mag
+#   over lietorch's SE3: dpvo/lietorch/include/se3.h:36-38 inv, :45-47 operator*, :53-56 act4; so3.h:31-37 every SO3 constructed
+#   from data is normalised, :43-45 inv, :51-53 operator*, :55-60 rotation of a point.
+#   keyframe distance / distance-based edges: dpvo/dpvo.py:383-408, :410-429.
+# Pinned by tests/golden/pops_ref.npz = outputs of the reference's own Python + lietorch CPU ops (oracle/make_golden.py).
+# ----------------------------------------------------------------------------------------------------------
+def _qnorm(q):
+    return q / np.sqrt((q * q).sum(-1, keepdims=True))
+
+
+def _qmul(a, b):  # Hamilton product, (x, y, z, w)
+    ax, ay, az, aw = np.moveaxis(a, -1, 0); bx, by, bz, bw = np.moveaxis(b, -1, 0)
+    return np.stack([aw * bx + ax * bw + ay * bz - az * by, aw * by + ay * bw + az * bx - ax * bz,
+                     aw * bz + az * bw + ax * by - ay * bx, aw * bw - ax * bx - ay * by - az * bz], -1)
+
+
+def _qrot(q, p):  # so3.h:55-60
+    v, w = q[..., :3], q[..., 3:]
+    uv = np.cross(v, p)
+    uv = uv + uv
+    return p + w * uv + np.cross(v, uv)
+
+
+def _lie_relative(Pi, Pj):
+    """poses[j] * poses[i].inv() in lietorch's construction order -> (t, q)"""
+    qi = _qnorm(Pi[..., 3:])
+    qc = _qnorm(qi * np.array([-1, -1, -1, 1], qi.dtype))
+    tinv = -_qrot(qc, Pi[..., :3])
+    qc2 = _qnorm(qc)
+    qj = _qnorm(Pj[..., 3:])
+    q = _qnorm(_qmul(qj, qc2))
+    t = Pj[..., :3] + _qrot(qj, tinv)
+    return t, q
+
+
+def _act_project(t, q, X0, K, depth=False):
+    """act4 then proj; t, q: [E, 3|4]; X0 [E, P, P, 4]; K [E, 4]"""
+    q = _qnorm(q)[:, None, None]
+    X1 = _qrot(q, X0[..., :3]) + t[:, None, None] * X0[..., 3:]
+    Z = X1[..., 2]
+    d = 1.0 / np.maximum(Z, X0.dtype.type(0.1))
+    fx, fy, cx, cy = (K[:, c, None, None] for c in range(4))
+    x = fx * (d * X1[..., 0]) + cx
+    y = fy * (d * X1[..., 1]) + cy
+    return (np.stack([x, y, d], -1) if depth else np.stack([x, y], -1)), Z
+
+
+def _pops_prep(poses, patches, intrinsics, dtype):
+    P = int(np.asarray(patches.shape)[-1])
+    return _np(poses, dtype).reshape(-1, 7), _np(patches, dtype).reshape(-1, 3, P, P), _np(intrinsics, dtype).reshape(-1, 4)
+
+
+def _iproj(pa, K):  # pa [E, 3, P, P], K [E, 4]
+    fx, fy, cx, cy = (K[:, c, None, None] for c in range(4))
+    x, y, d = pa[:, 0], pa[:, 1], pa[:, 2]
+    return np.stack([(x - cx) / fx, (y - cy) / fy, np.ones_like(d), d], -1)
+
+
+def pops_transform(poses, patches, intrinsics, ii, jj, kk, depth=False, valid=False, tonly=False, dtype=np.float64):
+    po, pa, K = _pops_prep(poses, patches, intrinsics, dtype)
+    ii, jj, kk = _np(ii, np.int64), _np(jj, np.int64), _np(kk, np.int64)
+    X0 = _iproj(pa[kk], K[ii])
+    t, q = _lie_relative(po[ii], po[jj])
+    if tonly:
+        q = np.broadcast_to(np.array([0, 0, 0, 1], dtype), q.shape).copy()
+    x1, Z = _act_project(t, q, X0, K[jj], depth)
+    if valid:
+        return x1[None], (Z > 0.2).astype(dtype)[None]
+    return x1[None]
+
+
+def pops_flow_mag(poses, patches, intrinsics, ii, jj, kk, beta=0.3, dtype=np.float64):
+    c0 = pops_transform(poses, patches, intrinsics, ii, ii, kk, dtype=dtype)
+    c1 = pops_transform(poses, patches, intrinsics, ii, jj, kk, dtype=dtype)
+    c2 = pops_transform(poses, patches, intrinsics, ii, jj, kk, tonly=True, dtype=dtype)
+    f1 = np.sqrt(((c1 - c0) ** 2).sum(-1)); f2 = np.sqrt(((c2 - c0) ** 2).sum(-1))
+    return dtype(beta) * f1 + (dtype(1) - dtype(beta)) * f2
+
+
+def pops_point_cloud(poses, patches, intrinsics, ix, dtype=np.float64):
+    po, pa, K = _pops_prep(poses, patches, intrinsics, dtype)
+    ix = _np(ix, np.int64)
+    X0 = _iproj(pa, K[ix])
+    Pf = po[ix]
+    qc = _qnorm(_qnorm(Pf[:, 3:]) * np.array([-1, -1, -1, 1], dtype))
+    tinv = -_qrot(qc, Pf[:, :3])
+    qa = _qnorm(qc)[:, None, None]
+    xyz = _qrot(qa, X0[..., :3]) + tinv[:, None, None] * X0[..., 3:]
+    return np.concatenate([xyz, X0[..., 3:]], -1)[None]
+
+
+def frame_distance(poses, patches, intrinsics, n, M, beta=0.5, dtype=np.float64):
+    D = np.zeros((n, n), dtype)
+    for i in range(n):
+        for j in range(i + 1, n):
+            a = np.full(M, i, np.int64); b = np.full(M, j, np.int64)
+            fij = pops_flow_mag(poses, patches, intrinsics, a, b, np.arange(M * i, M * (i + 1)), beta, dtype)
+            fji = pops_flow_mag(poses, patches, intrinsics, b, a, np.arange(M * j, M * (j + 1)), beta, dtype)
+            D[i, j] = D[j, i] = 0.5 * (fij.mean() + fji.mean())
+    return D
+
+
+def distance_based_edges(D, thresh):
+    n = D.shape[0]
+    ei, ej = list(range(n - 1)), list(range(1, n))
+    for i in range(n):
+        for j in range(i + 2, n):
+            if D[i, j] < thresh:
+                ei.append(i); ej.append(j)
+    return np.array(ei, np.int64), np.array(ej, np.int64)

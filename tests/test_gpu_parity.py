@@ -617,3 +617,70 @@ def test_planned_ba_detects_a_plan_built_for_other_edges(syn):
     st, _, patches = planned(D["kk"], D["kk"], n_patches // 2)   # half the patch buffer: ids beyond it are flagged ...
     assert st & 1                      # WV_STATUS_BAD_INDEX
     assert torch.equal(patches[n_patches // 2:], D["patches"][n_patches // 2:])  # ... and never touched
+
+
+# ------------------------------------------------------------------------------------------------- fused projective ops (N1 / N4)
+def _pops_dev(g, name):
+    return [dev(g[f"{name}_{k}"]) for k in ("poses", "patches", "intrinsics", "ii", "jj", "kk")]
+
+
+@pytest.mark.parametrize("name", ["trk", "glb"])
+def test_pops_matches_reference_python(golden, name):
+    """projective_ops mirror (one kernel per call) vs outputs of the reference's own dpvo/projective_ops.py + lietorch CPU ops.
+    tolerance (stated): 2e-4 px on coordinates of magnitude ~150 px, 2e-6 relative on 3-D points; validity flags exact"""
+    pops = importlib.import_module(PKG + ".projective_ops")
+    g = golden["pops_ref"]
+    a = _pops_dev(g, name)
+    a[0], a[1], a[2] = a[0][None], a[1][None], a[2][None]  # the reference's [1, N, ...] layout
+    co = pops.transform(*a)
+    assert tuple(co.shape) == (1,) + g[f"{name}_transform"].shape
+    assert np.abs(co[0].cpu().numpy() - g[f"{name}_transform"]).max() < 2e-4
+    cd, val = pops.transform(*a, depth=True, valid=True)
+    assert np.abs(cd[0].cpu().numpy() - g[f"{name}_transform_depth"]).max() < 2e-4
+    assert np.array_equal(val[0].cpu().numpy(), g[f"{name}_valid"])
+    assert np.abs(pops.transform(*a, tonly=True)[0].cpu().numpy() - g[f"{name}_transform_tonly"]).max() < 2e-4
+    for beta in (0.3, 0.5):
+        assert np.abs(pops.flow_mag(*a, beta=beta)[0].cpu().numpy() - g[f"{name}_flow_mag_{beta}"]).max() < 2e-4
+    pc = pops.point_cloud(a[0], a[1], a[2], dev(g[f"{name}_ix"]))[0].cpu().numpy()
+    assert np.abs(pc - g[f"{name}_point_cloud"]).max() < 2e-6 * max(1.0, np.abs(g[f"{name}_point_cloud"]).max())
+    with pytest.raises(NotImplementedError):
+        pops.transform(*a, jacobian=True)
+
+    class FakeSE3:  # anything with .data, like lietorch's SE3
+        data = a[0]
+    assert torch.equal(pops.transform(FakeSE3(), *a[1:]), co)
+
+
+@pytest.mark.parametrize("name", ["trk", "glb"])
+def test_frame_distance_and_edges_match_reference(golden, name):
+    pops = importlib.import_module(PKG + ".projective_ops")
+    g = golden["pops_ref"]
+    a = _pops_dev(g, name)
+    Dref = g[f"{name}_frame_distance"]
+    n = Dref.shape[0]
+    M = 6 if name == "trk" else 4
+    D = pops.frame_distance(a[0], a[1], a[2], n, M, beta=0.5).cpu().numpy()
+    assert np.abs(D - Dref).max() < 2e-4 * max(1.0, Dref.max()) and np.array_equal(D, D.T) and np.all(np.diag(D) == 0)
+    ei, ej = pops.distance_based_edges(a[0], a[1], a[2], n, M, float(g[f"{name}_thresh"]), beta=0.5)
+    assert ei == g[f"{name}_edges_ii"].tolist() and ej == g[f"{name}_edges_jj"].tolist()   # bit-exact edge list, reference order
+
+
+def test_pops_full_size_vs_oracle_and_bad_index(syn):
+    """tracker-size edge list (E = 45 312): transform / flow_mag vs the fp64 oracle; out-of-range index raises"""
+    pops = importlib.import_module(PKG + ".projective_ops")
+    s = syn.make_ba_scene(seed=2, n=40, M=96, edges="tracker")
+    a = [dev(s[k]) for k in ("poses", "patches", "intrinsics", "ii", "jj", "kk")]
+    co = pops.transform(*a)[0].cpu().numpy()
+    ref = oracle.pops_transform(*[s[k] for k in ("poses", "patches", "intrinsics", "ii", "jj", "kk")])[0]
+    far = np.abs(ref) > 1e4  # points projected through d = 1 / 0.1 from behind the camera: compare relatively
+    assert np.abs(co - ref)[~far].max() < 1e-3 and np.all(np.abs(co - ref)[far] <= 1e-5 * np.abs(ref)[far])
+    fm = pops.flow_mag(*a, beta=0.5)[0].cpu().numpy()
+    fref = oracle.pops_flow_mag(*[s[k] for k in ("poses", "patches", "intrinsics", "ii", "jj", "kk")], beta=0.5)[0]
+    assert np.abs(fm - fref).max() < 1e-3 * max(1.0, np.abs(fref).max() * 1e-2)
+    bad = a[4].clone(); bad[3] = 10 ** 6
+    os.environ["WVB200_CHECK_INDICES"] = "1"
+    try:
+        with pytest.raises(IndexError):
+            pops.transform(a[0], a[1], a[2], a[3], bad, a[5])
+    finally:
+        del os.environ["WVB200_CHECK_INDICES"]

@@ -100,3 +100,39 @@ def test_prior_term_matches_python_ba(golden, syn, name, tag):
     ok = (rd > 1.1e-3) & (rd < 9.9) & (d > 1.1e-3) & (d < 9.9)
     assert ok.mean() > 0.9
     assert np.abs(d[ok] - rd[ok]).max() < 2e-3
+
+
+# ------------------------------------------------------------------------------------------------- projective ops (N1 / N4)
+def _pops_args(g, name):
+    return [g[f"{name}_{k}"] for k in ("poses", "patches", "intrinsics", "ii", "jj", "kk")]
+
+
+@pytest.mark.parametrize("name", ["trk", "glb"])
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+def test_pops_oracle_matches_reference_python(golden, name, dtype):
+    """numpy restatement of dpvo/projective_ops.py over lietorch's SE3 == the reference's own Python + lietorch CPU ops"""
+    g = golden["pops_ref"]
+    a = _pops_args(g, name)
+    # tolerance (stated): 2e-4 px on coordinates of magnitude ~150 px (the reference computes in fp32), 2e-6 on 3-D points
+    assert np.abs(oracle.pops_transform(*a, dtype=dtype)[0] - g[f"{name}_transform"]).max() < 2e-4
+    co, val = oracle.pops_transform(*a, depth=True, valid=True, dtype=dtype)
+    assert np.abs(co[0] - g[f"{name}_transform_depth"]).max() < 2e-4 and np.array_equal(val[0], g[f"{name}_valid"])
+    assert np.abs(oracle.pops_transform(*a, tonly=True, dtype=dtype)[0] - g[f"{name}_transform_tonly"]).max() < 2e-4
+    for beta in (0.3, 0.5):
+        assert np.abs(oracle.pops_flow_mag(*a, beta=beta, dtype=dtype)[0] - g[f"{name}_flow_mag_{beta}"]).max() < 2e-4
+    pc = oracle.pops_point_cloud(a[0], a[1], a[2], g[f"{name}_ix"], dtype=dtype)[0]
+    assert np.abs(pc - g[f"{name}_point_cloud"]).max() < 2e-6 * max(1.0, np.abs(g[f"{name}_point_cloud"]).max())
+
+
+@pytest.mark.parametrize("name", ["trk", "glb"])
+def test_frame_distance_oracle_and_edge_selection(golden, name):
+    g = golden["pops_ref"]
+    a = _pops_args(g, name)
+    Dref = g[f"{name}_frame_distance"]
+    n = Dref.shape[0]
+    M = 6 if name == "trk" else 4
+    D = oracle.frame_distance(a[0], a[1], a[2], n, M, beta=0.5)
+    assert np.abs(D - Dref).max() < 2e-4 * max(1.0, Dref.max())
+    ei, ej = oracle.distance_based_edges(D, float(g[f"{name}_thresh"]))
+    assert np.array_equal(ei, g[f"{name}_edges_ii"]) and np.array_equal(ej, g[f"{name}_edges_jj"])   # bit-exact edge list
+    assert len(ei) > n - 1   # some long-range edges selected, not only the sequential ones

@@ -42,6 +42,6 @@ def capi():
 
 
 def __getattr__(name):
-    if name in ("altcorr", "fastba", "synthetic", "hostapi", "dist"):
+    if name in ("altcorr", "fastba", "synthetic", "hostapi", "dist", "projective_ops"):
         return importlib.import_module(f"{__name__}.{name}")
     raise AttributeError(name)

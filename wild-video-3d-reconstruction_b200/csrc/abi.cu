@@ -53,6 +53,12 @@ int ba_global_dz(float*, float*, const float*, const float*, const float*, const
                  cudaStream_t);
 int ba_global_retract(float*, float*, int64_t, int64_t, int64_t, int, int, int, const float*, const float*, void*, size_t,
                       cudaStream_t);
+int pops_transform(const float*, const float*, const float*, const int64_t*, const int64_t*, const int64_t*, int64_t, int64_t, int64_t,
+                   int, int, int, float*, float*, int*, cudaStream_t);
+int pops_flow_mag(const float*, const float*, const float*, const int64_t*, const int64_t*, const int64_t*, int64_t, int64_t, int64_t,
+                  int, float, float*, int*, cudaStream_t);
+int pops_point_cloud(const float*, const float*, const float*, const int64_t*, int64_t, int64_t, int, float*, int*, cudaStream_t);
+int frame_distance(const float*, const float*, const float*, int, int, int, float, float*, cudaStream_t);
 }  // namespace wv
 
 using namespace wv;
@@ -223,6 +229,42 @@ int wv_ba_reproject(const float* poses, const float* patches, const float* intri
   if (E == 0) return WV_OK;
   if (!poses || !patches || !intrinsics || !ii || !jj || !kk || !coords) return WV_EINVAL;
   return ba_reproject(poses, patches, intrinsics, ii, jj, kk, E, n_poses, n_patches, P, coords, status, as_stream(stream));
+}
+
+int wv_pops_transform(const float* poses, const float* patches, const float* intrinsics, const int64_t* ii, const int64_t* jj,
+                      const int64_t* kk, int64_t E, int64_t n_poses, int64_t n_patches, int P, int tonly, int depth, float* coords,
+                      float* valid, int* status, wv_stream_t stream) {
+  if (E < 0 || n_poses <= 0 || n_patches <= 0 || P <= 0) return WV_EINVAL;
+  if (E == 0) return WV_OK;
+  if (!poses || !patches || !intrinsics || !ii || !jj || !kk || !coords) return WV_EINVAL;
+  return pops_transform(poses, patches, intrinsics, ii, jj, kk, E, n_poses, n_patches, P, tonly != 0, depth != 0, coords, valid, status,
+                        as_stream(stream));
+}
+
+int wv_pops_flow_mag(const float* poses, const float* patches, const float* intrinsics, const int64_t* ii, const int64_t* jj,
+                     const int64_t* kk, int64_t E, int64_t n_poses, int64_t n_patches, int P, float beta, float* out, int* status,
+                     wv_stream_t stream) {
+  if (E < 0 || n_poses <= 0 || n_patches <= 0 || P <= 0) return WV_EINVAL;
+  if (E == 0) return WV_OK;
+  if (!poses || !patches || !intrinsics || !ii || !jj || !kk || !out) return WV_EINVAL;
+  return pops_flow_mag(poses, patches, intrinsics, ii, jj, kk, E, n_poses, n_patches, P, beta, out, status, as_stream(stream));
+}
+
+int wv_pops_point_cloud(const float* poses, const float* patches, const float* intrinsics, const int64_t* ix, int64_t n,
+                        int64_t n_poses, int P, float* out, int* status, wv_stream_t stream) {
+  if (n < 0 || n_poses <= 0 || P <= 0) return WV_EINVAL;
+  if (n == 0) return WV_OK;
+  if (!poses || !patches || !intrinsics || !ix || !out) return WV_EINVAL;
+  return pops_point_cloud(poses, patches, intrinsics, ix, n, n_poses, P, out, status, as_stream(stream));
+}
+
+int wv_frame_distance(const float* poses, const float* patches, const float* intrinsics, int64_t n, int64_t n_poses,
+                      int64_t n_patches, int M, int P, float beta, float* D, wv_stream_t stream) {
+  if (n < 0 || M <= 0 || P <= 0 || n > n_poses || n * M > n_patches) return WV_EINVAL;
+  if (n > 65535) return WV_EUNSUPPORTED;
+  if (n == 0) return WV_OK;
+  if (!poses || !patches || !intrinsics || !D) return WV_EINVAL;
+  return frame_distance(poses, patches, intrinsics, (int)n, M, P, beta, D, as_stream(stream));
 }
 
 int wv_neighbors(const int64_t* ii, const int64_t* jj, int64_t E, int64_t n_groups, int64_t* ix, int64_t* jx,

@@ -253,6 +253,82 @@ torch::Tensor reproject(torch::Tensor poses, torch::Tensor patches, torch::Tenso
   return coords;
 }
 
+// ---- fused projective ops (dpvo/projective_ops.py over lietorch), SURVEY 8f N1 / N4 ---------------------------------------
+struct PopsIn { torch::Tensor po, pa, in, ii, jj, kk; int P; int64_t E, n_poses, n_patches; };
+
+PopsIn pops_inputs(const torch::Tensor& poses, const torch::Tensor& patches, const torch::Tensor& intrinsics, const torch::Tensor& ii,
+                   const torch::Tensor& jj, const torch::Tensor& kk) {
+  check_cuda(poses, "poses"); check_cuda(patches, "patches"); check_cuda(intrinsics, "intrinsics");
+  PopsIn x;
+  x.po = poses.to(torch::kFloat).contiguous(); x.pa = patches.to(torch::kFloat).contiguous(); x.in = intrinsics.to(torch::kFloat).contiguous();
+  TORCH_CHECK(x.pa.dim() >= 4, "projective ops: patches must be [..., 3, P, P]");
+  x.P = x.pa.size(-1);
+  x.n_poses = x.po.numel() / 7; x.n_patches = x.pa.numel() / (3 * x.P * x.P);
+  TORCH_CHECK(x.in.numel() == 4 * x.n_poses, "projective ops: intrinsics must have one row per pose");
+  x.ii = idx(ii, "ii"); x.jj = idx(jj, "jj"); x.kk = idx(kk, "kk");
+  x.E = x.ii.numel();
+  TORCH_CHECK(x.jj.numel() == x.E && x.kk.numel() == x.E, "projective ops: ii, jj, kk must have the same length");
+  return x;
+}
+
+std::vector<torch::Tensor> pops_transform(torch::Tensor poses, torch::Tensor patches, torch::Tensor intrinsics, torch::Tensor ii,
+                                          torch::Tensor jj, torch::Tensor kk, bool depth, bool valid, bool tonly) {
+  c10::cuda::CUDAGuard guard(poses.device());
+  PopsIn x = pops_inputs(poses, patches, intrinsics, ii, jj, kk);
+  torch::Tensor coords = torch::empty({1, x.E, x.P, x.P, depth ? 3 : 2}, x.po.options());
+  torch::Tensor val = valid ? torch::empty({1, x.E, x.P, x.P}, x.po.options()) : torch::Tensor();
+  check_rc(wv_pops_transform(x.po.data_ptr<float>(), x.pa.data_ptr<float>(), x.in.data_ptr<float>(), x.ii.data_ptr<int64_t>(),
+                             x.jj.data_ptr<int64_t>(), x.kk.data_ptr<int64_t>(), x.E, x.n_poses, x.n_patches, x.P, tonly, depth,
+                             coords.data_ptr<float>(), valid ? val.data_ptr<float>() : nullptr,
+                             status_word(x.po.device()).data_ptr<int>(), current_stream()),
+           "cuda_ba.transform");
+  if (env_flag("WVB200_CHECK_INDICES")) raise_on_status(x.po.device(), "cuda_ba.transform");
+  if (valid) return {coords, val};
+  return {coords};
+}
+
+torch::Tensor pops_flow_mag(torch::Tensor poses, torch::Tensor patches, torch::Tensor intrinsics, torch::Tensor ii, torch::Tensor jj,
+                            torch::Tensor kk, double beta) {
+  c10::cuda::CUDAGuard guard(poses.device());
+  PopsIn x = pops_inputs(poses, patches, intrinsics, ii, jj, kk);
+  torch::Tensor out = torch::empty({1, x.E, x.P, x.P}, x.po.options());
+  check_rc(wv_pops_flow_mag(x.po.data_ptr<float>(), x.pa.data_ptr<float>(), x.in.data_ptr<float>(), x.ii.data_ptr<int64_t>(),
+                            x.jj.data_ptr<int64_t>(), x.kk.data_ptr<int64_t>(), x.E, x.n_poses, x.n_patches, x.P, (float)beta,
+                            out.data_ptr<float>(), status_word(x.po.device()).data_ptr<int>(), current_stream()),
+           "cuda_ba.flow_mag");
+  if (env_flag("WVB200_CHECK_INDICES")) raise_on_status(x.po.device(), "cuda_ba.flow_mag");
+  return out;
+}
+
+torch::Tensor pops_point_cloud(torch::Tensor poses, torch::Tensor patches, torch::Tensor intrinsics, torch::Tensor ix) {
+  check_cuda(poses, "poses"); check_cuda(patches, "patches"); check_cuda(intrinsics, "intrinsics");
+  c10::cuda::CUDAGuard guard(poses.device());
+  torch::Tensor po = poses.to(torch::kFloat).contiguous(), pa = patches.to(torch::kFloat).contiguous(),
+                in = intrinsics.to(torch::kFloat).contiguous(), ixc = idx(ix, "ix");
+  const int P = pa.size(-1);
+  const int64_t n = pa.numel() / (3 * P * P), n_poses = po.numel() / 7;
+  TORCH_CHECK(ixc.numel() == n, "point_cloud: ix must have one frame index per patch");
+  torch::Tensor out = torch::empty({1, n, P, P, 4}, po.options());
+  check_rc(wv_pops_point_cloud(po.data_ptr<float>(), pa.data_ptr<float>(), in.data_ptr<float>(), ixc.data_ptr<int64_t>(), n, n_poses, P,
+                               out.data_ptr<float>(), status_word(po.device()).data_ptr<int>(), current_stream()),
+           "cuda_ba.point_cloud");
+  if (env_flag("WVB200_CHECK_INDICES")) raise_on_status(po.device(), "cuda_ba.point_cloud");
+  return out;
+}
+
+torch::Tensor frame_distance(torch::Tensor poses, torch::Tensor patches, torch::Tensor intrinsics, int64_t n, int64_t M, double beta) {
+  check_cuda(poses, "poses"); check_cuda(patches, "patches"); check_cuda(intrinsics, "intrinsics");
+  c10::cuda::CUDAGuard guard(poses.device());
+  torch::Tensor po = poses.to(torch::kFloat).contiguous(), pa = patches.to(torch::kFloat).contiguous(),
+                in = intrinsics.to(torch::kFloat).contiguous();
+  const int P = pa.size(-1);
+  torch::Tensor D = torch::empty({n, n}, po.options());
+  check_rc(wv_frame_distance(po.data_ptr<float>(), pa.data_ptr<float>(), in.data_ptr<float>(), n, po.numel() / 7,
+                             pa.numel() / (3 * P * P), (int)M, P, (float)beta, D.data_ptr<float>(), current_stream()),
+           "cuda_ba.frame_distance");
+  return D;
+}
+
 std::vector<torch::Tensor> solve_system(torch::Tensor J_Ginv_i, torch::Tensor J_Ginv_j, torch::Tensor ii, torch::Tensor jj,
                                         torch::Tensor res, float ep, float lm, int freen) {
   const torch::Device device = res.device();
@@ -289,4 +365,12 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.def("neighbors", &neighbors, "temporal neighboor indicies");
   m.def("reproject", &reproject, "fused reprojection of all patch pixels");
   m.def("solve_system", &solve_system, "solve system");
+  m.def("transform", &pops_transform, "fused projective transform (projective_ops.transform, jacobian=False)", py::arg("poses"),
+        py::arg("patches"), py::arg("intrinsics"), py::arg("ii"), py::arg("jj"), py::arg("kk"), py::arg("depth") = false,
+        py::arg("valid") = false, py::arg("tonly") = false);
+  m.def("flow_mag", &pops_flow_mag, "fused projective_ops.flow_mag", py::arg("poses"), py::arg("patches"), py::arg("intrinsics"),
+        py::arg("ii"), py::arg("jj"), py::arg("kk"), py::arg("beta") = 0.3);
+  m.def("point_cloud", &pops_point_cloud, "fused projective_ops.point_cloud");
+  m.def("frame_distance", &frame_distance, "all-pairs keyframe distance (DPVO.compute_keyframe_distance)", py::arg("poses"),
+        py::arg("patches"), py::arg("intrinsics"), py::arg("n"), py::arg("M"), py::arg("beta") = 0.5);
 }
