@@ -317,21 +317,29 @@ def run_b200(args):
     for _ in range(max(args.warmup, 3)):
         step(False)
     barrier()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
+    sampler = ClockSampler(local)  # every rank samples its own GPU; rank 0 reports its own line and the slowest clock seen
+    sampler.start()
     wall0 = time.perf_counter()
     for _ in range(args.steps):
         step(True)
     barrier()
     wall = time.perf_counter() - wall0
-    clocks = sampler.stop() if rank == 0 else None
+    clocks = sampler.stop()
     seg = np.array([[a.elapsed_time(b) for a, b in zip(e[:-1], e[1:])] for e in marks["ev"]])  # ms: L0, L1, neighbors, BA
     t_dev = float(seg.sum())  # ms over the K timed steps, flush/reset excluded
     tt = torch.tensor([t_dev], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     t_max = float(tt.item())
+    # per-rank segment times and clocks, for the record (the value above is the max over ranks)
+    per_rank = None
+    if world > 1:
+        mine = torch.tensor(list(seg.sum(0) / args.steps) + [clocks["sm_mhz"] or 0.0, float(len(clocks["reasons"]))], device=dev,
+                            dtype=torch.float64)
+        allr = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        per_rank = [[round(float(v), 4) for v in r.tolist()] for r in allr]
+        clocks["sm_mhz_min_over_ranks"] = min(r[4] for r in per_rank)
 
     # ---- end to end through the C ABI with HOST buffers (pinned), copies inside the timed region -----------------
     # the call a non-torch embedder makes: hostapi.Session.update == wv_session_update_host (include/wvb200.h)
@@ -393,6 +401,7 @@ def run_b200(args):
                          "algorithmic_bytes_per_launch": CORR_BYTES_L0 * E},
             "e2e": {"value": world * K / te, "unit": "frames/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "api": "hostapi.Session.update -> wv_session_update_host (C ABI, pinned host buffers, 3 streams)"},
+            "per_rank": {"columns": ["corr_l0_ms", "corr_l1_ms", "neighbors_ms", "ba_ms", "sm_mhz", "n_throttle_reasons"], "rows": per_rank},
             "gpu_launches": 6 * K,
             "gpu_launches_per_step": "corr: (restage + tiled kernel) x2 levels; plan kernel (neighbors; its plan is reused by BA); window kernel (BA) -- profiles/r1_launches_final.csv",
             "clocks": clocks,

@@ -51,6 +51,11 @@ const char* wv_strerror(int code);
 int wv_last_cuda_error(void);
 /* 1 when a device of compute capability 10.x is current, else 0 (the library has sm_100a code only) */
 int wv_device_supported(void);
+/* Read a device status word back to the host after everything enqueued on `stream` so far, and clear it when non-zero.
+ * Blocks (a short spin on an event, then a blocking wait); *value receives the WV_STATUS_* bits.  This is the one host
+ * synchronisation a caller needs to turn a data-dependent failure into an exception from the same call, as the reference's
+ * torch::linalg::cholesky does (dpvo/fastba/ba_cuda.cu:521). */
+int wv_status_read(int* status, int* value, wv_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * altcorr

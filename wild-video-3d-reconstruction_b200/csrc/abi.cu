@@ -86,6 +86,31 @@ int wv_device_supported(void) {
   return major == 10 ? 1 : 0;
 }
 
+int wv_status_read(int* status, int* value, wv_stream_t stream) {
+  if (!status || !value) return WV_EINVAL;
+  // one pinned word + one event per device, created on first use (callers hold the GIL / serialise per device)
+  struct Chan { int* host = nullptr; cudaEvent_t ev = nullptr; };
+  static Chan chans[64];
+  int dev = 0;
+  WV_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return WV_EUNSUPPORTED;
+  Chan& c = chans[dev];
+  if (!c.host) {
+    WV_CUDA_TRY(cudaHostAlloc(reinterpret_cast<void**>(&c.host), sizeof(int), cudaHostAllocDefault));
+    WV_CUDA_TRY(cudaEventCreateWithFlags(&c.ev, cudaEventDisableTiming));
+  }
+  cudaStream_t st = as_stream(stream);
+  WV_CUDA_TRY(cudaMemcpyAsync(c.host, status, sizeof(int), cudaMemcpyDeviceToHost, st));
+  WV_CUDA_TRY(cudaEventRecord(c.ev, st));
+  cudaError_t q = cudaErrorNotReady;
+  for (int spin = 0; spin < 200000 && q == cudaErrorNotReady; spin++) q = cudaEventQuery(c.ev);  // ~ a few hundred us at most
+  if (q == cudaErrorNotReady) q = cudaEventSynchronize(c.ev);
+  WV_CUDA_TRY(q);
+  *value = *c.host;
+  if (*value != 0) WV_CUDA_TRY(cudaMemsetAsync(status, 0, sizeof(int), st));
+  return WV_OK;
+}
+
 static bool corr_args_ok(const void* f1, const void* f2, const float* co, const int64_t* ii, const int64_t* jj, int dtype,
                          int B, int E, int C, int PH, int PW, int n1, int n2, int H2, int W2, int R) {
   if (dtype != WV_F16 && dtype != WV_F32) return false;

@@ -46,9 +46,9 @@ inline torch::Tensor& status_word(const torch::Device& dev) {
 // read + clear the status word (host sync); raises like the reference would
 inline void raise_on_status(const torch::Device& dev, const char* what) {
   torch::Tensor& w = status_word(dev);
-  const int s = w.item<int>();
+  int s = 0;
+  check_rc(wv_status_read(w.data_ptr<int>(), &s, current_stream()), what);  // async copy to a pinned word + event spin; clears when set
   if (s == 0) return;
-  w.zero_();
   TORCH_CHECK_INDEX(!(s & WV_STATUS_BAD_INDEX), what, ": index out of range in the edge list");
   TORCH_CHECK(!(s & WV_STATUS_STALE_PLAN), what, ": the cached edge plan did not match kk (poses / patches of this call are invalid); "
               "set WVB200_NO_PLAN_CACHE=1 and report this");
