@@ -43,7 +43,7 @@ enum {
 enum {
   WV_STATUS_BAD_INDEX = 1, /* an ii/jj/kk entry was outside its tensor; that edge was skipped */
   WV_STATUS_NOT_SPD = 2,   /* Cholesky met a non-positive pivot (reference: torch::linalg::cholesky throws, ba_cuda.cu:521) */
-  WV_STATUS_TOO_DENSE = 4, /* global BA: one patch had more than 128 free-pose observations; the excess was dropped */
+  WV_STATUS_TOO_DENSE = 4, /* global BA: one patch had more than 384 free-pose observations; the excess was dropped */
   WV_STATUS_STALE_PLAN = 8 /* wv_ba_forward_planned: the plan in the workspace was not built for this kk; the result is invalid */
 };
 
@@ -139,7 +139,7 @@ int wv_ba_forward_planned(float* poses, float* patches, const float* intrinsics,
  *     wv_ba_global_build -> (allreduce S, y) -> wv_ba_global_damp -> dX = S^-1 y (caller) ->
  *     wv_ba_global_dz -> (allreduce dZ) -> wv_ba_global_retract.
  * The dense 6N x Mp matrix E of the reference (:443-444) is never formed.
- *   S [6N][6N] row-major: only the LOWER triangle is written (the upper is left zero); y [6N]; N = t1 - t0.
+ *   S [6N][6N] row-major, 16-byte aligned: only the LOWER triangle is written (the upper is left zero); y [6N]; N = t1 - t0.
  *   dX [N][6]; dZ [min(E, n_patches)] indexed by the rank of the patch id among the sorted unique kk.
  *   build_plan != 0 rebuilds the edge plan in `workspace` (needed once per edge list, not per iteration).
  *   workspace_bytes >= wv_ba_global_workspace_bytes(E, n_patches); the same workspace goes to all four calls. */

@@ -684,3 +684,16 @@ def test_pops_full_size_vs_oracle_and_bad_index(syn):
             pops.transform(a[0], a[1], a[2], a[3], bad, a[5])
     finally:
         del os.environ["WVB200_CHECK_INDICES"]
+
+
+def test_global_ba_dense_patches_and_entry_limit(syn):
+    """every patch observed by every frame: 60 observations per patch go through the per-warp entry list (2 lane chunks per patch);
+    more than 384 observations per patch is refused loudly, not silently truncated"""
+    s = syn.make_ba_scene(seed=16, n=60, M=2, edges="all", pose_noise=0.005)
+    o, *tols = _global_tol(s, 1, 60, 1)
+    poses, patches = run_ba(s, 1, 60, 1)
+    _check_global(poses, patches, o, *tols)
+    big = syn.make_ba_scene(seed=17, n=400, M=1, edges="all", pose_noise=0.002)
+    with pytest.raises(RuntimeError, match="more than 384"):
+        run_ba(big, 1, 400, 1)
+    run_ba(s, 1, 60, 1)  # and the extension keeps working

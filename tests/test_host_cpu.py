@@ -170,6 +170,9 @@ class _ToyGlobalBA:
             dZ[r] = float((u - (e * dX.double().view(-1)).sum()) / (C + float(lmbda[0])))
         return dZ
 
+    def check_status(self, like):
+        self.calls.append(("check",))
+
     def global_retract(self, poses, patches, E, t0, t1, dX, dZ):
         import torch
         kx = self._kx

@@ -6,6 +6,8 @@
 
 #include <vector>
 
+#include <cstdint>
+
 #include "wv_common.cuh"
 
 namespace wv {
@@ -218,6 +220,7 @@ int wv_ba_global_build(float* poses, float* patches, const float* intrinsics, co
   if (rc != WV_OK) return rc;
   if (!poses || !patches || !intrinsics || !target || !weight || !lmbda || !ii || !jj || !kk || !workspace) return WV_EINVAL;
   if (t1 > t0 && (!S || !y)) return WV_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(S) & 15) != 0) return WV_EINVAL;  // vector REDs into S
   return ba_global_build(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk, E, n_poses, n_patches, P, t0, t1,
                          patches_est, mu, shard, nshards, build_plan, S, y, workspace, workspace_bytes, status, as_stream(stream));
 }

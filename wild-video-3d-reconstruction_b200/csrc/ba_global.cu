@@ -26,7 +26,8 @@ namespace wv {
 
 static constexpr int kGThreads = 256;
 static constexpr int kGWarps = kGThreads / 32;
-static constexpr int kMaxEntries = 128;  // (frame, 6-vector) entries of one patch's column of E
+static constexpr int kMaxEntries = 384;  // (frame, 6-vector) entries of one patch's column of E (per-warp list in shared memory)
+static constexpr size_t kEntryBytes = (size_t)kGWarps * kMaxEntries * (6 * sizeof(float) + sizeof(int));
 
 struct GArgs {
   float* poses; float* patches; const float* intr; const float* target; const float* weight; const float* lmbda;
@@ -59,7 +60,7 @@ static constexpr int kWinDim = 6 * kWinFrames;  // 192
 static constexpr int kTile = 8;
 static constexpr int kTilesPerDim = kWinDim / kTile;                    // 24
 static constexpr int kTiles = kTilesPerDim * (kTilesPerDim + 1) / 2;    // 300 lower tiles
-static constexpr size_t kBuildSmem = sizeof(float) * (kChunk * kWinDim + 2 * kChunk);
+static constexpr size_t kBuildSmem = kEntryBytes + sizeof(float) * (kChunk * kWinDim + 2 * kChunk);
 
 // 8-byte vector RED (sm_90+): rows of a 6x6 block start at an even float offset (n6 and 6*fb are even), S is 256-B aligned
 __device__ __forceinline__ void red2(float* p, float x, float y) { atomicAdd(reinterpret_cast<float2*>(p), make_float2(x, y)); }
@@ -135,9 +136,10 @@ __device__ __forceinline__ void lane_acc_flush(const LaneAcc& A, float* S, float
 
 template <bool BUILD>
 __global__ void __launch_bounds__(kGThreads) ba_global_kernel(GArgs a) {
-  extern __shared__ float dyn_mem[];  // BUILD: Ecol [kChunk][kWinDim], q [kChunk], qu [kChunk]
-  __shared__ float ent_v[kGWarps][kMaxEntries][6];
-  __shared__ int ent_f[kGWarps][kMaxEntries];
+  extern __shared__ float smem_all[];  // entry lists [kGWarps][kMaxEntries] x (6 floats + frame); BUILD: + Ecol, q, qu
+  float(*ent_v)[kMaxEntries][6] = reinterpret_cast<float(*)[kMaxEntries][6]>(smem_all);
+  int(*ent_f)[kMaxEntries] = reinterpret_cast<int(*)[kMaxEntries]>(smem_all + kGWarps * kMaxEntries * 6);
+  float* dyn_mem = smem_all + kEntryBytes / sizeof(float);  // BUILD: Ecol [kChunk][kWinDim], q [kChunk], qu [kChunk]
   __shared__ int s_wb;
   __shared__ int perm[kGWarps][32];
   const int N = a.N, n6 = 6 * N;
@@ -532,7 +534,8 @@ int ba_global_dz(float* poses, float* patches, const float* intr, const float* t
                        shard, nshards, status);
   a.dX = dX; a.dZ = dZ;
   WV_CUDA_TRY(cudaMemsetAsync(dZ, 0, sizeof(float) * (size_t)std::min(E, n_patches), st));
-  ba_global_kernel<false><<<global_grid(std::min(E, n_patches)), kGThreads, 0, st>>>(a);
+  WV_CUDA_TRY(cudaFuncSetAttribute(ba_global_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kEntryBytes));
+  ba_global_kernel<false><<<global_grid(std::min(E, n_patches)), kGThreads, kEntryBytes, st>>>(a);
   WV_LAUNCH_CHECK();
   return WV_OK;
 }

@@ -177,6 +177,7 @@ std::vector<torch::Tensor> ba_forward(torch::Tensor poses, torch::Tensor patches
   if (t1 - t0 > 16) {  // global BA: dense reduced system in HBM, the reference's own dense solver
     for (int it = 0; it < iterations; it++) {
       torch::Tensor Sy = global_build(poses, patches, intrinsics, tg, wt, lm, iic, jjc, kkc, t0, t1, 0, 1, it == 0, patches_est, mu);
+      raise_on_status(poses.device(), "cuda_ba.forward");  // bad index / over-dense patch: say so before the solve trips over it
       torch::Tensor dX = global_solve(Sy, t1 - t0);
       Sy = torch::Tensor();
       torch::Tensor dZ = global_dz(poses, patches, intrinsics, tg, wt, lm, iic, jjc, kkc, t0, t1, 0, 1, dX, patches_est, mu);
@@ -362,6 +363,8 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
         py::arg("target"), py::arg("weight"), py::arg("lmbda"), py::arg("ii"), py::arg("jj"), py::arg("kk"), py::arg("t0"),
         py::arg("t1"), py::arg("shard"), py::arg("nshards"), py::arg("dX"), py::arg("patches_est") = py::none(), py::arg("mu") = 2.0);
   m.def("global_retract", &global_retract, "global BA: pose + patch retraction");
+  m.def("check_status", [](torch::Tensor like) { c10::cuda::CUDAGuard guard(like.device()); raise_on_status(like.device(), "cuda_ba"); },
+        "raise if an earlier call on this device flagged a data-dependent failure (bad index, non-SPD system, ...)");
   m.def("neighbors", &neighbors, "temporal neighboor indicies");
   m.def("reproject", &reproject, "fused reprojection of all patch pixels");
   m.def("solve_system", &solve_system, "solve system");

@@ -37,6 +37,7 @@ def BA_sharded(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk, t0
     for it in range(iterations):
         Sy = cuda_ba.global_build(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk, t0, t1, rank, world, it == 0,
                                   patches_est, mu)
+        cuda_ba.check_status(poses)  # bad index / over-dense patch: say so before the solve trips over it
         if world > 1:
             dist.all_reduce(Sy, group=group)
         dX = cuda_ba.global_solve(Sy, t1 - t0)
@@ -45,3 +46,4 @@ def BA_sharded(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk, t0
         if world > 1:
             dist.all_reduce(dZ, group=group)
         cuda_ba.global_retract(poses, patches, E, t0, t1, dX, dZ)
+    cuda_ba.check_status(poses)  # bad index / over-dense patch flagged by any piece above (one host sync, like cuda_ba.forward)
