@@ -137,7 +137,7 @@ constexpr int kTrStrideW = 65;  // 32-bit words per pixel row in smem (64 + 1: o
 __global__ void __launch_bounds__(256) restage_kernel(const __half* __restrict__ fmap2, __half* __restrict__ nhwc, int HW,
                                                       int tiles_per_slot, long long n_tiles, int vec_ok,
                                                       const __half* __restrict__ gmap, __half* __restrict__ gT, long long n_patches,
-                                                      int tile_blocks) {
+                                                      int tile_blocks, int patch_kmajor) {
   __shared__ uint32_t T[kTrPix * kTrStrideW];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if ((int)blockIdx.x >= tile_blocks) {
@@ -146,10 +146,21 @@ __global__ void __launch_bounds__(256) restage_kernel(const __half* __restrict__
     for (long long n = w0; n < n_patches; n += wstep) {
       const unsigned short* in = reinterpret_cast<const unsigned short*>(gmap) + n * (kC * kPP);
       uint32_t* out = reinterpret_cast<uint32_t*>(gT + n * (kC * kPP));
+      if (patch_kmajor) {
+        // tcgen05 B operand: [64-channel half][patch pixel p][64 ch] = rows of 128 B with the 128-B swizzle already applied, so
+        // that two plain bulk copies (9 rows x 128 B each) land it in canonical K-major form
 #pragma unroll
-      for (int i = 0; i < kPP * 64 / 32; i++) {
-        const int o = i * 32 + lane, p = o >> 6, cp = o & 63;
-        out[o] = (uint32_t)in[(2 * cp) * kPP + p] | ((uint32_t)in[(2 * cp + 1) * kPP + p] << 16);
+        for (int i = 0; i < kPP * 64 / 32; i++) {
+          const int o = i * 32 + lane, h = o / (kPP * 32), r = o - h * (kPP * 32), p = r >> 5, w = r & 31;
+          const int cp = h * 32 + (((w >> 2) ^ (p & 7)) & 7) * 4 + (w & 3);
+          out[o] = (uint32_t)in[(2 * cp) * kPP + p] | ((uint32_t)in[(2 * cp + 1) * kPP + p] << 16);
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < kPP * 64 / 32; i++) {
+          const int o = i * 32 + lane, p = o >> 6, cp = o & 63;
+          out[o] = (uint32_t)in[(2 * cp) * kPP + p] | ((uint32_t)in[(2 * cp + 1) * kPP + p] << 16);
+        }
       }
     }
     return;
@@ -487,6 +498,305 @@ corr_tiled_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_co
 }  // namespace
 
 // ---------------------------------------------------------------------------------------------------
+// pass 2, tcgen05 form: corr_tc5_kernel.  Same tiles, same ring, but the contraction runs on the 5th-generation tensor cores:
+//   D[128 window pixels x 16] = tile[128 px x 128 ch] . patch[16 x 128 ch]^T        (100 or 72 pixel rows and 9 columns are real)
+// with BOTH operands read straight from the 128-B-swizzled shared memory the TMA wrote (K-major canonical layout: the tile IS the
+// A operand, M = window pixels; the pre-swizzled patch is the B operand, N = 16), the accumulator in TMEM, 8 tcgen05.mma
+// (M128 N16 K16) per tile issued by ONE thread.  mma.sync needs 104 warp-wide m16n8k16 per tile at ~16 cycles each on a
+// sub-core's legacy path (66 us per level for the tensor pipe alone, 7/16 of it on padding rows); here the MMA cost vanishes
+// and, because tcgen05.commit releases a stage the moment its MMAs retire, stages recycle without waiting for the blend.
+//
+// Two independent pipelines per CTA (each half of the CTA's edges), 6 warps each:
+//   producer warp  16 lanes prepare an edge each (window box, per-pixel origins + fractions -> a record), then issue in order:
+//                  wait empty[stage] -> expect_tx on full[stage] -> 2 TMA tile loads + 2 bulk copies of the patch halves
+//   MMA warp       one lane: wait full[stage], wait accempty[acc], 8 x tcgen05.mma, commit -> empty[stage], commit -> accfull[acc]
+//   4 consumer warps (one TMEM lane quarter each): wait accfull[acc], tcgen05.ld 32 pixel rows x 16 columns, scatter the 9 real
+//                  columns into the edge's D scratch, release the accumulator; after the edge's last part a 128-thread barrier,
+//                  then the 441 outputs of the edge, 4-tap bilinear each, written as coalesced fp16.
+// Every mbarrier has one waiter (or one group waiting for the same phase) and advances strictly in slot order.
+// ---------------------------------------------------------------------------------------------------
+namespace {
+
+constexpr int kT5Pipes = 2, kT5Stages = 3, kT5Acc = 4, kT5Rec = 32;
+constexpr int kT5Warps = 6;                                   // per pipeline: producer, MMA, 4 consumers
+constexpr int kT5Threads = 32 * kT5Pipes * kT5Warps;          // 384
+constexpr int kT5StageBytes = 30 * 1024;                      // two 13 KB tile halves + the patch as B operand [2][16][128 B]
+constexpr int kT5PatchOff = 26 * 1024, kT5PatchHalf = 2048, kT5PatchCopy = kPP * 128;  // 9 real rows per half
+constexpr int kT5RecBytes = 104;
+constexpr int kT5PipeBytes = kT5Stages * kT5StageBytes + 2 * kRawBytes + kT5Rec * kT5RecBytes;
+constexpr int kT5Bars = 2 * kT5Stages + 2 * kT5Acc;           // per pipeline
+constexpr int kT5Smem = 1024 + kT5Pipes * kT5PipeBytes + kT5Pipes * kT5Bars * 8 + 64;
+static_assert(kT5Smem <= 227 * 1024, "tcgen05 kernel shared memory budget");
+static_assert((kT5Stages * kT5StageBytes) % 1024 == 0 && kT5PipeBytes % 16 == 0, "alignment");
+
+struct T5Rec {  // one per SLOT (an edge with a 12x12 window owns two)
+  int kind;                  // 0 small tile, 1 half of a large tile, 2 direct gather, 3 nothing to read, 4 end of stream
+  int part, nparts;
+  int be;                    // b * E + e
+  unsigned char org[12];
+  float dx[kPP], dy[kPP];
+};
+
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {  // K-major, 128-B swizzle, 8-row groups 1024 B apart
+  return (uint64_t)((saddr >> 4) & 0x3fff) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+}
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+static_assert(sizeof(T5Rec) <= kT5RecBytes, "record slot");
+
+__global__ void __launch_bounds__(kT5Threads, 1)
+corr_tc5_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_constant__ CUtensorMap map_half, const CorrParams P) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  __shared__ uint32_t tmem_base_s;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int pl = warp / kT5Warps, role = warp % kT5Warps;
+  // stages of both pipelines first (1024-B aligned), then per pipeline: D scratch x2, records; barriers last
+  uint8_t* stages = smem + (size_t)pl * kT5Stages * kT5StageBytes;
+  uint8_t* aux = smem + (size_t)kT5Pipes * kT5Stages * kT5StageBytes + (size_t)pl * (2 * kRawBytes + kT5Rec * kT5RecBytes);
+  float* raw0 = reinterpret_cast<float*>(aux);
+  uint8_t* recs = aux + 2 * kRawBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)kT5Pipes * kT5Stages * kT5StageBytes +
+                                               (size_t)kT5Pipes * (2 * kRawBytes + kT5Rec * kT5RecBytes)) + pl * kT5Bars;
+  const uint32_t full0 = smem_u32(bars), empty0 = full0 + 8 * kT5Stages, accfull0 = empty0 + 8 * kT5Stages,
+                 accempty0 = accfull0 + 8 * kT5Acc;
+
+  if (role == 0 && lane == 0) {
+    for (int i = 0; i < kT5Stages; i++) { mbar_init(full0 + 8 * i, 1); mbar_init(empty0 + 8 * i, 1); }
+    for (int i = 0; i < kT5Acc; i++) { mbar_init(accfull0 + 8 * i, 1); mbar_init(accempty0 + 8 * i, 4); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 128;" ::"r"(smem_u32(&tmem_base_s)) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_base_s + (uint32_t)(pl * kT5Acc * 16);  // this pipeline's accumulators: 16 columns each
+
+  const long long BE = (long long)P.B * P.E;
+  const long long lo = BE * blockIdx.x / gridDim.x, hi = BE * (blockIdx.x + 1) / gridDim.x;
+  const long long plo = lo + (hi - lo) * pl / kT5Pipes, phi = lo + (hi - lo) * (pl + 1) / kT5Pipes;
+  const int cnt = (int)(phi - plo);
+
+  if (role == 0) {
+    // ================================================================= producer
+    int sbase = 0;  // slots issued so far (warp-uniform)
+    const int nbatch = (cnt + 15) >> 4;
+    for (int bt = 0; bt <= nbatch; bt++) {
+      const int k = 16 * bt + lane;
+      const bool last = bt == nbatch;                 // the batch after the last one carries the end-of-stream slot in lane 0
+      const bool valid = !last && lane < 16 && k < cnt;
+      int kind = 3, x0 = 0, y0 = 0, slot = 0, nsl = 0;
+      long long pid = -1, be = 0;
+      unsigned char org[12];
+      float dxv[kPP], dyv[kPP];
+      if (valid) {
+        be = plo + k;
+        const int b = (int)(be / P.E), e = (int)(be % P.E);
+        const int64_t ix = P.ii[e], jx = P.jj[e];
+        const float2* c2 = reinterpret_cast<const float2*>(P.coords + be * (2 * kPP));
+        float v[2 * kPP];
+#pragma unroll
+        for (int i = 0; i < kPP; i++) { const float2 t = c2[i]; v[2 * i] = t.x; v[2 * i + 1] = t.y; }
+        int fx[kPP], fy[kPP];
+        int mnx = kClamp * 2, mxx = -kClamp * 2, mny = kClamp * 2, mxy = -kClamp * 2;
+#pragma unroll
+        for (int p = 0; p < kPP; p++) {
+          fx[p] = clamp_floor(v[p]); fy[p] = clamp_floor(v[kPP + p]);
+          dxv[p] = v[p] - floorf(v[p]); dyv[p] = v[kPP + p] - floorf(v[kPP + p]);
+          mnx = min(mnx, fx[p]); mxx = max(mxx, fx[p]); mny = min(mny, fy[p]); mxy = max(mxy, fy[p]);
+        }
+        x0 = mnx - kR; y0 = mny - kR;
+        const int wdt = mxx - mnx + kD, hgt = mxy - mny + kD;
+        const bool bad = ix < 0 || ix >= P.n1 || jx < 0 || jx >= P.n2;
+        const bool outside = x0 >= P.W || y0 >= P.H || x0 + wdt <= 0 || y0 + hgt <= 0;
+        if (bad) set_status(P.status, WV_STATUS_BAD_INDEX);
+        int BX = kD;
+        if (bad || outside) kind = 3;
+        else if (wdt <= kBoxSmall && hgt <= kBoxSmall) { kind = 0; BX = kBoxSmall; }
+        else if (wdt <= kBoxLarge && hgt <= kBoxLarge) { kind = 1; BX = kBoxLarge; }
+        else kind = 2;
+        slot = bad ? 0 : b * P.n2 + (int)jx;
+        if (kind <= 2) pid = (long long)b * P.n1 + ix;
+#pragma unroll
+        for (int p = 0; p < kPP; p++) org[p] = (unsigned char)(kind <= 1 ? (fy[p] - mny) * BX + (fx[p] - mnx) : 0);
+        nsl = kind == 1 ? 2 : 1;
+      }
+      if (last && lane == 0) { kind = 4; nsl = 1; }
+      // slot numbers: exclusive prefix sum of nsl over the lanes
+      int incl = nsl;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+      const int myslot = sbase + incl - nsl;
+      const int total = __shfl_sync(0xffffffffu, incl, 31);
+      for (int part = 0; part < nsl; part++) {
+        T5Rec* r = reinterpret_cast<T5Rec*>(recs + ((myslot + part) % kT5Rec) * kT5RecBytes);
+        r->kind = kind; r->part = part; r->nparts = nsl; r->be = (int)be;
+#pragma unroll
+        for (int p = 0; p < kPP; p++) { r->org[p] = org[p]; r->dx[p] = dxv[p]; r->dy[p] = dyv[p]; }
+      }
+      __syncwarp();
+      // ---- issue in slot order; the lane that prepared an edge issues it (its operands are in its registers)
+      for (int L = 0; L < 16; L++) {
+        const int nL = __shfl_sync(0xffffffffu, nsl, L);
+        if (lane == L) {
+          for (int part = 0; part < nL; part++) {
+            const int sidx = myslot + part, stage = sidx % kT5Stages;
+            mbar_wait(empty0 + 8 * stage, ((sidx / kT5Stages) & 1) ^ 1);
+            const uint32_t bar = full0 + 8 * stage, dst = smem_u32(stages + (size_t)stage * kT5StageBytes);
+            const int npix = kind == 0 ? kBoxSmall * kBoxSmall : kBoxLarge * kBoxLargeRows;
+            const uint32_t bytes = (kind <= 1 ? 2u * npix * 128u : 0u) + (kind <= 2 ? 2u * kT5PatchCopy : 0u);
+            if (bytes) mbar_arrive_expect_tx(bar, bytes); else mbar_arrive(bar);
+            if (kind <= 1) {
+              const CUtensorMap* map = kind == 0 ? &map_small : &map_half;
+              const int yy = y0 + part * kBoxLargeRows;
+              tma_load_4d(dst, map, bar, 0, x0, yy, slot);
+              tma_load_4d(dst + kHalfBytes, map, bar, 64, x0, yy, slot);
+            }
+            if (kind <= 2) {
+              const __half* src = P.gT + pid * (kC * kPP);
+              bulk_copy_g2s(dst + kT5PatchOff, src, kT5PatchCopy, bar);
+              bulk_copy_g2s(dst + kT5PatchOff + kT5PatchHalf, src + kT5PatchCopy / 2, kT5PatchCopy, bar);
+            }
+          }
+        }
+        __syncwarp();
+      }
+      sbase += total;
+    }
+  } else if (role == 1) {
+    // ================================================================= MMA issue (one lane)
+    if (lane == 0) {
+      const uint32_t idesc = (1u << 4) | ((16u >> 3) << 17) | ((128u >> 4) << 24);  // D fp32; A, B fp16 K-major; N = 16; M = 128
+      for (int sidx = 0;; sidx++) {
+        const int stage = sidx % kT5Stages, acc = sidx % kT5Acc;
+        mbar_wait(full0 + 8 * stage, (sidx / kT5Stages) & 1);
+        const int kind = reinterpret_cast<const T5Rec*>(recs + (sidx % kT5Rec) * kT5RecBytes)->kind;
+        mbar_wait(accempty0 + 8 * acc, ((sidx / kT5Acc) & 1) ^ 1);
+        if (kind <= 1) {
+          tc_fence_after();
+          const uint32_t sa = smem_u32(stages + (size_t)stage * kT5StageBytes);
+#pragma unroll
+          for (int kq = 0; kq < 8; kq++) {
+            const uint32_t h = kq >> 2, kk = kq & 3;
+            umma_f16(tmem + acc * 16, umma_desc(sa + h * kHalfBytes + kk * 32), umma_desc(sa + kT5PatchOff + h * kT5PatchHalf + kk * 32),
+                     idesc, kq > 0 ? 1u : 0u);
+          }
+          umma_commit(empty0 + 8 * stage);   // the stage is free once these MMAs have read it
+          umma_commit(accfull0 + 8 * acc);   // ... and the accumulator is complete
+        } else {
+          if (kind != 2) mbar_arrive(empty0 + 8 * stage);  // (a gather edge keeps its stage: the consumers read the patch)
+          mbar_arrive(accfull0 + 8 * acc);
+          if (kind == 4) break;
+        }
+      }
+    }
+  } else {
+    // ================================================================= consumers: one warpgroup per pipeline
+    const int q = warp & 3;                       // the TMEM lane quarter this warp may read
+    const int wt = (role - 2) * 32 + lane;        // thread index in the warpgroup
+    int eidx = 0;
+    for (int sidx = 0;; sidx++) {
+      const int acc = sidx % kT5Acc, stage = sidx % kT5Stages;
+      mbar_wait(accfull0 + 8 * acc, (sidx / kT5Acc) & 1);
+      const T5Rec* rec = reinterpret_cast<const T5Rec*>(recs + (sidx % kT5Rec) * kT5RecBytes);
+      const int kind = rec->kind;
+      if (kind == 4) break;
+      const int part = rec->part, nparts = rec->nparts;
+      const long long be = rec->be;
+      float* rawD = raw0 + (eidx & 1) * (kRawBytes / 4);
+      if (part == 0 && wt < kPP) {
+        float* gr = rawD + wt * kRawStride + kMaxPix;
+        gr[0] = __int_as_float((int)rec->org[wt]); gr[1] = rec->dx[wt]; gr[2] = rec->dy[wt];
+      }
+      if (kind <= 1) {
+        tc_fence_after();
+        uint32_t v[16];
+        const uint32_t taddr = tmem + acc * 16 + ((uint32_t)(32 * q) << 16);
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+            : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+              "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+            : "r"(taddr));
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        const int row = 32 * q + lane, npix = kind == 0 ? kBoxSmall * kBoxSmall : kBoxLarge * kBoxLargeRows;
+        if (row < npix) {
+          float* d = rawD + part * (kBoxLarge * kBoxLargeRows) + row;
+#pragma unroll
+          for (int p = 0; p < kPP; p++) d[p * kRawStride] = __uint_as_float(v[p]);
+        }
+        tc_fence_before();
+      } else if (kind == 2) {
+        // direct gather (windows too far apart for a tile): the only path that reads global memory from a consumer
+        const size_t plane = (size_t)P.H * P.W;
+        const int eb = (int)(be / P.E), ee = (int)(be % P.E);
+        const __half* f2 = P.fmap2 + ((size_t)eb * P.n2 + (size_t)P.jj[ee]) * kC * plane;
+        const uint8_t* pb = stages + (size_t)stage * kT5StageBytes + kT5PatchOff;
+        for (int t = wt; t < kPP * kD * kD; t += 128) {
+          const int bb = t & 7, a = (t >> 3) & 7, p = t >> 6;
+          const int i1 = clamp_floor(P.coords[be * (2 * kPP) + kPP + p]) + a - kR, j1 = clamp_floor(P.coords[be * (2 * kPP) + p]) + bb - kR;
+          float sacc = 0.f;
+          if (i1 >= 0 && i1 < P.H && j1 >= 0 && j1 < P.W) {
+            const __half* p2 = f2 + (size_t)i1 * P.W + j1;
+            for (int c = 0; c < kC; c++) {
+              const __half pv = *reinterpret_cast<const __half*>(pb + (c >> 6) * kT5PatchHalf + p * 128 + (((((c & 63) >> 3) ^ (p & 7)) & 7) << 4) + (c & 7) * 2);
+              sacc = fmaf(__half2float(pv), __half2float(p2[(size_t)c * plane]), sacc);
+            }
+          }
+          rawD[p * kRawStride + a * kD + bb] = sacc;
+        }
+      } else {
+        for (int t = wt; t < kPP * kD * kD; t += 128) rawD[(t >> 6) * kRawStride + (t & 63)] = 0.f;
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(accempty0 + 8 * acc);
+      if (part != nparts - 1) continue;
+
+      asm volatile("bar.sync %0, 128;" ::"r"(1 + pl) : "memory");  // the edge's D scratch is complete
+      if (kind == 2 && wt == 0) mbar_arrive(empty0 + 8 * stage);
+      // ---- the 441 outputs of the edge: out[x-tap b][y-tap a][p], 4-tap bilinear from pixel p's own 8x8 window
+      const int BX = kind == 0 ? kBoxSmall : (kind == 1 ? kBoxLarge : kD);
+      __half* o = P.out + be * (kT * kT * kPP);
+#pragma unroll
+      for (int rd = 0; rd < 4; rd++) {
+        const int oi = wt + 128 * rd;
+        if (oi < kT * kT * kPP) {
+          const int ba = (oi * 7282) >> 16, p = oi - 9 * ba;   // oi / 9 for oi < 441
+          const int bq = (ba * 9363) >> 16, a = ba - 7 * bq;   // ba / 7 for ba < 49
+          const float* row = rawD + p * kRawStride;
+          const int org = __float_as_int(row[kMaxPix]);
+          const float dx = row[kMaxPix + 1], dy = row[kMaxPix + 2];
+          const float* rr = row + org + a * BX + bq;
+          const float r00 = rr[0], r01 = rr[1], r10 = rr[BX], r11 = rr[BX + 1];
+          const float h0 = fmaf(dx, r01 - r00, r00), h1 = fmaf(dx, r11 - r10, r10);
+          o[oi] = __float2half_rn(fmaf(dy, h1 - h0, h0));
+        }
+      }
+      eidx++;
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 128;" ::"r"(tmem_base_s) : "memory");
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------------
 namespace {
@@ -529,6 +839,11 @@ int tiled_mode() {  // WVB200_CORR_TILED: unset = heuristic, 0 = never, 1 = when
 
 inline size_t al1k(size_t x) { return (x + 1023) & ~(size_t)1023; }
 
+bool tc5_mode() {  // WVB200_CORR_TC5=0: the mma.sync kernel (corr_tiled_kernel) instead of the tcgen05 one
+  const char* s = getenv("WVB200_CORR_TC5");
+  return !(s && s[0] == '0');
+}
+
 }  // namespace
 
 bool corr_tiled_supported(int dtype, int B, int E, int C, int PH, int PW, int n1, int n2, int H2, int W2, int R) {
@@ -564,6 +879,7 @@ int corr_forward_tiled(const void* fmap1, const void* fmap2, const float* coords
   if (!make_map(&ms, nhwc, W2, H2, slots, kBoxSmall, kBoxSmall) || !make_map(&mh, nhwc, W2, H2, slots, kBoxLarge, kBoxLargeRows))
     return WV_EUNSUPPORTED;
 
+  const bool use_tc5 = tc5_mode();
   const int tiles_per_slot = (HW + kTrPix - 1) / kTrPix;
   const long long n_tiles = slots * tiles_per_slot;
   const long long cap = (long long)sm_count() * 8;
@@ -572,16 +888,27 @@ int corr_forward_tiled(const void* fmap1, const void* fmap2, const float* coords
   const int patch_blocks = (int)(pb < sm_count() ? pb : sm_count());
   const int vec_ok = ((HW & 7) == 0 && (reinterpret_cast<uintptr_t>(fmap2) & 15) == 0) ? 1 : 0;
   restage_kernel<<<tile_blocks + patch_blocks, 256, 0, st>>>((const __half*)fmap2, nhwc, HW, tiles_per_slot, n_tiles, vec_ok,
-                                                            (const __half*)fmap1, gT, n_patches, tile_blocks);
+                                                            (const __half*)fmap1, gT, n_patches, tile_blocks, use_tc5 ? 1 : 0);
   WV_LAUNCH_CHECK();
 
+  CorrParams P{gT, (const __half*)fmap2, coords, ii, jj, (__half*)out, B, E, n1, n2, H2, W2, status};
+  const long long BE = (long long)B * E;
+  if (use_tc5) {
+    static bool t5_attr_set = false;
+    if (!t5_attr_set) {
+      WV_CUDA_TRY(cudaFuncSetAttribute(corr_tc5_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kT5Smem));
+      t5_attr_set = true;
+    }
+    const long long want5 = (BE + 7) / 8;
+    corr_tc5_kernel<<<(int)(want5 < sm_count() ? want5 : sm_count()), kT5Threads, kT5Smem, st>>>(ms, mh, P);
+    WV_LAUNCH_CHECK();
+    return WV_OK;
+  }
   static bool attr_set = false;
   if (!attr_set) {
     WV_CUDA_TRY(cudaFuncSetAttribute(corr_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
     attr_set = true;
   }
-  CorrParams P{gT, (const __half*)fmap2, coords, ii, jj, (__half*)out, B, E, n1, n2, H2, W2, status};
-  const long long BE = (long long)B * E;
   const long long want = (BE + kConsumers - 1) / kConsumers;
   const int grid = (int)(want < sm_count() ? want : sm_count());
   corr_tiled_kernel<<<grid, kThreads, kSmemBytes, st>>>(ms, mh, P);
