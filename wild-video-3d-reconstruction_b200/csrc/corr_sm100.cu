@@ -517,17 +517,19 @@ corr_tiled_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_co
 // ---------------------------------------------------------------------------------------------------
 namespace {
 
-constexpr int kT5Pipes = 2, kT5Stages = 3, kT5Acc = 4, kT5Rec = 32;
+constexpr int kT5Pipes = 3, kT5Stages = 2, kT5Acc = 4, kT5Rec = 32;
+constexpr int kT5RawStride = 149;                             // odd: the 9 pixel rows start in 9 different banks
+constexpr int kT5RawBytes = kPP * kT5RawStride * 4;
 constexpr int kT5Warps = 6;                                   // per pipeline: producer, MMA, 4 consumers
 constexpr int kT5Threads = 32 * kT5Pipes * kT5Warps;          // 384
 constexpr int kT5StageBytes = 30 * 1024;                      // two 13 KB tile halves + the patch as B operand [2][16][128 B]
 constexpr int kT5PatchOff = 26 * 1024, kT5PatchHalf = 2048, kT5PatchCopy = kPP * 128;  // 9 real rows per half
 constexpr int kT5RecBytes = 104;
-constexpr int kT5PipeBytes = kT5Stages * kT5StageBytes + 2 * kRawBytes + kT5Rec * kT5RecBytes;
+constexpr int kT5PipeBytes = kT5Stages * kT5StageBytes + 2 * kT5RawBytes + kT5Rec * kT5RecBytes;
 constexpr int kT5Bars = 2 * kT5Stages + 2 * kT5Acc;           // per pipeline
 constexpr int kT5Smem = 1024 + kT5Pipes * kT5PipeBytes + kT5Pipes * kT5Bars * 8 + 64;
-static_assert(kT5Smem <= 227 * 1024, "tcgen05 kernel shared memory budget");
-static_assert((kT5Stages * kT5StageBytes) % 1024 == 0 && kT5PipeBytes % 16 == 0, "alignment");
+static_assert(kT5Smem <= 227 * 1024 && kT5Pipes * kT5Acc * 16 <= 256, "tcgen05 kernel shared memory / TMEM budget");
+static_assert((kT5Stages * kT5StageBytes) % 1024 == 0 && kT5PipeBytes % 8 == 0 && kMaxPix + 3 <= kT5RawStride, "alignment");
 
 struct T5Rec {  // one per SLOT (an edge with a 12x12 window owns two)
   int kind;                  // 0 small tile, 1 half of a large tile, 2 direct gather, 3 nothing to read, 4 end of stream
@@ -564,11 +566,11 @@ corr_tc5_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_cons
   const int pl = warp / kT5Warps, role = warp % kT5Warps;
   // stages of both pipelines first (1024-B aligned), then per pipeline: D scratch x2, records; barriers last
   uint8_t* stages = smem + (size_t)pl * kT5Stages * kT5StageBytes;
-  uint8_t* aux = smem + (size_t)kT5Pipes * kT5Stages * kT5StageBytes + (size_t)pl * (2 * kRawBytes + kT5Rec * kT5RecBytes);
+  uint8_t* aux = smem + (size_t)kT5Pipes * kT5Stages * kT5StageBytes + (size_t)pl * (2 * kT5RawBytes + kT5Rec * kT5RecBytes);
   float* raw0 = reinterpret_cast<float*>(aux);
-  uint8_t* recs = aux + 2 * kRawBytes;
+  uint8_t* recs = aux + 2 * kT5RawBytes;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)kT5Pipes * kT5Stages * kT5StageBytes +
-                                               (size_t)kT5Pipes * (2 * kRawBytes + kT5Rec * kT5RecBytes)) + pl * kT5Bars;
+                                               (size_t)kT5Pipes * (2 * kT5RawBytes + kT5Rec * kT5RecBytes)) + pl * kT5Bars;
   const uint32_t full0 = smem_u32(bars), empty0 = full0 + 8 * kT5Stages, accfull0 = empty0 + 8 * kT5Stages,
                  accempty0 = accfull0 + 8 * kT5Acc;
 
@@ -579,7 +581,7 @@ corr_tc5_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_cons
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
   if (warp == 0) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 128;" ::"r"(smem_u32(&tmem_base_s)) : "memory");
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 256;" ::"r"(smem_u32(&tmem_base_s)) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   tc_fence_before();
@@ -709,6 +711,14 @@ corr_tc5_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_cons
     // ================================================================= consumers: one warpgroup per pipeline
     const int q = warp & 3;                       // the TMEM lane quarter this warp may read
     const int wt = (role - 2) * 32 + lane;        // thread index in the warpgroup
+    // this thread's (up to) four outputs of every edge: oi = wt + 128 rd = (x-tap b * 7 + y-tap a) * 9 + p
+    int o_p[4], o_a[4], o_b[4];
+#pragma unroll
+    for (int rd = 0; rd < 4; rd++) {
+      const int oi = min(wt + 128 * rd, kT * kT * kPP - 1);
+      const int ba = oi / kPP;
+      o_p[rd] = oi - kPP * ba; o_b[rd] = ba / kT; o_a[rd] = ba - kT * (ba / kT);
+    }
     int eidx = 0;
     for (int sidx = 0;; sidx++) {
       const int acc = sidx % kT5Acc, stage = sidx % kT5Stages;
@@ -718,9 +728,9 @@ corr_tc5_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_cons
       if (kind == 4) break;
       const int part = rec->part, nparts = rec->nparts;
       const long long be = rec->be;
-      float* rawD = raw0 + (eidx & 1) * (kRawBytes / 4);
+      float* rawD = raw0 + (eidx & 1) * (kT5RawBytes / 4);
       if (part == 0 && wt < kPP) {
-        float* gr = rawD + wt * kRawStride + kMaxPix;
+        float* gr = rawD + wt * kT5RawStride + kMaxPix;
         gr[0] = __int_as_float((int)rec->org[wt]); gr[1] = rec->dx[wt]; gr[2] = rec->dy[wt];
       }
       if (kind <= 1) {
@@ -737,7 +747,7 @@ corr_tc5_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_cons
         if (row < npix) {
           float* d = rawD + part * (kBoxLarge * kBoxLargeRows) + row;
 #pragma unroll
-          for (int p = 0; p < kPP; p++) d[p * kRawStride] = __uint_as_float(v[p]);
+          for (int p = 0; p < kPP; p++) d[p * kT5RawStride] = __uint_as_float(v[p]);
         }
         tc_fence_before();
       } else if (kind == 2) {
@@ -757,10 +767,10 @@ corr_tc5_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_cons
               sacc = fmaf(__half2float(pv), __half2float(p2[(size_t)c * plane]), sacc);
             }
           }
-          rawD[p * kRawStride + a * kD + bb] = sacc;
+          rawD[p * kT5RawStride + a * kD + bb] = sacc;
         }
       } else {
-        for (int t = wt; t < kPP * kD * kD; t += 128) rawD[(t >> 6) * kRawStride + (t & 63)] = 0.f;
+        for (int t = wt; t < kPP * kD * kD; t += 128) rawD[(t >> 6) * kT5RawStride + (t & 63)] = 0.f;
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(accempty0 + 8 * acc);
@@ -775,12 +785,10 @@ corr_tc5_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_cons
       for (int rd = 0; rd < 4; rd++) {
         const int oi = wt + 128 * rd;
         if (oi < kT * kT * kPP) {
-          const int ba = (oi * 7282) >> 16, p = oi - 9 * ba;   // oi / 9 for oi < 441
-          const int bq = (ba * 9363) >> 16, a = ba - 7 * bq;   // ba / 7 for ba < 49
-          const float* row = rawD + p * kRawStride;
+          const float* row = rawD + o_p[rd] * kT5RawStride;
           const int org = __float_as_int(row[kMaxPix]);
           const float dx = row[kMaxPix + 1], dy = row[kMaxPix + 2];
-          const float* rr = row + org + a * BX + bq;
+          const float* rr = row + org + o_a[rd] * BX + o_b[rd];
           const float r00 = rr[0], r01 = rr[1], r10 = rr[BX], r11 = rr[BX + 1];
           const float h0 = fmaf(dx, r01 - r00, r00), h1 = fmaf(dx, r11 - r10, r10);
           o[oi] = __float2half_rn(fmaf(dy, h1 - h0, h0));
@@ -791,7 +799,7 @@ corr_tc5_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_cons
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 128;" ::"r"(tmem_base_s) : "memory");
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 256;" ::"r"(tmem_base_s) : "memory");
 }
 
 }  // namespace
