@@ -692,11 +692,12 @@ corr_tc5_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_cons
         if (kind <= 1) {
           tc_fence_after();
           const uint32_t sa = smem_u32(stages + (size_t)stage * kT5StageBytes);
+          const uint64_t da0 = umma_desc(sa), db0 = umma_desc(sa + kT5PatchOff);  // advancing K or the half only moves the start address
 #pragma unroll
           for (int kq = 0; kq < 8; kq++) {
             const uint32_t h = kq >> 2, kk = kq & 3;
-            umma_f16(tmem + acc * 16, umma_desc(sa + h * kHalfBytes + kk * 32), umma_desc(sa + kT5PatchOff + h * kT5PatchHalf + kk * 32),
-                     idesc, kq > 0 ? 1u : 0u);
+            umma_f16(tmem + acc * 16, da0 + ((h * kHalfBytes + kk * 32) >> 4), db0 + ((h * kT5PatchHalf + kk * 32) >> 4), idesc,
+                     kq > 0 ? 1u : 0u);
           }
           umma_commit(empty0 + 8 * stage);   // the stage is free once these MMAs have read it
           umma_commit(accfull0 + 8 * acc);   // ... and the accumulator is complete
@@ -711,13 +712,14 @@ corr_tc5_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_cons
     // ================================================================= consumers: one warpgroup per pipeline
     const int q = warp & 3;                       // the TMEM lane quarter this warp may read
     const int wt = (role - 2) * 32 + lane;        // thread index in the warpgroup
-    // this thread's (up to) four outputs of every edge: oi = wt + 128 rd = (x-tap b * 7 + y-tap a) * 9 + p
-    int o_p[4], o_a[4], o_b[4];
+    // outputs of an edge: out[tap = x-tap b * 7 + y-tap a][p].  Thread wt < 126 owns patch pixel p = wt % 9 and the taps
+    // wt / 9 + 14 j (j = 0..3): its geometry is read once per edge, and for a fixed j the 126 threads write 126 consecutive halves.
+    const int o_p = wt % kPP, tap0 = wt / kPP;
+    int o_a[4], o_b[4];
 #pragma unroll
-    for (int rd = 0; rd < 4; rd++) {
-      const int oi = min(wt + 128 * rd, kT * kT * kPP - 1);
-      const int ba = oi / kPP;
-      o_p[rd] = oi - kPP * ba; o_b[rd] = ba / kT; o_a[rd] = ba - kT * (ba / kT);
+    for (int j = 0; j < 4; j++) {
+      const int tap = min(tap0 + 14 * j, kT * kT - 1);
+      o_b[j] = tap / kT; o_a[j] = tap - kT * (tap / kT);
     }
     int eidx = 0;
     for (int sidx = 0;; sidx++) {
@@ -781,17 +783,18 @@ corr_tc5_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_cons
       // ---- the 441 outputs of the edge: out[x-tap b][y-tap a][p], 4-tap bilinear from pixel p's own 8x8 window
       const int BX = kind == 0 ? kBoxSmall : (kind == 1 ? kBoxLarge : kD);
       __half* o = P.out + be * (kT * kT * kPP);
+      if (wt < 14 * kPP) {
+        const float* row = rawD + o_p * kT5RawStride;
+        const float dx = row[kMaxPix + 1], dy = row[kMaxPix + 2];
+        const float* r0 = row + __float_as_int(row[kMaxPix]);
 #pragma unroll
-      for (int rd = 0; rd < 4; rd++) {
-        const int oi = wt + 128 * rd;
-        if (oi < kT * kT * kPP) {
-          const float* row = rawD + o_p[rd] * kT5RawStride;
-          const int org = __float_as_int(row[kMaxPix]);
-          const float dx = row[kMaxPix + 1], dy = row[kMaxPix + 2];
-          const float* rr = row + org + o_a[rd] * BX + o_b[rd];
-          const float r00 = rr[0], r01 = rr[1], r10 = rr[BX], r11 = rr[BX + 1];
-          const float h0 = fmaf(dx, r01 - r00, r00), h1 = fmaf(dx, r11 - r10, r10);
-          o[oi] = __float2half_rn(fmaf(dy, h1 - h0, h0));
+        for (int j = 0; j < 4; j++) {
+          if (tap0 + 14 * j < kT * kT) {
+            const float* rr = r0 + o_a[j] * BX + o_b[j];
+            const float r00 = rr[0], r01 = rr[1], r10 = rr[BX], r11 = rr[BX + 1];
+            const float h0 = fmaf(dx, r01 - r00, r00), h1 = fmaf(dx, r11 - r10, r10);
+            o[wt + 14 * kPP * j] = __float2half_rn(fmaf(dy, h1 - h0, h0));
+          }
         }
       }
       eidx++;
