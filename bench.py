@@ -34,8 +34,8 @@ for p in (ROOT,):
 # indices + output):  s*C*P^2 + s*C*F + 4*2*P^2 + 2*8 + s*49*P^2,  F0 = 100 px, F1 = 81 px
 CORR_BYTES_L0 = 2 * 128 * 9 + 2 * 128 * 100 + 72 + 16 + 2 * 49 * 9   # 28 874
 CORR_BYTES_L1 = 2 * 128 * 9 + 2 * 128 * 81 + 72 + 16 + 2 * 49 * 9    # 24 010
-# dram__bytes_read.sum + dram__bytes_write.sum per level-0 call (restage 121.2 + 73.6 MB, tiled 284.1 + 35.6 MB), ncu --set full
-NCU_TRAFFIC_L0 = 514.5e6
+# dram__bytes_read.sum + dram__bytes_write.sum per level-0 call (restage 121.2 + 73.7 MB, tcgen05 kernel 281.7 + 36.7 MB), ncu --set full
+NCU_TRAFFIC_L0 = 513.4e6
 WORKLOAD = ("configs[1]: 512x384 -> fmaps 96x128 + 24x32, C=128 fp16, pmem=36, M=96, tracker edge list E=45312, "
             "radius 3; one update(): corr x2 levels + neighbors + BA(10 free poses, 2 GN iterations)")
 
@@ -397,13 +397,13 @@ def run_b200(args):
             "wall_ms_per_step_incl_flush": 1e3 * wall / K,
             "roofline": {"kernel": "corr forward, level 0 (fp16 maps)", "bound": "hbm", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak, "traffic": NCU_TRAFFIC_L0, "peak_source": peak_src,
-                         "traffic_source": "dram__bytes_read+write of restage_kernel + corr_tiled_kernel, ncu --set full, profiles/r1_final_ncu_summary.txt",
+                         "traffic_source": "dram__bytes_read+write of restage_kernel + corr_tc5_kernel, ncu --set full, profiles/r1_final_ncu_summary.txt",
                          "algorithmic_bytes_per_launch": CORR_BYTES_L0 * E},
             "e2e": {"value": world * K / te, "unit": "frames/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "api": "hostapi.Session.update -> wv_session_update_host (C ABI, pinned host buffers, 3 streams)"},
             "per_rank": {"columns": ["corr_l0_ms", "corr_l1_ms", "neighbors_ms", "ba_ms", "sm_mhz", "n_throttle_reasons"], "rows": per_rank},
             "gpu_launches": 6 * K,
-            "gpu_launches_per_step": "corr: (restage + tiled kernel) x2 levels; plan kernel (neighbors; its plan is reused by BA); window kernel (BA) -- profiles/r1_launches_final.csv",
+            "gpu_launches_per_step": "corr: (restage + tcgen05 tile kernel) x2 levels; plan kernel (neighbors; its plan is reused by BA); window kernel (BA) -- profiles/r1_launches_final.csv",
             "clocks": clocks,
         }
         if world == 1 and not args.no_cpu:
