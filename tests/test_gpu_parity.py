@@ -301,6 +301,12 @@ def _check_tiled(g, f, co, ii, jj):
         out = run_corr(g, f, co, ii, jj, 3, torch.float16)
     with _tiled(False):
         gen = run_corr(g, f, co, ii, jj, 3, torch.float16)
+    os.environ["WVB200_CORR_TC5"] = "0"      # the mma.sync form of the tile kernel: same tiles, same blend, other tensor path
+    try:
+        with _tiled(True):
+            legacy = run_corr(g, f, co, ii, jj, 3, torch.float16)
+    finally:
+        del os.environ["WVB200_CORR_TC5"]
     g16 = torch.from_numpy(g).half().float().numpy()
     f16 = torch.from_numpy(f).half().float().numpy()
     truth = oracle.corr_forward(g16, f16, co, ii, jj, 3, mode=oracle.F64)
@@ -308,6 +314,8 @@ def _check_tiled(g, f, co, ii, jj):
     assert np.abs(out - truth).max() <= 2.0 ** -10 * scale
     # both paths accumulate in fp32 and round once: they may differ by one fp16 rounding where the sums differ in the last bits
     assert np.abs(out - gen).max() <= 2.0 ** -9 * scale
+    assert np.abs(legacy - truth).max() <= 2.0 ** -10 * scale
+    assert np.abs(out - legacy).max() <= 2.0 ** -9 * scale
     return out
 
 

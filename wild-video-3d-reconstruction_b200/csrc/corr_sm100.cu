@@ -5,27 +5,32 @@
 //   pass 1  restage_kernel: the frame-feature ring fmap2 [slot][C][H][W] is restaged channels-last [slot][H][W][C] in the
 //           caller's workspace, so that one pixel's 128 channels are one aligned 256-B line (in NCHW the contiguous unit
 //           is a ~20-B x-run per (c, y): every 32-B sector fetched is 2/3 waste); the source patches gmap [n][C][3][3] are
-//           restaged pixel-major [n][9][C] (the tensor-core A operand, fetched with one bulk copy).
-//   pass 2  corr_tiled_kernel, persistent, one CTA per SM, warp-specialised:
-//             producer warp   owns all global reads.  32 edges per pass (one lane each): bounding box of the nine 8x8 tap
-//                             windows, per-pixel window origin + bilinear fractions.  Then, per edge, into the next stage
-//                             of a 6-stage shared-memory ring: a 128-B record (STS), two TMA tile loads
-//                             (cp.async.bulk.tensor.4d, 64 channels x 10x10 px, 128-B swizzle, OOB zero fill == the
-//                             reference's within_bounds rule), one bulk copy of the 2 304-B patch, all completing on the
-//                             owning consumer warp's mbarrier.  Windows up to 12x12 px go as two 12x6 half tiles.
-//             8 consumer warps  no global reads: A fragments by ldmatrix from the patch, B fragments by ldmatrix from the
-//                             swizzled tile, D[9 x npix] = patch[9 x 128] . tile[128 x npix] with mma.sync m16n8k16
-//                             (fp16 in, fp32 accumulate), stage released, then the 4-corner bilinear blend of every
-//                             patch pixel's own 8x8 sub-window and the permuted [x-tap][y-tap][3][3] fp16 store
-//                             (correlation_kernel.cu:221-232), fused.
+//           restaged pixel-major: [n][2 halves][9][64] rows of 128 B with the 128-B swizzle applied (the tcgen05 B operand,
+//           two bulk copies), or plain [n][9][C] for the mma.sync variant.
+//   pass 2  corr_tc5_kernel (default), persistent, one CTA per SM, three independent pipelines of six warps each:
+//             producer warp   owns all global reads.  16 lanes prepare one edge each: bounding box of the nine 8x8 tap
+//                             windows, per-pixel window origin + bilinear fractions -> a 104-B record.  Then, per edge,
+//                             into the next of the pipeline's 2 stages: two TMA tile loads (cp.async.bulk.tensor.4d,
+//                             64 channels x 10x10 px, 128-B swizzle, OOB zero fill == the reference's within_bounds rule)
+//                             and two bulk copies of the pre-swizzled patch halves, all completing on the stage's
+//                             mbarrier.  Windows up to 12x12 px go as two 12x6 half tiles (two slots).
+//             MMA warp        one lane: D[128 px x 16] = tile[128 px x 128 ch] . patch[16 x 128 ch]^T as 8 tcgen05.mma
+//                             (M128 N16 K16, fp16 in, fp32 accumulate in TMEM); the TMA-written tile is the K-major A
+//                             operand in place; tcgen05.commit releases the stage and publishes the accumulator.
+//             4 consumer warps  tcgen05.ld of their TMEM lane quarter, the 9 real columns scattered to a per-edge fp32
+//                             scratch, then the 4-corner bilinear blend of every patch pixel's own 8x8 sub-window and
+//                             the permuted [x-tap][y-tap][3][3] fp16 store (correlation_kernel.cu:221-232), fused.
+//           corr_tiled_kernel (WVB200_CORR_TC5=0) is the earlier form of pass 2 with the contraction on mma.sync m16n8k16
+//           inside 8 consumer warps; it is kept as a cross-check of the tcgen05 path (tests run both).
 //
 // Why tensor cores here (BASELINE north_star: "only if ncu shows that step is compute-bound"): the contraction is
 // 2*128*64*9 = 147 kflop per edge and level, 13.4 GFLOP per two-level call; on the fp32 pipe (fp16 -> fp32 converts
 // included) that is >= 0.4 ms on 148 SMs, above the 0.37 ms HBM time of the algorithmic bytes -- see profiles/.
-// As a [16 x 128] x [128 x npix] MMA per edge it is ~1 % of the tensor pipe and the kernel goes back to being bound
-// by L2 -> SM tile traffic.
+// mma.sync measured ~66 us of tensor-pipe time per level on the warps that also blend (104 warp-wide MMAs per edge, 7/16
+// of the A rows padding); with tcgen05 the MMAs cost one thread 8 instructions per edge and the kernel is bound by
+// L2 -> SM tile traffic and the blend.
 //
-// Edges whose windows do not fit 12x12 px (patch magnified > ~2x between frames) take a per-warp direct-gather path
+// Edges whose windows do not fit 12x12 px (patch magnified > ~2x between frames) take a direct-gather path
 // inside the same kernel (same arithmetic, no tile); edges with an out-of-range index produce zeros and set the status.
 #include <cuda.h>
 #include <mma.h>
