@@ -77,6 +77,22 @@ int wv_corr_forward(const void* fmap1, const void* fmap2, const float* coords, c
                     int n1, int n2, int H2, int W2, int radius, void* workspace, size_t workspace_bytes,
                     int* status, wv_stream_t stream);
 
+/* DPVO.corr (dpvo/dpvo.py:325-333) as ONE call: both pyramid levels of every edge and the final
+ * torch.stack([corr1, corr2], -1).view(1, E, -1), replacing 2 x wv_corr_forward + the stack (a read of both
+ * volumes and a write of the stacked one).  Tracker configuration only (WV_F16, C = 128, 3x3 patches, radius 3):
+ * wv_corr_stacked_workspace_bytes returns 0 for anything else and the caller composes the two-call form.
+ *   fmap2_l0 [B][n2][C][H0][W0], fmap2_l1 [B][n2][C][H1][W1] (the same ring slots jj at both levels),
+ *   level l samples at coords * cmul_l (the reference divides by 1 and 4: pass 1.0f and 0.25f -- exact),
+ *   out [B][E][2r+1][2r+1][PH][PW][2] (dtype): [...][0] = level 0, [...][1] = level 1.
+ * workspace is required.  status may be NULL. */
+size_t wv_corr_stacked_workspace_bytes(int dtype, int B, int E, int C, int PH, int PW, int n1, int n2,
+                                       int H0, int W0, int H1, int W1, int radius);
+int wv_corr_forward_stacked(const void* fmap1, const void* fmap2_l0, const void* fmap2_l1,
+                            const float* coords, float cmul0, float cmul1, const int64_t* ii,
+                            const int64_t* jj, void* out, int dtype, int B, int E, int C, int PH, int PW,
+                            int n1, int n2, int H0, int W0, int H1, int W1, int radius, void* workspace,
+                            size_t workspace_bytes, int* status, wv_stream_t stream);
+
 /* cuda_corr.backward -- replaces corr_cuda_backward + corr_backward_kernel (correlation_kernel.cu:139-190, 236-286).
  *   grad [B][E][2r+1][2r+1][PH][PW] fp32 (same permuted order as `out`), fmap1_grad / fmap2_grad fp32
  *   accumulators shaped like fmap1 / fmap2, ZEROED BY THE CALLER; the binding casts them to dtype. */

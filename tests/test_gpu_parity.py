@@ -354,6 +354,79 @@ def test_corr_tiled_batch_and_few_edges(syn):
     _check_tiled(g, f, co, rng.integers(0, n1, E).astype(np.int64), rng.integers(0, n2, E).astype(np.int64))
 
 
+def _check_stacked(g, f0, f1, co, ii, jj):
+    """two-level kernel vs the two-call form (same tiles, same arithmetic: bit-identical) and vs the fp64 oracle"""
+    cc, _ = pkg().native_modules()
+    altcorr = importlib.import_module(PKG + ".altcorr.correlation")
+    gd, f0d, f1d, cod, iid, jjd = dev(g, torch.float16), dev(f0, torch.float16), dev(f1, torch.float16), dev(co), dev(ii), dev(jj)
+    st = altcorr.corr_stacked(gd, (f0d, f1d), cod, iid, jjd, 3)
+    B, E = co.shape[0], co.shape[1]
+    assert st.shape == (B, E, 882) and st.dtype == torch.float16
+    with _tiled(True):
+        c0, = cc.forward(gd, f0d, cod / 1, iid, jjd, 3)
+        c1, = cc.forward(gd, f1d, cod / 4, iid, jjd, 3)
+    two = torch.stack([c0, c1], -1).view(B, E, -1)   # dpvo/dpvo.py:333
+    torch.cuda.synchronize()
+    assert torch.equal(st, two)
+    g16, f016, f116 = (torch.from_numpy(x).half().float().numpy() for x in (g, f0, f1))
+    t0 = oracle.corr_forward(g16, f016, co, ii, jj, 3, mode=oracle.F64)
+    t1 = oracle.corr_forward(g16, f116, (co / 4).astype(np.float32), ii, jj, 3, mode=oracle.F64)
+    truth = np.stack([t0, t1], -1).reshape(B, E, -1)
+    scale = max(1.0, np.abs(truth).max())
+    assert np.abs(st.float().cpu().numpy() - truth).max() <= 2.0 ** -10 * scale
+    return st
+
+
+def test_corr_stacked_tracker_workload(syn):
+    w = syn.make_corr_workload(seed=2, M=8, pmem=12, n_frames=14, ht=24, wd=32, C=128, lifetime=6, removal=9, oob_frac=0.15)
+    st = _check_stacked(w["gmap"], w["fmap0"], w["fmap1"], w["coords"], w["ii1"], w["jj1"])
+    assert st.float().abs().max() > 0.1
+
+
+def test_corr_stacked_magnified_batch_and_few_edges(syn):
+    """small / large / direct-gather windows at both levels, B = 2, odd maps, fewer edges than pipelines"""
+    rng = np.random.default_rng(17)
+    n1, n2, E = 40, 5, 500
+    gy, gx = np.meshgrid(np.arange(-1, 2), np.arange(-1, 2), indexing="ij")
+    for B, H0, W0, H1, W1, E in ((1, 46, 62, 11, 15, 500), (2, 24, 32, 6, 8, 3)):
+        g = (0.25 * rng.standard_normal((B, n1, 128, 3, 3))).astype(np.float32)
+        f0 = (0.25 * rng.standard_normal((B, n2, 128, H0, W0))).astype(np.float32)
+        f1 = (0.25 * rng.standard_normal((B, n2, 128, H1, W1))).astype(np.float32)
+        ctr = np.stack([rng.uniform(-8, W0 + 8, (B, E)), rng.uniform(-8, H0 + 8, (B, E))], -1)
+        sp = rng.uniform(1.0, 14.0, (B, E))        # up to 3.5 px spacing at level 1, far beyond the tiles at level 0
+        co = np.stack([ctr[..., 0, None, None] + sp[..., None, None] * gx, ctr[..., 1, None, None] + sp[..., None, None] * gy], 2).astype(np.float32)
+        ii = rng.integers(0, n1, E).astype(np.int64); jj = rng.integers(0, n2, E).astype(np.int64)
+        if E > 200:
+            ii[100:130] = ii[100]
+        _check_stacked(g, f0, f1, co, ii, jj)
+
+
+def test_corr_stacked_composed_form_and_bad_index(golden):
+    """fp32 maps take the composed two-call form (same result layout); a bad index raises from the fused call"""
+    cc, _ = pkg().native_modules()
+    altcorr = importlib.import_module(PKG + ".altcorr.correlation")
+    rng = np.random.default_rng(19)
+    g = dev((0.25 * rng.standard_normal((1, 4, 128, 3, 3))).astype(np.float32))
+    f0 = dev((0.25 * rng.standard_normal((1, 2, 128, 24, 32))).astype(np.float32))
+    f1 = dev((0.25 * rng.standard_normal((1, 2, 128, 6, 8))).astype(np.float32))
+    co = dev(np.full((1, 3, 2, 3, 3), 10.25, np.float32))
+    ii, jj = torch.tensor([0, 1, 2], device="cuda"), torch.tensor([0, 1, 1], device="cuda")
+    comp = altcorr.corr_stacked(g, (f0, f1), co, ii, jj, 3)
+    fused = altcorr.corr_stacked(g.half(), (f0.half(), f1.half()), co, ii, jj, 3)
+    assert comp.shape == fused.shape == (1, 3, 882)
+    assert (comp - fused.float()).abs().max() < 2e-2
+    empty = altcorr.corr_stacked(g.half(), (f0.half(), f1.half()), co[:, :0], ii[:0], jj[:0], 3)
+    assert empty.shape == (1, 0, 882)
+    os.environ["WVB200_CHECK_INDICES"] = "1"
+    try:
+        with pytest.raises(IndexError):
+            cc.forward_stacked(g.half(), f0.half(), f1.half(), co, torch.tensor([0, 9, 2], device="cuda"), jj, 3, 1.0, 4.0)
+    finally:
+        del os.environ["WVB200_CHECK_INDICES"]
+    with pytest.raises(RuntimeError):
+        cc.forward_stacked(g.half(), f0.half(), f1.half(), co, ii, jj, 3, 1.0, 3.0)
+
+
 def test_corr_tiled_bad_index_and_nonfinite(golden):
     cc, _ = pkg().native_modules()
     rng = np.random.default_rng(9)

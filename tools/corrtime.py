@@ -22,3 +22,18 @@ def t(fm, co, n=10):
 if len(sys.argv) > 1 and sys.argv[1] == "generic":
     os.environ["WVB200_CORR_TILED"] = "0"
 print("L0 %.4f ms  L1 %.4f ms" % (t(f0, c0), t(f1, c1)), flush=True)
+# the two-level stacked form (DPVO.corr in one call) next to the two-call form + torch.stack
+altcorr = importlib.import_module("wild-video-3d-reconstruction_b200.altcorr.correlation")
+def t2(fn, n=10):
+    ts = []
+    for i in range(n + 3):
+        flush.fill_(1)
+        a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
+        a.record(); fn(); b.record(); torch.cuda.synchronize()
+        if i >= 3: ts.append(a.elapsed_time(b))
+    return np.median(ts)
+E = ii.numel()
+two = lambda: torch.stack([cc.forward(g, f0, c0 / 1, ii, jj, 3)[0], cc.forward(g, f1, c0 / 4, ii, jj, 3)[0]], -1).view(1, E, -1)
+one = lambda: altcorr.corr_stacked(g, (f0, f1), c0, ii, jj, 3)
+assert torch.equal(two(), one())
+print("DPVO.corr: two calls + stack %.4f ms   stacked kernel %.4f ms" % (t2(two), t2(one)), flush=True)

@@ -57,3 +57,24 @@ def patchify(net, coords, radius, mode='bilinear'):
 
 def corr(fmap1, fmap2, coords, ii, jj, radius=1, dropout=1):
     return CorrLayer.apply(fmap1, fmap2, coords, ii, jj, radius, dropout)
+
+
+def corr_stacked(fmap1, pyramid, coords, ii, jj, radius=3, divs=(1, 4)):
+    """DPVO.corr (dpvo/dpvo.py:325-333) as one call:
+
+        torch.stack([corr(fmap1, pyramid[0], coords / divs[0], ii, jj, radius),
+                     corr(fmap1, pyramid[1], coords / divs[1], ii, jj, radius)], -1).view(B, E, -1)
+
+    The tracker's configuration (half maps, C = 128, 3x3 patches, radius 3, no gradient) runs both levels of every edge in one
+    kernel that writes the stacked layout directly; anything else is composed from `corr` exactly as the reference does."""
+    f0, f1l = pyramid
+    B, E = coords.shape[0], coords.shape[1]
+    fused = (fmap1.dtype == torch.float16 and f0.dtype == torch.float16 and f1l.dtype == torch.float16 and radius == 3
+             and fmap1.shape[2] == 128 and tuple(fmap1.shape[3:]) == (3, 3) and f0.shape[1] == f1l.shape[1]
+             and all(d > 0 and (d & (d - 1)) == 0 for d in (int(divs[0]), int(divs[1]))) and int(divs[0]) == divs[0] and int(divs[1]) == divs[1]
+             and not (torch.is_grad_enabled() and any(t.requires_grad for t in (fmap1, f0, f1l))))
+    if fused:
+        return cuda_corr.forward_stacked(fmap1, f0, f1l, coords, ii, jj, radius, float(divs[0]), float(divs[1]))[0]
+    c0 = corr(fmap1, f0, coords / divs[0], ii, jj, radius)
+    c1 = corr(fmap1, f1l, coords / divs[1], ii, jj, radius)
+    return torch.stack([c0, c1], -1).view(B, E, -1)

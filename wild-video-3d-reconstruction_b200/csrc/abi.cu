@@ -33,6 +33,10 @@ int patchify_backward(const void*, const float*, float*, int, int, int, int, int
 // corr_sm100.cu
 bool corr_tiled_supported(int dtype, int B, int E, int C, int PH, int PW, int n1, int n2, int H2, int W2, int R);
 size_t corr_tiled_workspace_bytes(int dtype, int B, int E, int C, int PH, int PW, int n1, int n2, int H2, int W2, int R);
+bool corr_stacked_supported(int dtype, int B, int E, int C, int PH, int PW, int n1, int n2, int H0, int W0, int H1, int W1, int R);
+size_t corr_stacked_workspace_bytes(int B, int n1, int n2, int H0, int W0, int H1, int W1);
+int corr_forward_stacked(const void*, const void*, const void*, const float*, float, float, const int64_t*, const int64_t*, void*, int,
+                         int, int, int, int, int, int, int, int, int, int, int, int, void*, size_t, int*, cudaStream_t);
 int corr_forward_tiled(const void*, const void*, const float*, const int64_t*, const int64_t*, void*, int, int, int, int,
                        int, int, int, int, int, int, int, void*, size_t, int*, cudaStream_t);
 // ba_window.cu
@@ -140,6 +144,25 @@ int wv_corr_forward(const void* fmap1, const void* fmap2, const float* coords, c
     if (rc != WV_EUNSUPPORTED) return rc;  // e.g. a misaligned base pointer: the generic kernel takes any
   }
   return corr_forward_generic(fmap1, fmap2, coords, ii, jj, out, dtype, B, E, C, PH, PW, n1, n2, H2, W2, radius, status, st);
+}
+
+size_t wv_corr_stacked_workspace_bytes(int dtype, int B, int E, int C, int PH, int PW, int n1, int n2, int H0, int W0, int H1,
+                                       int W1, int radius) {
+  if (!corr_stacked_supported(dtype, B, E, C, PH, PW, n1, n2, H0, W0, H1, W1, radius)) return 0;
+  return corr_stacked_workspace_bytes(B, n1, n2, H0, W0, H1, W1);
+}
+
+int wv_corr_forward_stacked(const void* fmap1, const void* fmap2_l0, const void* fmap2_l1, const float* coords, float cmul0,
+                            float cmul1, const int64_t* ii, const int64_t* jj, void* out, int dtype, int B, int E, int C, int PH,
+                            int PW, int n1, int n2, int H0, int W0, int H1, int W1, int radius, void* workspace,
+                            size_t workspace_bytes, int* status, wv_stream_t stream) {
+  if (!corr_args_ok(fmap1, fmap2_l0, coords, ii, jj, dtype, B, E, C, PH, PW, n1, n2, H0, W0, radius) || H1 <= 0 || W1 <= 0)
+    return WV_EINVAL;
+  if (!(cmul0 == cmul0) || !(cmul1 == cmul1)) return WV_EINVAL;
+  if ((int64_t)B * E == 0) return WV_OK;
+  if (!out || !fmap2_l1 || !workspace) return WV_EINVAL;
+  return corr_forward_stacked(fmap1, fmap2_l0, fmap2_l1, coords, cmul0, cmul1, ii, jj, out, dtype, B, E, C, PH, PW, n1, n2, H0, W0,
+                              H1, W1, radius, workspace, workspace_bytes, status, as_stream(stream));
 }
 
 int wv_corr_backward(const void* fmap1, const void* fmap2, const float* coords, const int64_t* ii, const int64_t* jj,

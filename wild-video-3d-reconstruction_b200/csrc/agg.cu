@@ -1,0 +1,330 @@
+// SoftAgg of the update operator (dpvo/blocks.py:31-48, called twice per update() from dpvo/net.py:88-89):
+//
+//     _, jx = torch.unique(ix, return_inverse=True)
+//     w = torch_scatter.scatter_softmax(g(x), jx, dim=1)
+//     y = torch_scatter.scatter_sum(f(x) * w, jx, dim=1)
+//
+// The reference runs a device sort + host sync (unique), then scatter_max, gather, sub, exp, scatter_sum, gather, div, mul and a
+// second scatter_sum: ten passes over [E][384] tensors and two atomics-based scatters (torch-scatter 2.1.2, composite/softmax.py).
+// Here:
+//   group plan   the inverse index without a sort: presence bitmap over the key range -> popcount prefix -> jx = rank of the key
+//                among the present keys (== torch.unique's sorted order), then member lists per group in ascending edge order
+//                (counting fill + a per-group rank sort), so that the reduction order is fixed: results are deterministic.
+//   soft_agg     ONE pass over f(x) and g(x): a thread owns 16 bytes of channels of one group and walks the group's members twice
+//                (max, then exp / sum / weighted sum, the second walk hits L1/L2), fp32 arithmetic, one rounding at the end.
+//                HBM-bound: algorithmic bytes = 2 * E * D * sizeof(T) read + G * D * sizeof(T) written.
+#include "wv_common.cuh"
+
+namespace wv {
+
+namespace {
+
+constexpr int kScanThreads = 1024, kScanPer = 4, kScanTile = kScanThreads * kScanPer;
+
+struct PopcOp {
+  const uint32_t* w;
+  __device__ __forceinline__ int operator()(long long i) const { return __popc(w[i]); }
+};
+struct CountOp {
+  const int* c;
+  long long n;  // entries beyond n read as 0 (the scan runs one past the end to produce the total)
+  __device__ __forceinline__ int operator()(long long i) const { return i < n ? c[i] : 0; }
+};
+
+__device__ __forceinline__ int block_exclusive_scan(int v, int* total) {
+  __shared__ int warp_sums[32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int incl = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+  if (lane == 31) warp_sums[warp] = incl;
+  __syncthreads();
+  if (warp == 0) {
+    int s = warp_sums[lane], si = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, si, o); if (lane >= o) si += t; }
+    warp_sums[lane] = si - s;
+    if (lane == 31 && total) *total = si;
+  }
+  __syncthreads();
+  const int r = warp_sums[warp] + incl - v;
+  __syncthreads();
+  return r;
+}
+
+// phase A: per-tile sums
+template <typename Op>
+__global__ void __launch_bounds__(kScanThreads) scan_tile_sums(Op op, long long n, int* tile_sums) {
+  const long long base = (long long)blockIdx.x * kScanTile + (long long)threadIdx.x * kScanPer;
+  int v = 0;
+#pragma unroll
+  for (int i = 0; i < kScanPer; i++) if (base + i < n) v += op(base + i);
+  __shared__ int tot;
+  block_exclusive_scan(v, &tot);
+  if (threadIdx.x == 0) tile_sums[blockIdx.x] = tot;
+}
+
+// phase B: one block turns the tile sums into exclusive tile offsets (any number of tiles: chunks of 1024 with a carry)
+__global__ void __launch_bounds__(kScanThreads) scan_tile_offsets(int* tile_sums, int n_tiles, int* grand_total) {
+  __shared__ int tot;
+  int carry = 0;
+  for (int c0 = 0; c0 < n_tiles; c0 += kScanThreads) {
+    const int i = c0 + threadIdx.x;
+    const int v = i < n_tiles ? tile_sums[i] : 0;
+    const int ex = block_exclusive_scan(v, &tot);
+    if (i < n_tiles) tile_sums[i] = carry + ex;
+    carry += tot;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0 && grand_total) *grand_total = carry;
+}
+
+// phase C: exclusive prefix of every element
+template <typename Op>
+__global__ void __launch_bounds__(kScanThreads) scan_apply(Op op, long long n, const int* tile_offsets, int* out) {
+  const long long base = (long long)blockIdx.x * kScanTile + (long long)threadIdx.x * kScanPer;
+  int v[kScanPer], s = 0;
+#pragma unroll
+  for (int i = 0; i < kScanPer; i++) { v[i] = base + i < n ? op(base + i) : 0; s += v[i]; }
+  int ex = block_exclusive_scan(s, nullptr) + tile_offsets[blockIdx.x];
+#pragma unroll
+  for (int i = 0; i < kScanPer; i++) { if (base + i < n) out[base + i] = ex; ex += v[i]; }
+}
+
+template <typename Op>
+int exclusive_scan(Op op, long long n, int* out, int* tile_sums, int* grand_total, cudaStream_t st) {
+  const int n_tiles = (int)((n + kScanTile - 1) / kScanTile);
+  if (n_tiles == 0) return WV_OK;
+  scan_tile_sums<<<n_tiles, kScanThreads, 0, st>>>(op, n, tile_sums);
+  WV_LAUNCH_CHECK();
+  scan_tile_offsets<<<1, kScanThreads, 0, st>>>(tile_sums, n_tiles, grand_total);
+  WV_LAUNCH_CHECK();
+  scan_apply<<<n_tiles, kScanThreads, 0, st>>>(op, n, tile_sums, out);
+  WV_LAUNCH_CHECK();
+  return WV_OK;
+}
+
+__global__ void mark_keys(const int64_t* __restrict__ keys, long long E, int64_t key_min, int64_t range, uint32_t* bitmap, int* status) {
+  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < E; e += (long long)gridDim.x * blockDim.x) {
+    const int64_t k = keys[e] - key_min;
+    if (k < 0 || k >= range) { set_status(status, WV_STATUS_BAD_INDEX); continue; }
+    const uint32_t bit = 1u << (k & 31);
+    uint32_t* w = bitmap + (k >> 5);
+    if (!(*w & bit)) atomicOr(w, bit);   // most keys repeat: skip the atomic once the bit is visible
+  }
+}
+
+__global__ void rank_keys(const int64_t* __restrict__ keys, long long E, int64_t key_min, int64_t range, const uint32_t* __restrict__ bitmap,
+                          const int* __restrict__ word_prefix, int64_t* __restrict__ jx, int* counts) {
+  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < E; e += (long long)gridDim.x * blockDim.x) {
+    const int64_t k = keys[e] - key_min;
+    if (k < 0 || k >= range) { jx[e] = 0; continue; }   // flagged by mark_keys; member of no group
+    const int g = word_prefix[k >> 5] + __popc(bitmap[k >> 5] & ((1u << (k & 31)) - 1u));
+    jx[e] = g;
+    atomicAdd(counts + g, 1);
+  }
+}
+
+__global__ void fill_members(const int64_t* __restrict__ keys, long long E, int64_t key_min, int64_t range, const int64_t* __restrict__ jx,
+                             const int* __restrict__ offsets, int* counts, int* members) {
+  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < E; e += (long long)gridDim.x * blockDim.x) {
+    const int64_t k = keys[e] - key_min;
+    if (k < 0 || k >= range) continue;
+    const int g = (int)jx[e];
+    members[offsets[g] + atomicSub(counts + g, 1) - 1] = (int)e;   // any order inside the group; sorted next
+  }
+}
+
+// one warp per group: members into ascending edge order (rank sort; groups are a few dozen edges)
+__global__ void sort_members(const int* __restrict__ offsets, const int* __restrict__ n_groups, const int* __restrict__ members, int* __restrict__ order) {
+  const int lane = threadIdx.x & 31;
+  const int G = *n_groups;
+  for (int g = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); g < G; g += gridDim.x * (blockDim.x >> 5)) {
+    const int lo = offsets[g], n = offsets[g + 1] - lo;
+    if (n <= 32) {
+      const int mine = lane < n ? members[lo + lane] : 0x7fffffff;
+      int rank = 0;
+#pragma unroll
+      for (int o = 0; o < 32; o++) rank += __shfl_sync(0xffffffffu, mine, o) < mine ? 1 : 0;
+      if (lane < n) order[lo + rank] = mine;
+    } else {
+      for (int i = lane; i < n; i += 32) {
+        const int mine = members[lo + i];
+        int rank = 0;
+        for (int j = 0; j < n; j++) rank += members[lo + j] < mine ? 1 : 0;
+        order[lo + rank] = mine;
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// y[b][g][c] = sum_{e in g} f[b][e][c] * exp(s[b][e][c] - max_g) / sum_{e in g} exp(s[b][e][c] - max_g)
+// ---------------------------------------------------------------------------------------------------
+template <typename T, int V> struct Vec;
+template <> struct Vec<__half, 8> {
+  uint4 r;
+  __device__ __forceinline__ void load(const __half* p) { r = *reinterpret_cast<const uint4*>(p); }
+  __device__ __forceinline__ void get(float* o) const {
+    const __half2* h = reinterpret_cast<const __half2*>(&r);
+#pragma unroll
+    for (int i = 0; i < 4; i++) { const float2 f = __half22float2(h[i]); o[2 * i] = f.x; o[2 * i + 1] = f.y; }
+  }
+  static __device__ __forceinline__ void store(__half* p, const float* v) {
+    uint4 w;
+    __half2* h = reinterpret_cast<__half2*>(&w);
+#pragma unroll
+    for (int i = 0; i < 4; i++) h[i] = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
+    *reinterpret_cast<uint4*>(p) = w;
+  }
+};
+template <> struct Vec<float, 4> {
+  float4 r;
+  __device__ __forceinline__ void load(const float* p) { r = *reinterpret_cast<const float4*>(p); }
+  __device__ __forceinline__ void get(float* o) const { o[0] = r.x; o[1] = r.y; o[2] = r.z; o[3] = r.w; }
+  static __device__ __forceinline__ void store(float* p, const float* v) { *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]); }
+};
+template <typename T> struct Vec<T, 1> {
+  T r;
+  __device__ __forceinline__ void load(const T* p) { r = *p; }
+  __device__ __forceinline__ void get(float* o) const { o[0] = to_f32<T>(r); }
+  static __device__ __forceinline__ void store(T* p, const float* v) { *p = from_f32<T>(v[0]); }
+};
+
+template <typename T, int V>
+__global__ void __launch_bounds__(256) soft_agg_kernel(const T* __restrict__ fx, const T* __restrict__ gx, const int* __restrict__ order,
+                                                       const int* __restrict__ offsets, const int* __restrict__ n_groups, T* __restrict__ y,
+                                                       int B, long long E, int D, long long Gcap) {
+  const int tpg = D / V;                                 // threads per group row
+  const int G = (int)min((long long)*n_groups, Gcap);
+  const long long total = (long long)B * G * tpg;
+  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(t % tpg) * V;
+    const long long bg = t / tpg;
+    const int g = (int)(bg % G), b = (int)(bg / G);
+    const int lo = offsets[g], hi = offsets[g + 1];
+    const T* fb = fx + ((long long)b * E) * D + c;
+    const T* gb = gx + ((long long)b * E) * D + c;
+    float mx[V], s[V], a[V];
+#pragma unroll
+    for (int i = 0; i < V; i++) { mx[i] = -INFINITY; s[i] = 0.f; a[i] = 0.f; }
+    // walk 1: per-channel maximum of the scores
+    int m = lo;
+    for (; m + 4 <= hi; m += 4) {
+      Vec<T, V> r[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) r[u].load(gb + (long long)order[m + u] * D);
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        float v[V];
+        r[u].get(v);
+#pragma unroll
+        for (int i = 0; i < V; i++) mx[i] = fmaxf(mx[i], v[i]);
+      }
+    }
+    for (; m < hi; m++) {
+      Vec<T, V> r;
+      r.load(gb + (long long)order[m] * D);
+      float v[V];
+      r.get(v);
+#pragma unroll
+      for (int i = 0; i < V; i++) mx[i] = fmaxf(mx[i], v[i]);
+    }
+    // walk 2: weights, their sum, and the weighted sum of f (ascending edge order: fixed summation order)
+    m = lo;
+    for (; m + 2 <= hi; m += 2) {
+      Vec<T, V> rg[2], rf[2];
+#pragma unroll
+      for (int u = 0; u < 2; u++) { const long long e = order[m + u]; rg[u].load(gb + e * D); rf[u].load(fb + e * D); }
+#pragma unroll
+      for (int u = 0; u < 2; u++) {
+        float v[V], f[V];
+        rg[u].get(v); rf[u].get(f);
+#pragma unroll
+        for (int i = 0; i < V; i++) { const float w = expf(v[i] - mx[i]); s[i] += w; a[i] = fmaf(f[i], w, a[i]); }
+      }
+    }
+    for (; m < hi; m++) {
+      const long long e = order[m];
+      Vec<T, V> rg, rf;
+      rg.load(gb + e * D); rf.load(fb + e * D);
+      float v[V], f[V];
+      rg.get(v); rf.get(f);
+#pragma unroll
+      for (int i = 0; i < V; i++) { const float w = expf(v[i] - mx[i]); s[i] += w; a[i] = fmaf(f[i], w, a[i]); }
+    }
+    float o[V];
+#pragma unroll
+    for (int i = 0; i < V; i++) o[i] = a[i] / s[i];
+    Vec<T, V>::store(y + ((long long)b * Gcap + g) * D + c, o);
+  }
+}
+
+inline size_t al256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+struct PlanWs {
+  uint32_t* bitmap; int* word_prefix; int* tile_sums; int* counts; int* members;
+  size_t bytes;
+};
+
+PlanWs carve(void* ws, long long E, long long range) {
+  const long long W = (range + 31) / 32;
+  const long long tiles = (max(W, E + 1) + kScanTile - 1) / kScanTile + 1;
+  PlanWs p;
+  char* c = reinterpret_cast<char*>((reinterpret_cast<uintptr_t>(ws) + 255) & ~(uintptr_t)255);
+  size_t off = 0;
+  p.bitmap = reinterpret_cast<uint32_t*>(c + off); off += al256((size_t)W * 4);
+  p.counts = reinterpret_cast<int*>(c + off); off += al256((size_t)(E + 1) * 4);   // adjacent to the bitmap: one memset clears both
+  p.word_prefix = reinterpret_cast<int*>(c + off); off += al256((size_t)W * 4);
+  p.tile_sums = reinterpret_cast<int*>(c + off); off += al256((size_t)tiles * 4);
+  p.members = reinterpret_cast<int*>(c + off); off += al256((size_t)(E + 1) * 4);
+  p.bytes = off + 256;
+  return p;
+}
+
+}  // namespace
+
+size_t group_plan_workspace_bytes(long long E, long long range) { return carve(nullptr, E, range).bytes; }
+
+int group_plan(const int64_t* keys, long long E, int64_t key_min, long long range, int64_t* jx, int* order, int* offsets, int* n_groups,
+               void* workspace, size_t workspace_bytes, int* status, cudaStream_t st) {
+  if (workspace_bytes < group_plan_workspace_bytes(E, range)) return WV_EWORKSPACE;
+  const PlanWs p = carve(workspace, E, range);
+  const long long W = (range + 31) / 32;
+  WV_CUDA_TRY(cudaMemsetAsync(p.bitmap, 0, (size_t)(reinterpret_cast<char*>(p.word_prefix) - reinterpret_cast<char*>(p.bitmap)), st));
+  const int tb = 256;
+  const int grid = (int)min((long long)sm_count() * 8, (E + tb - 1) / tb);
+  mark_keys<<<grid, tb, 0, st>>>(keys, E, key_min, range, p.bitmap, status);
+  WV_LAUNCH_CHECK();
+  int rc = exclusive_scan(PopcOp{p.bitmap}, W, p.word_prefix, p.tile_sums, n_groups, st);
+  if (rc != WV_OK) return rc;
+  rank_keys<<<grid, tb, 0, st>>>(keys, E, key_min, range, p.bitmap, p.word_prefix, jx, p.counts);
+  WV_LAUNCH_CHECK();
+  rc = exclusive_scan(CountOp{p.counts, E}, E + 1, offsets, p.tile_sums, nullptr, st);   // offsets[G .. E] = number of grouped edges
+  if (rc != WV_OK) return rc;
+  fill_members<<<grid, tb, 0, st>>>(keys, E, key_min, range, jx, offsets, p.counts, p.members);
+  WV_LAUNCH_CHECK();
+  sort_members<<<(int)min((long long)sm_count() * 8, (E + 7) / 8), 256, 0, st>>>(offsets, n_groups, p.members, order);
+  WV_LAUNCH_CHECK();
+  return WV_OK;
+}
+
+int soft_agg_forward(const void* fx, const void* gx, const int* order, const int* offsets, const int* n_groups, void* y, int dtype,
+                     int B, long long E, int D, long long Gcap, cudaStream_t st) {
+  const bool al16 = ((reinterpret_cast<uintptr_t>(fx) | reinterpret_cast<uintptr_t>(gx) | reinterpret_cast<uintptr_t>(y)) & 15) == 0;
+  const int V = dtype == WV_F16 ? ((D % 8 == 0 && al16) ? 8 : 1) : ((D % 4 == 0 && al16) ? 4 : 1);
+  const long long total = (long long)B * Gcap * (D / V);
+  if (total == 0) return WV_OK;
+  const int grid = (int)min((total + 255) / 256, (long long)sm_count() * 32);
+  if (dtype == WV_F16) {
+    if (V == 8) soft_agg_kernel<__half, 8><<<grid, 256, 0, st>>>((const __half*)fx, (const __half*)gx, order, offsets, n_groups, (__half*)y, B, E, D, Gcap);
+    else soft_agg_kernel<__half, 1><<<grid, 256, 0, st>>>((const __half*)fx, (const __half*)gx, order, offsets, n_groups, (__half*)y, B, E, D, Gcap);
+  } else {
+    if (V == 4) soft_agg_kernel<float, 4><<<grid, 256, 0, st>>>((const float*)fx, (const float*)gx, order, offsets, n_groups, (float*)y, B, E, D, Gcap);
+    else soft_agg_kernel<float, 1><<<grid, 256, 0, st>>>((const float*)fx, (const float*)gx, order, offsets, n_groups, (float*)y, B, E, D, Gcap);
+  }
+  WV_LAUNCH_CHECK();
+  return WV_OK;
+}
+
+}  // namespace wv

@@ -2,6 +2,8 @@
 // dpvo/altcorr/correlation.cpp:57-63, so dpvo/altcorr/correlation.py:2 imports it unchanged.
 #include "bind_common.h"
 
+#include <cmath>
+
 using namespace wvbind;
 
 namespace {
@@ -38,6 +40,45 @@ std::vector<torch::Tensor> corr_forward(torch::Tensor fmap1, torch::Tensor fmap2
            "cuda_corr.forward");
   if (env_flag("WVB200_CHECK_INDICES")) raise_on_status(f1.device(), "cuda_corr.forward");
   if (in_dtype == torch::kDouble) out = out.to(torch::kDouble);
+  return {out};
+}
+
+// DPVO.corr (dpvo/dpvo.py:325-333) in one call: returns [B, E, T*T*PH*PW*2] == torch.stack([corr1, corr2], -1).view(B, E, -1).
+// div0 / div1 are the reference's coordinate divisors (1 and 4).  Raises for configurations the two-level kernel does not cover;
+// the Python mirror (altcorr.corr_stacked) composes those from forward().
+std::vector<torch::Tensor> corr_forward_stacked(torch::Tensor fmap1, torch::Tensor fmap2_l0, torch::Tensor fmap2_l1,
+                                                torch::Tensor coords, torch::Tensor ii, torch::Tensor jj, int radius, double div0,
+                                                double div1) {
+  check_cuda(fmap1, "fmap1"); check_cuda(fmap2_l0, "fmap2_l0"); check_cuda(fmap2_l1, "fmap2_l1"); check_cuda(coords, "coords");
+  check_cuda(ii, "ii"); check_cuda(jj, "jj");
+  TORCH_CHECK(fmap1.dim() == 5 && fmap2_l0.dim() == 5 && fmap2_l1.dim() == 5 && coords.dim() == 5, "corr: fmap1/fmap2/coords must be 5-d");
+  TORCH_CHECK(fmap1.scalar_type() == torch::kHalf && fmap2_l0.scalar_type() == torch::kHalf && fmap2_l1.scalar_type() == torch::kHalf,
+              "corr_stacked: half maps only");
+  TORCH_CHECK(coords.scalar_type() == torch::kFloat, "corr: coords must be float32");
+  TORCH_CHECK(ii.scalar_type() == torch::kLong && jj.scalar_type() == torch::kLong, "corr: ii/jj must be int64");
+  int e0 = 0, e1 = 0;
+  TORCH_CHECK(std::frexp(div0, &e0) == 0.5 && std::frexp(div1, &e1) == 0.5, "corr_stacked: divisors must be powers of two");
+  c10::cuda::CUDAGuard guard(fmap1.device());
+  torch::Tensor f1 = fmap1.contiguous(), f20 = fmap2_l0.contiguous(), f21 = fmap2_l1.contiguous(), co = coords.contiguous(),
+                iic = ii.contiguous(), jjc = jj.contiguous();
+  const int B = co.size(0), E = co.size(1), PH = co.size(3), PW = co.size(4);
+  const int n1 = f1.size(1), C = f1.size(2), n2 = f20.size(1), H0 = f20.size(3), W0 = f20.size(4), H1 = f21.size(3), W1 = f21.size(4);
+  TORCH_CHECK(co.size(2) == 2 && f1.size(3) == PH && f1.size(4) == PW && f20.size(2) == C && f21.size(2) == C && f21.size(1) == n2 &&
+                  f1.size(0) == B && f20.size(0) == B && f21.size(0) == B,
+              "corr_stacked: inconsistent shapes");
+  TORCH_CHECK(iic.numel() == E && jjc.numel() == E, "corr: ii/jj must have one entry per edge");
+  const int T = 2 * radius + 1;
+  const size_t wsb = wv_corr_stacked_workspace_bytes(WV_F16, B, E, C, PH, PW, n1, n2, H0, W0, H1, W1, radius);
+  torch::Tensor out = torch::empty({B, E, (int64_t)T * T * PH * PW * 2}, f1.options());
+  if (E == 0) return {out};
+  TORCH_CHECK(wsb > 0, "corr_stacked: configuration not covered by the two-level kernel");
+  torch::Tensor ws = torch::empty({(int64_t)wsb}, torch::dtype(torch::kUInt8).device(f1.device()));
+  check_rc(wv_corr_forward_stacked(f1.data_ptr(), f20.data_ptr(), f21.data_ptr(), co.data_ptr<float>(), (float)(1.0 / div0),
+                                   (float)(1.0 / div1), iic.data_ptr<int64_t>(), jjc.data_ptr<int64_t>(), out.data_ptr(), WV_F16, B, E,
+                                   C, PH, PW, n1, n2, H0, W0, H1, W1, radius, ws.data_ptr(), wsb,
+                                   status_word(f1.device()).data_ptr<int>(), current_stream()),
+           "cuda_corr.forward_stacked");
+  if (env_flag("WVB200_CHECK_INDICES")) raise_on_status(f1.device(), "cuda_corr.forward_stacked");
   return {out};
 }
 
@@ -97,6 +138,7 @@ std::vector<torch::Tensor> patchify_backward(torch::Tensor net, torch::Tensor co
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.def("forward", &corr_forward, "CORR forward");
   m.def("backward", &corr_backward, "CORR backward");
+  m.def("forward_stacked", &corr_forward_stacked, "both pyramid levels, stacked (DPVO.corr)");  // beyond the reference's table
   m.def("patchify_forward", &patchify_forward, "PATCHIFY forward");
   m.def("patchify_backward", &patchify_backward, "PATCHIFY backward");
 }

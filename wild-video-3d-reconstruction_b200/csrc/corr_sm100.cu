@@ -225,9 +225,17 @@ struct CorrParams {
   const float* coords;  // [B][E][2][3][3]
   const int64_t* ii;
   const int64_t* jj;
-  __half* out;          // [B][E][7][7][3][3]
+  __half* out;          // [B][E][7][7][3][3]; two-level form: [B][E][7][7][3][3][2]
   int B, E, n1, n2, H, W;
   int* status;
+  // second pyramid level of the two-level (stacked) form: its own map ring, extent and coordinate multiplier
+  const __half* fmap2_l1;
+  int H1, W1;
+  float cmul0, cmul1;
+};
+
+struct CorrMaps {  // [level][small | half]
+  CUtensorMap m[4];
 };
 
 __device__ __forceinline__ void bulk_copy_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
@@ -529,7 +537,7 @@ constexpr int kT5Warps = 6;                                   // per pipeline: p
 constexpr int kT5Threads = 32 * kT5Pipes * kT5Warps;          // 384
 constexpr int kT5StageBytes = 30 * 1024;                      // two 13 KB tile halves + the patch as B operand [2][16][128 B]
 constexpr int kT5PatchOff = 26 * 1024, kT5PatchHalf = 2048, kT5PatchCopy = kPP * 128;  // 9 real rows per half
-constexpr int kT5RecBytes = 104;
+constexpr int kT5RecBytes = 104;  // sizeof(T5Rec), 8-byte aligned slots
 constexpr int kT5PipeBytes = kT5Stages * kT5StageBytes + 2 * kT5RawBytes + kT5Rec * kT5RecBytes;
 constexpr int kT5Bars = 2 * kT5Stages + 2 * kT5Acc;           // per pipeline
 constexpr int kT5Smem = 1024 + kT5Pipes * kT5PipeBytes + kT5Pipes * kT5Bars * 8 + 64;
@@ -538,7 +546,8 @@ static_assert((kT5Stages * kT5StageBytes) % 1024 == 0 && kT5PipeBytes % 8 == 0 &
 
 struct T5Rec {  // one per SLOT (an edge with a 12x12 window owns two)
   int kind;                  // 0 small tile, 1 half of a large tile, 2 direct gather, 3 nothing to read, 4 end of stream
-  int part, nparts;
+  short part, nparts;
+  int level;                 // pyramid level of the slot (two-level form)
   int be;                    // b * E + e
   unsigned char org[12];
   float dx[kPP], dy[kPP];
@@ -562,8 +571,13 @@ __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::
 
 static_assert(sizeof(T5Rec) <= kT5RecBytes, "record slot");
 
+// NL = 1: one map ring, out [B][E][7][7][3][3].  NL = 2 (the tracker's DPVO.corr, dpvo/dpvo.py:325-333): every edge goes through
+// the pipeline twice in a row -- level 0 against fmap2 at coords * cmul0, then level 1 against fmap2_l1 at coords * cmul1 -- and
+// the consumer that owns an output keeps its level-0 value in a register until the level-1 value exists, then stores the pair:
+// out [B][E][7][7][3][3][2] == torch.stack([corr1, corr2], -1), written once, 4 bytes per thread.
+template <int NL>
 __global__ void __launch_bounds__(kT5Threads, 1)
-corr_tc5_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_constant__ CUtensorMap map_half, const CorrParams P) {
+corr_tc5_kernel(const __grid_constant__ CorrMaps maps, const CorrParams P) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   __shared__ uint32_t tmem_base_s;
@@ -602,23 +616,31 @@ corr_tc5_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_cons
   if (role == 0) {
     // ================================================================= producer
     int sbase = 0;  // slots issued so far (warp-uniform)
-    const int nbatch = (cnt + 15) >> 4;
+    const int nitems = NL * cnt;                      // item = (edge, level), an edge's levels back to back
+    const int nbatch = (nitems + 15) >> 4;
     for (int bt = 0; bt <= nbatch; bt++) {
       const int k = 16 * bt + lane;
       const bool last = bt == nbatch;                 // the batch after the last one carries the end-of-stream slot in lane 0
-      const bool valid = !last && lane < 16 && k < cnt;
+      const bool valid = !last && lane < 16 && k < nitems;
+      const int level = NL == 1 ? 0 : (k & 1);
+      const int LH = level ? P.H1 : P.H, LW = level ? P.W1 : P.W;
       int kind = 3, x0 = 0, y0 = 0, slot = 0, nsl = 0;
       long long pid = -1, be = 0;
       unsigned char org[12];
       float dxv[kPP], dyv[kPP];
       if (valid) {
-        be = plo + k;
+        be = plo + (NL == 1 ? k : (k >> 1));
         const int b = (int)(be / P.E), e = (int)(be % P.E);
         const int64_t ix = P.ii[e], jx = P.jj[e];
         const float2* c2 = reinterpret_cast<const float2*>(P.coords + be * (2 * kPP));
         float v[2 * kPP];
 #pragma unroll
         for (int i = 0; i < kPP; i++) { const float2 t = c2[i]; v[2 * i] = t.x; v[2 * i + 1] = t.y; }
+        if (NL == 2) {  // dpvo/dpvo.py:331-332: coords / 1, coords / 4 (multipliers are exact powers of two)
+          const float cm = level ? P.cmul1 : P.cmul0;
+#pragma unroll
+          for (int i = 0; i < 2 * kPP; i++) v[i] *= cm;
+        }
         int fx[kPP], fy[kPP];
         int mnx = kClamp * 2, mxx = -kClamp * 2, mny = kClamp * 2, mxy = -kClamp * 2;
 #pragma unroll
@@ -630,7 +652,7 @@ corr_tc5_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_cons
         x0 = mnx - kR; y0 = mny - kR;
         const int wdt = mxx - mnx + kD, hgt = mxy - mny + kD;
         const bool bad = ix < 0 || ix >= P.n1 || jx < 0 || jx >= P.n2;
-        const bool outside = x0 >= P.W || y0 >= P.H || x0 + wdt <= 0 || y0 + hgt <= 0;
+        const bool outside = x0 >= LW || y0 >= LH || x0 + wdt <= 0 || y0 + hgt <= 0;
         if (bad) set_status(P.status, WV_STATUS_BAD_INDEX);
         int BX = kD;
         if (bad || outside) kind = 3;
@@ -652,7 +674,7 @@ corr_tc5_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_cons
       const int total = __shfl_sync(0xffffffffu, incl, 31);
       for (int part = 0; part < nsl; part++) {
         T5Rec* r = reinterpret_cast<T5Rec*>(recs + ((myslot + part) % kT5Rec) * kT5RecBytes);
-        r->kind = kind; r->part = part; r->nparts = nsl; r->be = (int)be;
+        r->kind = kind; r->part = (short)part; r->nparts = (short)nsl; r->level = level; r->be = (int)be;
 #pragma unroll
         for (int p = 0; p < kPP; p++) { r->org[p] = org[p]; r->dx[p] = dxv[p]; r->dy[p] = dyv[p]; }
       }
@@ -669,7 +691,7 @@ corr_tc5_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_cons
             const uint32_t bytes = (kind <= 1 ? 2u * npix * 128u : 0u) + (kind <= 2 ? 2u * kT5PatchCopy : 0u);
             if (bytes) mbar_arrive_expect_tx(bar, bytes); else mbar_arrive(bar);
             if (kind <= 1) {
-              const CUtensorMap* map = kind == 0 ? &map_small : &map_half;
+              const CUtensorMap* map = &maps.m[2 * level + (kind == 0 ? 0 : 1)];
               const int yy = y0 + part * kBoxLargeRows;
               tma_load_4d(dst, map, bar, 0, x0, yy, slot);
               tma_load_4d(dst + kHalfBytes, map, bar, 64, x0, yy, slot);
@@ -727,13 +749,16 @@ corr_tc5_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_cons
       o_b[j] = tap / kT; o_a[j] = tap - kT * (tap / kT);
     }
     int eidx = 0;
+    __half keep[4];                               // two-level form: this thread's level-0 outputs of the edge in flight
+#pragma unroll
+    for (int j = 0; j < 4; j++) keep[j] = __float2half_rn(0.f);
     for (int sidx = 0;; sidx++) {
       const int acc = sidx % kT5Acc, stage = sidx % kT5Stages;
       mbar_wait(accfull0 + 8 * acc, (sidx / kT5Acc) & 1);
       const T5Rec* rec = reinterpret_cast<const T5Rec*>(recs + (sidx % kT5Rec) * kT5RecBytes);
       const int kind = rec->kind;
       if (kind == 4) break;
-      const int part = rec->part, nparts = rec->nparts;
+      const int part = rec->part, nparts = rec->nparts, level = NL == 1 ? 0 : rec->level;
       const long long be = rec->be;
       float* rawD = raw0 + (eidx & 1) * (kT5RawBytes / 4);
       if (part == 0 && wt < kPP) {
@@ -759,16 +784,19 @@ corr_tc5_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_cons
         tc_fence_before();
       } else if (kind == 2) {
         // direct gather (windows too far apart for a tile): the only path that reads global memory from a consumer
-        const size_t plane = (size_t)P.H * P.W;
+        const int LH = level ? P.H1 : P.H, LW = level ? P.W1 : P.W;
+        const float cm = NL == 1 ? 1.f : (level ? P.cmul1 : P.cmul0);
+        const size_t plane = (size_t)LH * LW;
         const int eb = (int)(be / P.E), ee = (int)(be % P.E);
-        const __half* f2 = P.fmap2 + ((size_t)eb * P.n2 + (size_t)P.jj[ee]) * kC * plane;
+        const __half* f2 = (level ? P.fmap2_l1 : P.fmap2) + ((size_t)eb * P.n2 + (size_t)P.jj[ee]) * kC * plane;
         const uint8_t* pb = stages + (size_t)stage * kT5StageBytes + kT5PatchOff;
         for (int t = wt; t < kPP * kD * kD; t += 128) {
           const int bb = t & 7, a = (t >> 3) & 7, p = t >> 6;
-          const int i1 = clamp_floor(P.coords[be * (2 * kPP) + kPP + p]) + a - kR, j1 = clamp_floor(P.coords[be * (2 * kPP) + p]) + bb - kR;
+          const int i1 = clamp_floor(P.coords[be * (2 * kPP) + kPP + p] * cm) + a - kR,
+                    j1 = clamp_floor(P.coords[be * (2 * kPP) + p] * cm) + bb - kR;
           float sacc = 0.f;
-          if (i1 >= 0 && i1 < P.H && j1 >= 0 && j1 < P.W) {
-            const __half* p2 = f2 + (size_t)i1 * P.W + j1;
+          if (i1 >= 0 && i1 < LH && j1 >= 0 && j1 < LW) {
+            const __half* p2 = f2 + (size_t)i1 * LW + j1;
             for (int c = 0; c < kC; c++) {
               const __half pv = *reinterpret_cast<const __half*>(pb + (c >> 6) * kT5PatchHalf + p * 128 + (((((c & 63) >> 3) ^ (p & 7)) & 7) << 4) + (c & 7) * 2);
               sacc = fmaf(__half2float(pv), __half2float(p2[(size_t)c * plane]), sacc);
@@ -787,7 +815,7 @@ corr_tc5_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_cons
       if (kind == 2 && wt == 0) mbar_arrive(empty0 + 8 * stage);
       // ---- the 441 outputs of the edge: out[x-tap b][y-tap a][p], 4-tap bilinear from pixel p's own 8x8 window
       const int BX = kind == 0 ? kBoxSmall : (kind == 1 ? kBoxLarge : kD);
-      __half* o = P.out + be * (kT * kT * kPP);
+      __half* o = P.out + be * (NL * kT * kT * kPP);
       if (wt < 14 * kPP) {
         const float* row = rawD + o_p * kT5RawStride;
         const float dx = row[kMaxPix + 1], dy = row[kMaxPix + 2];
@@ -798,7 +826,10 @@ corr_tc5_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_cons
             const float* rr = r0 + o_a[j] * BX + o_b[j];
             const float r00 = rr[0], r01 = rr[1], r10 = rr[BX], r11 = rr[BX + 1];
             const float h0 = fmaf(dx, r01 - r00, r00), h1 = fmaf(dx, r11 - r10, r10);
-            o[wt + 14 * kPP * j] = __float2half_rn(fmaf(dy, h1 - h0, h0));
+            const __half val = __float2half_rn(fmaf(dy, h1 - h0, h0));
+            if (NL == 1) o[wt + 14 * kPP * j] = val;
+            else if (level == 0) keep[j] = val;
+            else reinterpret_cast<__half2*>(o)[wt + 14 * kPP * j] = __halves2half2(keep[j], val);  // (level 0, level 1) pair
           }
         }
       }
@@ -907,16 +938,18 @@ int corr_forward_tiled(const void* fmap1, const void* fmap2, const float* coords
                                                             (const __half*)fmap1, gT, n_patches, tile_blocks, use_tc5 ? 1 : 0);
   WV_LAUNCH_CHECK();
 
-  CorrParams P{gT, (const __half*)fmap2, coords, ii, jj, (__half*)out, B, E, n1, n2, H2, W2, status};
+  CorrParams P{gT, (const __half*)fmap2, coords, ii, jj, (__half*)out, B, E, n1, n2, H2, W2, status, nullptr, 0, 0, 1.f, 1.f};
   const long long BE = (long long)B * E;
   if (use_tc5) {
     static bool t5_attr_set = false;
     if (!t5_attr_set) {
-      WV_CUDA_TRY(cudaFuncSetAttribute(corr_tc5_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kT5Smem));
+      WV_CUDA_TRY(cudaFuncSetAttribute(corr_tc5_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kT5Smem));
       t5_attr_set = true;
     }
+    CorrMaps maps;
+    maps.m[0] = ms; maps.m[1] = mh; maps.m[2] = ms; maps.m[3] = mh;
     const long long want5 = (BE + 7) / 8;
-    corr_tc5_kernel<<<(int)(want5 < sm_count() ? want5 : sm_count()), kT5Threads, kT5Smem, st>>>(ms, mh, P);
+    corr_tc5_kernel<1><<<(int)(want5 < sm_count() ? want5 : sm_count()), kT5Threads, kT5Smem, st>>>(maps, P);
     WV_LAUNCH_CHECK();
     return WV_OK;
   }
@@ -928,6 +961,70 @@ int corr_forward_tiled(const void* fmap1, const void* fmap2, const float* coords
   const long long want = (BE + kConsumers - 1) / kConsumers;
   const int grid = (int)(want < sm_count() ? want : sm_count());
   corr_tiled_kernel<<<grid, kThreads, kSmemBytes, st>>>(ms, mh, P);
+  WV_LAUNCH_CHECK();
+  return WV_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// two-level (stacked) form: DPVO.corr (dpvo/dpvo.py:325-333) in one pass-2 launch.
+//   out [B][E][7][7][3][3][2] fp16 == torch.stack([corr(gmap, pyramid[0], coords * cmul0), corr(gmap, pyramid[1], coords * cmul1)], -1)
+// The reference runs 2 x (corr kernel + 9 ATen blend launches) and then torch.stack, which reads both 40 MB volumes and writes 80 MB.
+// ---------------------------------------------------------------------------------------------------
+bool corr_stacked_supported(int dtype, int B, int E, int C, int PH, int PW, int n1, int n2, int H0, int W0, int H1, int W1, int R) {
+  if (dtype != WV_F16 || C != kC || PH != kP || PW != kP || R != kR) return false;
+  if (B <= 0 || E <= 0 || n1 <= 0 || n2 <= 0 || (long long)B * n2 > 0x7fffffffLL || (long long)B * E > 0x7fffffffLL / 2) return false;
+  if (H0 <= 0 || W0 <= 0 || H1 <= 0 || W1 <= 0 || H0 > (1 << 20) || W0 > (1 << 20) || H1 > (1 << 20) || W1 > (1 << 20)) return false;
+  return encode_tiled_fn() != nullptr;
+}
+
+size_t corr_stacked_workspace_bytes(int B, int n1, int n2, int H0, int W0, int H1, int W1) {
+  return 1024 + al1k((size_t)B * n2 * H0 * W0 * kC * 2) + al1k((size_t)B * n2 * H1 * W1 * kC * 2) + al1k((size_t)B * n1 * kPP * kC * 2);
+}
+
+int corr_forward_stacked(const void* fmap1, const void* fmap2_l0, const void* fmap2_l1, const float* coords, float cmul0, float cmul1,
+                         const int64_t* ii, const int64_t* jj, void* out, int dtype, int B, int E, int C, int PH, int PW, int n1,
+                         int n2, int H0, int W0, int H1, int W1, int R, void* workspace, size_t workspace_bytes, int* status,
+                         cudaStream_t st) {
+  if (!corr_stacked_supported(dtype, B, E, C, PH, PW, n1, n2, H0, W0, H1, W1, R)) return WV_EUNSUPPORTED;
+  if (workspace_bytes < corr_stacked_workspace_bytes(B, n1, n2, H0, W0, H1, W1)) return WV_EWORKSPACE;
+  if ((reinterpret_cast<uintptr_t>(fmap1) & 1) || (reinterpret_cast<uintptr_t>(fmap2_l0) & 1) ||
+      (reinterpret_cast<uintptr_t>(fmap2_l1) & 1) || (reinterpret_cast<uintptr_t>(coords) & 7) || (reinterpret_cast<uintptr_t>(out) & 3))
+    return WV_EUNSUPPORTED;
+  const long long slots = (long long)B * n2, n_patches = (long long)B * n1;
+  __half* nhwc0 = reinterpret_cast<__half*>((reinterpret_cast<uintptr_t>(workspace) + 1023) & ~(uintptr_t)1023);
+  __half* nhwc1 = reinterpret_cast<__half*>(reinterpret_cast<char*>(nhwc0) + al1k((size_t)slots * H0 * W0 * kC * 2));
+  __half* gT = reinterpret_cast<__half*>(reinterpret_cast<char*>(nhwc1) + al1k((size_t)slots * H1 * W1 * kC * 2));
+  CorrMaps maps;
+  if (!make_map(&maps.m[0], nhwc0, W0, H0, slots, kBoxSmall, kBoxSmall) || !make_map(&maps.m[1], nhwc0, W0, H0, slots, kBoxLarge, kBoxLargeRows) ||
+      !make_map(&maps.m[2], nhwc1, W1, H1, slots, kBoxSmall, kBoxSmall) || !make_map(&maps.m[3], nhwc1, W1, H1, slots, kBoxLarge, kBoxLargeRows))
+    return WV_EUNSUPPORTED;
+
+  // pass 1: level 0 together with the patches, then level 1
+  for (int level = 0; level < 2; level++) {
+    const void* src = level ? fmap2_l1 : fmap2_l0;
+    const int HW = level ? H1 * W1 : H0 * W0;
+    const int tiles_per_slot = (HW + kTrPix - 1) / kTrPix;
+    const long long n_tiles = slots * tiles_per_slot;
+    const long long cap = (long long)sm_count() * 8;
+    const int tile_blocks = (int)(n_tiles < cap ? n_tiles : cap);
+    const long long np = level ? 0 : n_patches;
+    const long long pb = (np + 7) / 8;
+    const int patch_blocks = (int)(pb < sm_count() ? pb : sm_count());
+    const int vec_ok = ((HW & 7) == 0 && (reinterpret_cast<uintptr_t>(src) & 15) == 0) ? 1 : 0;
+    restage_kernel<<<tile_blocks + patch_blocks, 256, 0, st>>>((const __half*)src, level ? nhwc1 : nhwc0, HW, tiles_per_slot, n_tiles,
+                                                              vec_ok, (const __half*)fmap1, gT, np, tile_blocks, 1);
+    WV_LAUNCH_CHECK();
+  }
+
+  CorrParams P{gT, (const __half*)fmap2_l0, coords, ii, jj, (__half*)out, B, E, n1, n2, H0, W0, status,
+               (const __half*)fmap2_l1, H1, W1, cmul0, cmul1};
+  static bool attr_set2 = false;
+  if (!attr_set2) {
+    WV_CUDA_TRY(cudaFuncSetAttribute(corr_tc5_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kT5Smem));
+    attr_set2 = true;
+  }
+  const long long want = ((long long)B * E + 7) / 8;
+  corr_tc5_kernel<2><<<(int)(want < sm_count() ? want : sm_count()), kT5Threads, kT5Smem, st>>>(maps, P);
   WV_LAUNCH_CHECK();
   return WV_OK;
 }
