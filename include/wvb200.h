@@ -56,6 +56,9 @@ int wv_device_supported(void);
  * synchronisation a caller needs to turn a data-dependent failure into an exception from the same call, as the reference's
  * torch::linalg::cholesky does (dpvo/fastba/ba_cuda.cu:521). */
 int wv_status_read(int* status, int* value, wv_stream_t stream);
+/* The same read for 1 <= n <= 16 consecutive device ints that the host needs to size an output (the group count of
+ * wv_group_plan); never clears. */
+int wv_words_read(const int* words, int n, int* values, wv_stream_t stream);
 
 /* ---------------------------------------------------------------------------------------------
  * altcorr
@@ -202,6 +205,25 @@ int wv_pops_point_cloud(const float* poses, const float* patches, const float* i
                         int64_t n, int64_t n_poses, int P, float* out, int* status, wv_stream_t stream);
 int wv_frame_distance(const float* poses, const float* patches, const float* intrinsics, int64_t n, int64_t n_poses,
                       int64_t n_patches, int M, int P, float beta, float* D, wv_stream_t stream);
+
+/* ---- SoftAgg of the update operator (dpvo/blocks.py:31-48, called from dpvo/net.py:88-89) ----------
+ * wv_group_plan: `_, jx = torch.unique(ix, return_inverse=True)` (blocks.py:41) without the sort or the host sync.
+ *   keys [E] int64 with key_min <= key < key_min + key_range (key_range <= 2^28; a key outside sets WV_STATUS_BAD_INDEX and
+ *   belongs to no group) -> jx [E] int64 = rank of the key among the distinct keys present (torch.unique's sorted order),
+ *   *n_groups (device word) = G, offsets [E + 1] int32 (entries 0..G valid: group g's members are order[offsets[g] ..
+ *   offsets[g+1])), order [E] int32 = the edges grouped by jx, ascending edge index inside a group.
+ * wv_soft_agg_forward: torch_scatter.scatter_softmax(gx, jx, dim=1) and scatter_sum(fx * w, jx, dim=1) (blocks.py:42-43;
+ *   torch-scatter 2.1.2 composite/softmax.py: max per group, exp(src - max), sum, divide) in one pass:
+ *   fx, gx [B][E][D] (dtype) -> y [B][g_capacity][D] (dtype), rows 0 .. min(G, g_capacity)-1 written.  fp32 arithmetic, members
+ *   rows G .. g_capacity-1 zeroed (a caller that knows a bound on G -- patches in the buffer, frame pairs -- needs no host read
+ *   of G: those rows are never gathered by jx).  fp32 arithmetic in a fixed order (deterministic; the reference's atomics are not). */
+size_t wv_group_plan_workspace_bytes(int64_t E, int64_t key_range);
+int wv_group_plan(const int64_t* keys, int64_t E, int64_t key_min, int64_t key_range, int64_t* jx, int32_t* order,
+                  int32_t* offsets, int32_t* n_groups, void* workspace, size_t workspace_bytes, int* status,
+                  wv_stream_t stream);
+int wv_soft_agg_forward(const void* fx, const void* gx, const int32_t* order, const int32_t* offsets,
+                        const int32_t* n_groups, void* y, int dtype, int B, int64_t E, int D, int64_t g_capacity,
+                        wv_stream_t stream);
 
 /* cuda_ba.neighbors (dpvo/fastba/ba.cpp:106-151), on the device and without host synchronisation:
  * for every edge the index of the previous / next edge of the same group `ii` in (jj, original index)

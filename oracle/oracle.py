@@ -273,3 +273,41 @@ def distance_based_edges(D, thresh):
             if D[i, j] < thresh:
                 ei.append(i); ej.append(j)
     return np.array(ei, np.int64), np.array(ej, np.int64)
+
+
+# ------------------------------------------------------------------------------------------------- SoftAgg (dpvo/blocks.py:31-48)
+# The reference's arithmetic lives in a dependency that is NOT in /root/reference: torch-scatter==2.1.2 (environment.yaml:43).
+# Its published algorithm (torch_scatter/composite/softmax.py::scatter_softmax at that tag) is restated below:
+#     max_value_per_index = scatter_max(src, index)[0];  recentered = src - max_value_per_index.gather(index)
+#     e = recentered.exp();  sum_per_index = scatter_sum(e, index);  return e / sum_per_index.gather(index)
+# followed by blocks.py:43  y = scatter_sum(f(x) * w, jx, dim=1).  PARITY UNPINNED for the softmax/sum arithmetic (torch_scatter
+# cannot be imported here); the grouping itself (`torch.unique(ix, return_inverse=True)`, blocks.py:41) is pinned against
+# torch.unique in tests/test_oracle_golden.py.
+def unique_inverse(ix):
+    """blocks.py:41: `_, jx = torch.unique(ix, return_inverse=True)` -> (sorted distinct keys, jx)"""
+    u, jx = np.unique(np.asarray(ix, np.int64), return_inverse=True)
+    return u, jx.astype(np.int64).reshape(-1)
+
+
+def _seq_scatter(acc, jx, src):
+    """acc[:, jx[e]] += src[:, e] for e ascending, rounding to acc.dtype after every addition"""
+    for e in range(src.shape[1]):
+        acc[:, jx[e]] = (acc[:, jx[e]] + src[:, e]).astype(acc.dtype)
+    return acc
+
+
+def soft_agg(fx, gx, ix, dtype=np.float64):
+    """fx, gx [B, E, D]; returns (y [B, G, D], jx).  dtype=np.float16 rounds after every step like the reference's fp16 tensors
+    do under autocast (scatter_sum accumulating in ascending edge order); np.float64 is the exact value of the same formula."""
+    _, jx = unique_inverse(ix)
+    G = int(jx.max()) + 1 if jx.size else 0
+    f = np.asarray(fx).astype(dtype); g = np.asarray(gx).astype(dtype)
+    B, E, D = g.shape
+    mx = np.full((B, G, D), -np.inf, dtype)
+    for e in range(E):
+        mx[:, jx[e]] = np.maximum(mx[:, jx[e]], g[:, e])
+    ex = np.exp((g - mx[:, jx]).astype(dtype)).astype(dtype)
+    den = _seq_scatter(np.zeros((B, G, D), dtype), jx, ex)
+    w = (ex / den[:, jx]).astype(dtype)
+    y = _seq_scatter(np.zeros((B, G, D), dtype), jx, (f * w).astype(dtype))
+    return y, jx

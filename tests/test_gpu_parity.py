@@ -778,3 +778,130 @@ def test_global_ba_dense_patches_and_entry_limit(syn):
     with pytest.raises(RuntimeError, match="more than 384"):
         run_ba(big, 1, 400, 1)
     run_ba(s, 1, 60, 1)  # and the extension keeps working
+
+
+# ------------------------------------------------------------------------------------------------- SoftAgg (group plan + fused scatter softmax / sum)
+def _keys(syn, kind, **kw):
+    s = syn.make_ba_scene(**kw)
+    return (s["kk"] if kind == "kk" else s["ii"] * 12345 + s["jj"]).astype(np.int64)   # dpvo/net.py:88-89
+
+
+@pytest.mark.parametrize("kind", ["kk", "ij"])
+def test_group_plan_bit_exact_vs_torch_unique(syn, kind):
+    agg = pkg().native_agg()
+    for kw in (dict(seed=5, n=12, M=6, edges="tracker", lifetime=4, removal=6), dict(seed=2, n=40, M=96, edges="tracker")):
+        ix = dev(_keys(syn, kind, **kw))
+        tu, tj = torch.unique(ix, return_inverse=True)          # the reference's call, dpvo/blocks.py:41
+        for hint in ((0, -1), (int(ix.min()), int(ix.max())), (int(ix.min()) - 3, int(ix.max()) + 1000)):
+            jx, order, offsets, ng, G = agg.group_plan(ix, *hint)
+            assert G == tu.numel() == int(ng[0].item()) and torch.equal(jx, tj)
+            order, offsets = order.cpu().numpy(), offsets.cpu().numpy()
+            j = tj.cpu().numpy()
+            assert offsets[0] == 0 and offsets[G] == len(j) and np.array_equal(np.diff(offsets[:G + 1]), np.bincount(j, minlength=G))
+            assert np.array_equal(order, np.argsort(j, kind="stable"))   # grouped, ascending edge index inside a group
+
+
+def test_group_plan_edge_cases(syn):
+    agg = pkg().native_agg()
+    jx, order, offsets, ng, G = agg.group_plan(torch.zeros(0, dtype=torch.long, device="cuda"))
+    assert G == 0 and jx.numel() == 0
+    ix = torch.tensor([5, -7, 5, 900000, -7, 5], device="cuda")
+    jx, order, offsets, ng, G = agg.group_plan(ix)
+    assert G == 3 and jx.tolist() == [1, 0, 1, 2, 0, 1] and order.tolist() == [1, 4, 0, 2, 5, 3] and offsets.tolist()[:4] == [0, 2, 5, 6]
+    big = torch.arange(0, 5000, device="cuda").repeat_interleave(40)[torch.randperm(200000, device="cuda")]   # groups of 40 > one warp
+    jx, order, offsets, ng, G = agg.group_plan(big)
+    assert G == 5000 and torch.equal(jx, big) and np.array_equal(order.cpu().numpy(), np.argsort(big.cpu().numpy(), kind="stable"))
+    with pytest.raises(IndexError):
+        agg.group_plan(ix, 0, 100)                              # keys outside the promised bounds
+    assert agg.group_plan(ix)[4] == 3                           # the failure left nothing behind
+    with pytest.raises(RuntimeError):
+        agg.group_plan(torch.tensor([0, 1 << 40], device="cuda"))
+
+
+@pytest.mark.parametrize("dtype,D,tol", [(torch.float16, 384, 2.0 ** -10), (torch.float32, 384, 2e-6), (torch.float16, 20, 2.0 ** -10),
+                                         (torch.float32, 7, 2e-6)])
+def test_soft_agg_vs_oracle(syn, dtype, D, tol):
+    """tolerance: fp32 arithmetic + ONE rounding to the output dtype -> half an ulp of the result scale (2^-11 relative for fp16;
+    the reference's own fp16 evaluation is ~10x further from the exact value, see test_soft_agg_oracle_properties)"""
+    blocks = importlib.import_module(PKG + ".blocks")
+    rng = np.random.default_rng(31)
+    ix = _keys(syn, "ij", seed=5, n=12, M=6, edges="tracker", lifetime=4, removal=6)
+    E = len(ix)
+    B = 2
+    f = dev(rng.standard_normal((B, E, D)).astype(np.float32), dtype)
+    g = dev((3 * rng.standard_normal((B, E, D))).astype(np.float32), dtype)
+    jx, plan = blocks.group_plan(dev(ix))
+    y = blocks.scatter_softmax_sum(f, g, plan)
+    y2 = blocks.scatter_softmax_sum(f, g, plan)
+    truth, tj = oracle.soft_agg(f.float().cpu().numpy().astype(np.float64), g.float().cpu().numpy().astype(np.float64), ix)
+    assert y.dtype == dtype and tuple(y.shape) == truth.shape and np.array_equal(jx.cpu().numpy(), tj)
+    assert torch.equal(y, y2)                                   # fixed summation order
+    scale = max(1.0, np.abs(truth).max())
+    assert np.abs(y.float().cpu().numpy() - truth).max() <= tol * scale
+
+
+def test_soft_agg_module_matches_composed_reference_form(syn):
+    """blocks.SoftAgg (expand=True / False, autocast like the tracker) against the same module evaluated with torch ops in the
+    reference's order: unique -> softmax per group -> weighted sum -> h -> expand (dpvo/blocks.py:40-48)"""
+    blocks = importlib.import_module(PKG + ".blocks")
+    torch.manual_seed(0)
+    ix = dev(_keys(syn, "kk", seed=6, n=12, M=6, edges="tracker", lifetime=4, removal=6))
+    E, D = ix.numel(), 384
+    x = torch.randn(1, E, D, device="cuda")
+    for expand in (True, False):
+        m = blocks.SoftAgg(D, expand=expand).cuda()
+        with torch.no_grad(), torch.autocast("cuda", enabled=True):
+            out = m(x, ix)
+            _, jx = torch.unique(ix, return_inverse=True)
+            y = blocks._soft_agg_autograd(m.f(x).float(), m.g(x).float(), jx, int(jx.max()) + 1)
+            ref = m.h(y.half())[:, jx] if expand else m.h(y.half())
+        assert out.shape == ref.shape and out.dtype == torch.float16
+        assert (out.float() - ref.float()).abs().max() <= 4e-3 * max(1.0, ref.float().abs().max().item())
+    # gradients flow through the composed form (training path)
+    m = blocks.SoftAgg(D).cuda()
+    xg = x.clone().requires_grad_(True)
+    m(xg, ix).sum().backward()
+    assert xg.grad is not None and torch.isfinite(xg.grad).all() and m.g.weight.grad.abs().sum() > 0
+
+
+def test_soft_agg_full_size_properties(syn):
+    """E = 45 312, D = 384 fp16 (the tracker's update operator): size-independent properties + an oracle sample"""
+    blocks = importlib.import_module(PKG + ".blocks")
+    rng = np.random.default_rng(33)
+    for kind in ("kk", "ij"):
+        ixn = _keys(syn, kind, seed=2, n=40, M=96, edges="tracker")
+        ix = dev(ixn)
+        E, D = len(ixn), 384
+        f = torch.randn(1, E, D, device="cuda").half(); g = (3 * torch.randn(1, E, D, device="cuda")).half()
+        jx, plan = blocks.group_plan(ix)
+        y = blocks.scatter_softmax_sum(f, g, plan)
+        G = plan[3]
+        assert tuple(y.shape) == (1, G, D) and torch.isfinite(y).all()
+        # weights of a group sum to one: constant f -> constant y (exactly representable constant)
+        yc = blocks.scatter_softmax_sum(torch.full_like(f, 0.75), g, plan)
+        assert (yc.float() - 0.75).abs().max() <= 2.0 ** -11
+        # shift invariance in g (exact shift by a representable constant per channel is not exact in fp16; use linearity in f instead)
+        y2 = blocks.scatter_softmax_sum(2 * f, g, plan)          # linear in f: exact in fp32, identical roundings above fp16 subnormals
+        assert (y2.float() - 2 * y.float()).abs().max() <= 2.0 ** -23
+        # a bound on G instead of the host read of G: same rows, zeros beyond, nothing waits for the device
+        lo_k, hi_k = int(ixn.min()), int(ixn.max())
+        jb, planb = blocks.group_plan(ix, lo_k, hi_k, g_capacity=G + 37)
+        yb = blocks.scatter_softmax_sum(f, g, planb)
+        assert torch.equal(jb, jx) and tuple(yb.shape) == (1, G + 37, D) and torch.equal(yb[:, :G], y) and (yb[:, G:] == 0).all()
+        # convexity: every output lies inside the range of its group's f values
+        idx = jx.view(1, -1, 1).expand(1, E, D)
+        lo = torch.full((1, G, D), float("inf"), device="cuda").scatter_reduce(1, idx, f.float(), "amin")
+        hi = torch.full((1, G, D), float("-inf"), device="cuda").scatter_reduce(1, idx, f.float(), "amax")
+        assert (y.float() >= lo - 1e-3).all() and (y.float() <= hi + 1e-3).all()
+        # permuting the edges permutes nothing in y (groups are sets) up to the fp32 summation order
+        perm = torch.randperm(E, device="cuda")
+        jp, planp = blocks.group_plan(ix[perm])
+        yp = blocks.scatter_softmax_sum(f[:, perm], g[:, perm], planp)
+        assert (yp.float() - y.float()).abs().max() <= 2.0 ** -9 * max(1.0, y.float().abs().max().item())
+        # oracle on a sample of groups
+        sel = rng.choice(G, 24, replace=False)
+        jn = jx.cpu().numpy()
+        keep = np.isin(jn, sel)
+        truth, _ = oracle.soft_agg(f[:, keep].float().cpu().numpy().astype(np.float64), g[:, keep].float().cpu().numpy().astype(np.float64), ixn[keep])
+        got = y[:, np.sort(sel)].float().cpu().numpy()
+        assert np.abs(got - truth).max() <= 2.0 ** -10 * max(1.0, np.abs(truth).max())

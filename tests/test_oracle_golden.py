@@ -136,3 +136,37 @@ def test_frame_distance_oracle_and_edge_selection(golden, name):
     ei, ej = oracle.distance_based_edges(D, float(g[f"{name}_thresh"]))
     assert np.array_equal(ei, g[f"{name}_edges_ii"]) and np.array_equal(ej, g[f"{name}_edges_jj"])   # bit-exact edge list
     assert len(ei) > n - 1   # some long-range edges selected, not only the sequential ones
+
+
+# ------------------------------------------------------------------------------------------------- SoftAgg oracle
+def test_unique_inverse_matches_torch_unique(syn):
+    """blocks.py:41 calls torch.unique(ix, return_inverse=True): the oracle's grouping is pinned against that very call"""
+    import torch
+    rng = np.random.default_rng(3)
+    s = syn.make_ba_scene(seed=5, n=12, M=6, edges="tracker", lifetime=4, removal=6)
+    cases = [s["kk"], s["ii"] * 12345 + s["jj"], rng.integers(-50, 50, 300), np.array([7], np.int64), np.zeros(0, np.int64)]
+    for ix in cases:
+        u, jx = oracle.unique_inverse(ix)
+        tu, tj = torch.unique(torch.from_numpy(np.asarray(ix, np.int64)), return_inverse=True)
+        assert np.array_equal(u, tu.numpy()) and np.array_equal(jx, tj.numpy())
+
+
+def test_soft_agg_oracle_properties():
+    """torch_scatter is not importable here (parity unpinned, see oracle.py): check the restated formula's defining properties"""
+    rng = np.random.default_rng(4)
+    E, D = 120, 8
+    ix = rng.integers(0, 9, E) * 12345 + rng.integers(0, 4, E)
+    f = rng.standard_normal((2, E, D)); g = 3 * rng.standard_normal((2, E, D))
+    y, jx = oracle.soft_agg(f, g, ix)
+    G = jx.max() + 1
+    for b in range(2):
+        for k in range(G):
+            m = jx == k
+            w = np.exp(g[b, m] - g[b, m].max(0)); w /= w.sum(0)
+            assert np.allclose(y[b, k], (f[b, m] * w).sum(0), rtol=1e-12, atol=1e-12)
+    yc, _ = oracle.soft_agg(np.full_like(f, 0.75), g, ix)      # weights of a group sum to one
+    assert np.allclose(yc, 0.75, rtol=1e-12)
+    ys, _ = oracle.soft_agg(f, g + 100.0, ix)                  # shift invariance of the softmax
+    assert np.allclose(ys, y, rtol=1e-9, atol=1e-9)
+    y16, _ = oracle.soft_agg(f.astype(np.float16), g.astype(np.float16), ix, dtype=np.float16)
+    assert np.abs(y16 - y).max() < 2e-2                        # the reference's own fp16 evaluation error, for scale

@@ -34,6 +34,16 @@ def native_modules():
         raise ImportError(f"native modules missing ({e}); build them with `python {HERE}/build.py`") from e
 
 
+def native_agg():
+    """cuda_agg: group plan + fused scatter-softmax / scatter-sum (the reference calls torch_scatter here, dpvo/blocks.py:41-43)"""
+    install_as_dpvo_backends()
+    import torch  # noqa: F401
+    try:
+        return importlib.import_module("cuda_agg")
+    except ImportError as e:
+        raise ImportError(f"native module cuda_agg missing ({e}); build it with `python {HERE}/build.py`") from e
+
+
 def capi():
     """ctypes handle on the C ABI (include/wvb200.h)"""
     if not os.path.exists(LIB_PATH):
@@ -42,6 +52,6 @@ def capi():
 
 
 def __getattr__(name):
-    if name in ("altcorr", "fastba", "synthetic", "hostapi", "dist", "projective_ops"):
+    if name in ("altcorr", "fastba", "synthetic", "hostapi", "dist", "projective_ops", "blocks", "colmap_export"):
         return importlib.import_module(f"{__name__}.{name}")
     raise AttributeError(name)

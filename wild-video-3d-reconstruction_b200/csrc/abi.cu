@@ -33,6 +33,10 @@ int patchify_backward(const void*, const float*, float*, int, int, int, int, int
 // corr_sm100.cu
 bool corr_tiled_supported(int dtype, int B, int E, int C, int PH, int PW, int n1, int n2, int H2, int W2, int R);
 size_t corr_tiled_workspace_bytes(int dtype, int B, int E, int C, int PH, int PW, int n1, int n2, int H2, int W2, int R);
+// agg.cu
+size_t group_plan_workspace_bytes(long long E, long long range);
+int group_plan(const int64_t*, long long, int64_t, long long, int64_t*, int*, int*, int*, void*, size_t, int*, cudaStream_t);
+int soft_agg_forward(const void*, const void*, const int*, const int*, const int*, void*, int, int, long long, int, long long, cudaStream_t);
 bool corr_stacked_supported(int dtype, int B, int E, int C, int PH, int PW, int n1, int n2, int H0, int W0, int H1, int W1, int R);
 size_t corr_stacked_workspace_bytes(int B, int n1, int n2, int H0, int W0, int H1, int W1);
 int corr_forward_stacked(const void*, const void*, const void*, const float*, float, float, const int64_t*, const int64_t*, void*, int,
@@ -92,8 +96,15 @@ int wv_device_supported(void) {
   return major == 10 ? 1 : 0;
 }
 
-int wv_status_read(int* status, int* value, wv_stream_t stream) {
-  if (!status || !value) return WV_EINVAL;
+static int word_read(int* status, int n, int* value, wv_stream_t stream, bool clear);
+
+int wv_status_read(int* status, int* value, wv_stream_t stream) { return word_read(status, 1, value, stream, true); }
+int wv_words_read(const int* words, int n, int* values, wv_stream_t stream) {
+  return word_read(const_cast<int*>(words), n, values, stream, false);
+}
+
+static int word_read(int* status, int n, int* value, wv_stream_t stream, bool clear) {
+  if (!status || !value || n < 1 || n > 16) return WV_EINVAL;
   // one pinned word + one event per device, created on first use (callers hold the GIL / serialise per device)
   struct Chan { int* host = nullptr; cudaEvent_t ev = nullptr; };
   static Chan chans[64];
@@ -102,18 +113,18 @@ int wv_status_read(int* status, int* value, wv_stream_t stream) {
   if (dev < 0 || dev >= 64) return WV_EUNSUPPORTED;
   Chan& c = chans[dev];
   if (!c.host) {
-    WV_CUDA_TRY(cudaHostAlloc(reinterpret_cast<void**>(&c.host), sizeof(int), cudaHostAllocDefault));
+    WV_CUDA_TRY(cudaHostAlloc(reinterpret_cast<void**>(&c.host), 16 * sizeof(int), cudaHostAllocDefault));
     WV_CUDA_TRY(cudaEventCreateWithFlags(&c.ev, cudaEventDisableTiming));
   }
   cudaStream_t st = as_stream(stream);
-  WV_CUDA_TRY(cudaMemcpyAsync(c.host, status, sizeof(int), cudaMemcpyDeviceToHost, st));
+  WV_CUDA_TRY(cudaMemcpyAsync(c.host, status, n * sizeof(int), cudaMemcpyDeviceToHost, st));
   WV_CUDA_TRY(cudaEventRecord(c.ev, st));
   cudaError_t q = cudaErrorNotReady;
   for (int spin = 0; spin < 200000 && q == cudaErrorNotReady; spin++) q = cudaEventQuery(c.ev);  // ~ a few hundred us at most
   if (q == cudaErrorNotReady) q = cudaEventSynchronize(c.ev);
   WV_CUDA_TRY(q);
-  *value = *c.host;
-  if (*value != 0) WV_CUDA_TRY(cudaMemsetAsync(status, 0, sizeof(int), st));
+  for (int i = 0; i < n; i++) value[i] = c.host[i];
+  if (clear && *value != 0) WV_CUDA_TRY(cudaMemsetAsync(status, 0, sizeof(int), st));
   return WV_OK;
 }
 
@@ -144,6 +155,27 @@ int wv_corr_forward(const void* fmap1, const void* fmap2, const float* coords, c
     if (rc != WV_EUNSUPPORTED) return rc;  // e.g. a misaligned base pointer: the generic kernel takes any
   }
   return corr_forward_generic(fmap1, fmap2, coords, ii, jj, out, dtype, B, E, C, PH, PW, n1, n2, H2, W2, radius, status, st);
+}
+
+size_t wv_group_plan_workspace_bytes(int64_t E, int64_t key_range) {
+  if (E < 0 || key_range < 0 || key_range > (1LL << 28) || E > 0x7ffffff0LL) return 0;
+  return group_plan_workspace_bytes(E, key_range);
+}
+
+int wv_group_plan(const int64_t* keys, int64_t E, int64_t key_min, int64_t key_range, int64_t* jx, int32_t* order, int32_t* offsets,
+                  int32_t* n_groups, void* workspace, size_t workspace_bytes, int* status, wv_stream_t stream) {
+  if (E < 0 || E > 0x7ffffff0LL || key_range < 0 || key_range > (1LL << 28) || !offsets || !n_groups || !workspace) return WV_EINVAL;
+  if (E > 0 && (!keys || !jx || !order)) return WV_EINVAL;
+  if (E > 0 && key_range == 0) return WV_EINVAL;
+  return group_plan(keys, E, key_min, key_range, jx, order, offsets, n_groups, workspace, workspace_bytes, status, as_stream(stream));
+}
+
+int wv_soft_agg_forward(const void* fx, const void* gx, const int32_t* order, const int32_t* offsets, const int32_t* n_groups, void* y,
+                        int dtype, int B, int64_t E, int D, int64_t g_capacity, wv_stream_t stream) {
+  if ((dtype != WV_F16 && dtype != WV_F32) || B < 0 || E < 0 || D <= 0 || g_capacity < 0 || g_capacity > 0x7fffffffLL) return WV_EINVAL;
+  if ((int64_t)B * g_capacity == 0) return WV_OK;
+  if (!fx || !gx || !order || !offsets || !n_groups || !y) return WV_EINVAL;
+  return soft_agg_forward(fx, gx, order, offsets, n_groups, y, dtype, B, E, D, g_capacity, as_stream(stream));
 }
 
 size_t wv_corr_stacked_workspace_bytes(int dtype, int B, int E, int C, int PH, int PW, int n1, int n2, int H0, int W0, int H1,

@@ -10,8 +10,9 @@
 //   group plan   the inverse index without a sort: presence bitmap over the key range -> popcount prefix -> jx = rank of the key
 //                among the present keys (== torch.unique's sorted order), then member lists per group in ascending edge order
 //                (counting fill + a per-group rank sort), so that the reduction order is fixed: results are deterministic.
-//   soft_agg     ONE pass over f(x) and g(x): a thread owns 16 bytes of channels of one group and walks the group's members twice
-//                (max, then exp / sum / weighted sum, the second walk hits L1/L2), fp32 arithmetic, one rounding at the end.
+//   soft_agg     ONE pass over f(x) and g(x): a CTA per group, a thread owns 16 bytes of channels and a share of the group's members
+//                and walks them twice (max, then exp / sum / weighted sum; the second walk hits L1/L2), fp32 arithmetic, one
+//                rounding at the end.
 //                HBM-bound: algorithmic bytes = 2 * E * D * sizeof(T) read + G * D * sizeof(T) written.
 #include "wv_common.cuh"
 
@@ -161,6 +162,10 @@ __global__ void sort_members(const int* __restrict__ offsets, const int* __restr
 // ---------------------------------------------------------------------------------------------------
 // y[b][g][c] = sum_{e in g} f[b][e][c] * exp(s[b][e][c] - max_g) / sum_{e in g} exp(s[b][e][c] - max_g)
 // ---------------------------------------------------------------------------------------------------
+template <typename T> __device__ __forceinline__ float soft_exp(float x);
+template <> __device__ __forceinline__ float soft_exp<float>(float x) { return expf(x); }
+template <> __device__ __forceinline__ float soft_exp<__half>(float x) { return __expf(x); }   // 2 ulp of fp32: far below the fp16 output rounding
+
 template <typename T, int V> struct Vec;
 template <> struct Vec<__half, 8> {
   uint4 r;
@@ -191,72 +196,113 @@ template <typename T> struct Vec<T, 1> {
   static __device__ __forceinline__ void store(T* p, const float* v) { *p = from_f32<T>(v[0]); }
 };
 
+// One CTA per (batch, group): thread (split, cl) owns V channels and a contiguous share of the group's members.  Walk 1 leaves each
+// split's per-channel maximum in shared memory; every thread then takes the maximum over the splits, walk 2 accumulates
+// sum(exp) and sum(f * exp) over its share (the rows come back from L1/L2), and split 0 adds the partial sums in split order.
+// The order of every addition is a function of (group size, splits) only: results are deterministic.
 template <typename T, int V>
-__global__ void __launch_bounds__(256) soft_agg_kernel(const T* __restrict__ fx, const T* __restrict__ gx, const int* __restrict__ order,
-                                                       const int* __restrict__ offsets, const int* __restrict__ n_groups, T* __restrict__ y,
-                                                       int B, long long E, int D, long long Gcap) {
-  const int tpg = D / V;                                 // threads per group row
+__global__ void __launch_bounds__(1024) soft_agg_kernel(const T* __restrict__ fx, const T* __restrict__ gx, const int* __restrict__ order,
+                                                        const int* __restrict__ offsets, const int* __restrict__ n_groups, T* __restrict__ y,
+                                                        int B, long long E, int D, long long Gcap, int tpc, int S) {
+  extern __shared__ float red[];                          // [2][S][tpc * V]
+  const int cpb = tpc * V;                               // channels per pass of the block
+  float* red0 = red;
+  float* red1 = red + (size_t)S * cpb;
+  const int split = threadIdx.x / tpc, cl = threadIdx.x - split * tpc;
   const int G = (int)min((long long)*n_groups, Gcap);
-  const long long total = (long long)B * G * tpg;
-  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
-    const int c = (int)(t % tpg) * V;
-    const long long bg = t / tpg;
-    const int g = (int)(bg % G), b = (int)(bg / G);
-    const int lo = offsets[g], hi = offsets[g + 1];
-    const T* fb = fx + ((long long)b * E) * D + c;
-    const T* gb = gx + ((long long)b * E) * D + c;
-    float mx[V], s[V], a[V];
+  for (long long bg = blockIdx.x; bg < (long long)B * Gcap; bg += gridDim.x) {
+    const int g = (int)(bg % Gcap), b = (int)(bg / Gcap);
+    T* yrow = y + ((long long)b * Gcap + g) * D;
+    if (g >= G) {                                         // rows beyond the groups present: defined (zero), never gathered
+      for (int c = threadIdx.x; c < D; c += blockDim.x) yrow[c] = from_f32<T>(0.f);
+      continue;
+    }
+    const int lo = offsets[g], n = offsets[g + 1] - lo;
+    const int m0 = lo + (int)((long long)n * split / S), m1 = lo + (int)((long long)n * (split + 1) / S);
+    for (int c0 = 0; c0 < D; c0 += cpb) {
+      const int c = c0 + cl * V;
+      const bool act = c < D;
+      const T* fb = fx + ((long long)b * E) * D + c;
+      const T* gb = gx + ((long long)b * E) * D + c;
+      float mx[V], s[V], a[V];
 #pragma unroll
-    for (int i = 0; i < V; i++) { mx[i] = -INFINITY; s[i] = 0.f; a[i] = 0.f; }
-    // walk 1: per-channel maximum of the scores
-    int m = lo;
-    for (; m + 4 <= hi; m += 4) {
-      Vec<T, V> r[4];
+      for (int i = 0; i < V; i++) { mx[i] = -INFINITY; s[i] = 0.f; a[i] = 0.f; }
+      if (act) {
+        int m = m0;
+        for (; m + 4 <= m1; m += 4) {
+          Vec<T, V> r[4];
 #pragma unroll
-      for (int u = 0; u < 4; u++) r[u].load(gb + (long long)order[m + u] * D);
+          for (int u = 0; u < 4; u++) r[u].load(gb + (long long)order[m + u] * D);
 #pragma unroll
-      for (int u = 0; u < 4; u++) {
-        float v[V];
-        r[u].get(v);
+          for (int u = 0; u < 4; u++) {
+            float v[V];
+            r[u].get(v);
 #pragma unroll
-        for (int i = 0; i < V; i++) mx[i] = fmaxf(mx[i], v[i]);
+            for (int i = 0; i < V; i++) mx[i] = fmaxf(mx[i], v[i]);
+          }
+        }
+        for (; m < m1; m++) {
+          Vec<T, V> r;
+          r.load(gb + (long long)order[m] * D);
+          float v[V];
+          r.get(v);
+#pragma unroll
+          for (int i = 0; i < V; i++) mx[i] = fmaxf(mx[i], v[i]);
+        }
       }
-    }
-    for (; m < hi; m++) {
-      Vec<T, V> r;
-      r.load(gb + (long long)order[m] * D);
-      float v[V];
-      r.get(v);
+      if (S > 1) {
 #pragma unroll
-      for (int i = 0; i < V; i++) mx[i] = fmaxf(mx[i], v[i]);
-    }
-    // walk 2: weights, their sum, and the weighted sum of f (ascending edge order: fixed summation order)
-    m = lo;
-    for (; m + 2 <= hi; m += 2) {
-      Vec<T, V> rg[2], rf[2];
+        for (int i = 0; i < V; i++) red0[(size_t)split * cpb + cl * V + i] = mx[i];
+        __syncthreads();
+        for (int sp = 0; sp < S; sp++)
 #pragma unroll
-      for (int u = 0; u < 2; u++) { const long long e = order[m + u]; rg[u].load(gb + e * D); rf[u].load(fb + e * D); }
-#pragma unroll
-      for (int u = 0; u < 2; u++) {
-        float v[V], f[V];
-        rg[u].get(v); rf[u].get(f);
-#pragma unroll
-        for (int i = 0; i < V; i++) { const float w = expf(v[i] - mx[i]); s[i] += w; a[i] = fmaf(f[i], w, a[i]); }
+          for (int i = 0; i < V; i++) mx[i] = fmaxf(mx[i], red0[(size_t)sp * cpb + cl * V + i]);
+        __syncthreads();
       }
-    }
-    for (; m < hi; m++) {
-      const long long e = order[m];
-      Vec<T, V> rg, rf;
-      rg.load(gb + e * D); rf.load(fb + e * D);
-      float v[V], f[V];
-      rg.get(v); rf.get(f);
+      if (act) {
+        int m = m0;
+        for (; m + 2 <= m1; m += 2) {
+          Vec<T, V> rg[2], rf[2];
 #pragma unroll
-      for (int i = 0; i < V; i++) { const float w = expf(v[i] - mx[i]); s[i] += w; a[i] = fmaf(f[i], w, a[i]); }
-    }
-    float o[V];
+          for (int u = 0; u < 2; u++) { const long long e = order[m + u]; rg[u].load(gb + e * D); rf[u].load(fb + e * D); }
 #pragma unroll
-    for (int i = 0; i < V; i++) o[i] = a[i] / s[i];
-    Vec<T, V>::store(y + ((long long)b * Gcap + g) * D + c, o);
+          for (int u = 0; u < 2; u++) {
+            float v[V], f[V];
+            rg[u].get(v); rf[u].get(f);
+#pragma unroll
+            for (int i = 0; i < V; i++) { const float w = soft_exp<T>(v[i] - mx[i]); s[i] += w; a[i] = fmaf(f[i], w, a[i]); }
+          }
+        }
+        for (; m < m1; m++) {
+          const long long e = order[m];
+          Vec<T, V> rg, rf;
+          rg.load(gb + e * D); rf.load(fb + e * D);
+          float v[V], f[V];
+          rg.get(v); rf.get(f);
+#pragma unroll
+          for (int i = 0; i < V; i++) { const float w = soft_exp<T>(v[i] - mx[i]); s[i] += w; a[i] = fmaf(f[i], w, a[i]); }
+        }
+      }
+      if (S > 1) {
+        if (split > 0) {
+#pragma unroll
+          for (int i = 0; i < V; i++) { red0[(size_t)split * cpb + cl * V + i] = s[i]; red1[(size_t)split * cpb + cl * V + i] = a[i]; }
+        }
+        __syncthreads();
+        if (split == 0) {
+          for (int sp = 1; sp < S; sp++)
+#pragma unroll
+            for (int i = 0; i < V; i++) { s[i] += red0[(size_t)sp * cpb + cl * V + i]; a[i] += red1[(size_t)sp * cpb + cl * V + i]; }
+        }
+      }
+      if (split == 0 && act) {
+        float o[V];
+#pragma unroll
+        for (int i = 0; i < V; i++) o[i] = a[i] / s[i];
+        Vec<T, V>::store(yrow + c, o);
+      }
+      if (S > 1) __syncthreads();
+    }
   }
 }
 
@@ -309,22 +355,35 @@ int group_plan(const int64_t* keys, long long E, int64_t key_min, long long rang
   return WV_OK;
 }
 
+template <typename T, int V>
+int launch_soft_agg(const void* fx, const void* gx, const int* order, const int* offsets, const int* n_groups, void* y, int B, long long E,
+                    int D, long long Gcap, cudaStream_t st) {
+  const int cv = (D + V - 1) / V;                        // channel vectors per row
+  const int tpc = cv < 128 ? cv : 128;
+  // splits: ~4 members per thread at the average group size, bounded by the block size and 48 KB of partials
+  const long long avg = Gcap > 0 ? (E + Gcap - 1) / Gcap : 1;
+  long long S = (avg + 3) / 4;
+  S = S < 1 ? 1 : S;
+  S = S > 8 ? 8 : S;
+  while (S > 1 && (S * tpc > 1024 || S * tpc * V * 8 > 48 * 1024)) S--;
+  const long long blocks = (long long)B * Gcap;
+  const int grid = (int)(blocks < (long long)sm_count() * 64 ? blocks : (long long)sm_count() * 64);
+  const size_t smem = S > 1 ? (size_t)S * tpc * V * 8 : 0;
+  soft_agg_kernel<T, V><<<grid, (int)(S * tpc), smem, st>>>((const T*)fx, (const T*)gx, order, offsets, n_groups, (T*)y, B, E, D, Gcap, tpc, (int)S);
+  WV_LAUNCH_CHECK();
+  return WV_OK;
+}
+
 int soft_agg_forward(const void* fx, const void* gx, const int* order, const int* offsets, const int* n_groups, void* y, int dtype,
                      int B, long long E, int D, long long Gcap, cudaStream_t st) {
   const bool al16 = ((reinterpret_cast<uintptr_t>(fx) | reinterpret_cast<uintptr_t>(gx) | reinterpret_cast<uintptr_t>(y)) & 15) == 0;
-  const int V = dtype == WV_F16 ? ((D % 8 == 0 && al16) ? 8 : 1) : ((D % 4 == 0 && al16) ? 4 : 1);
-  const long long total = (long long)B * Gcap * (D / V);
-  if (total == 0) return WV_OK;
-  const int grid = (int)min((total + 255) / 256, (long long)sm_count() * 32);
+  if ((long long)B * Gcap == 0) return WV_OK;
   if (dtype == WV_F16) {
-    if (V == 8) soft_agg_kernel<__half, 8><<<grid, 256, 0, st>>>((const __half*)fx, (const __half*)gx, order, offsets, n_groups, (__half*)y, B, E, D, Gcap);
-    else soft_agg_kernel<__half, 1><<<grid, 256, 0, st>>>((const __half*)fx, (const __half*)gx, order, offsets, n_groups, (__half*)y, B, E, D, Gcap);
-  } else {
-    if (V == 4) soft_agg_kernel<float, 4><<<grid, 256, 0, st>>>((const float*)fx, (const float*)gx, order, offsets, n_groups, (float*)y, B, E, D, Gcap);
-    else soft_agg_kernel<float, 1><<<grid, 256, 0, st>>>((const float*)fx, (const float*)gx, order, offsets, n_groups, (float*)y, B, E, D, Gcap);
+    if (D % 8 == 0 && al16) return launch_soft_agg<__half, 8>(fx, gx, order, offsets, n_groups, y, B, E, D, Gcap, st);
+    return launch_soft_agg<__half, 1>(fx, gx, order, offsets, n_groups, y, B, E, D, Gcap, st);
   }
-  WV_LAUNCH_CHECK();
-  return WV_OK;
+  if (D % 4 == 0 && al16) return launch_soft_agg<float, 4>(fx, gx, order, offsets, n_groups, y, B, E, D, Gcap, st);
+  return launch_soft_agg<float, 1>(fx, gx, order, offsets, n_groups, y, B, E, D, Gcap, st);
 }
 
 }  // namespace wv
