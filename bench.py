@@ -2,8 +2,9 @@
 """bench.py -- one JSON line for the altcorr + fastba hot path (BASELINE.json configs[1] sizes).
 
 A "step" is what the unchanged tracker does once per frame inside DPVO.update() on the path this repo
-replaces (dpvo/dpvo.py:711-749): altcorr.corr on both pyramid levels (E = 45 312 edges, fp16 maps, radius 3),
-fastba.neighbors, and fastba.BA with 2 Gauss-Newton iterations on the same edge list (10 free poses).
+replaces (dpvo/dpvo.py:711-749): DPVO.corr (dpvo/dpvo.py:325-333: altcorr.corr on both pyramid levels, E = 45 312 edges, fp16
+maps, radius 3, stacked into [1, E, 882]), fastba.neighbors, and fastba.BA with 2 Gauss-Newton iterations on the same edge list
+(10 free poses).
 One step == one frame, so the metric is frames/s of the hot path at 512x384.
 
   python bench.py [--gpus N] [--steps K] [--warmup W]             our arm (CUDA, through the torch extensions -> C ABI)
@@ -34,10 +35,11 @@ for p in (ROOT,):
 # indices + output):  s*C*P^2 + s*C*F + 4*2*P^2 + 2*8 + s*49*P^2,  F0 = 100 px, F1 = 81 px
 CORR_BYTES_L0 = 2 * 128 * 9 + 2 * 128 * 100 + 72 + 16 + 2 * 49 * 9   # 28 874
 CORR_BYTES_L1 = 2 * 128 * 9 + 2 * 128 * 81 + 72 + 16 + 2 * 49 * 9    # 24 010
-# dram__bytes_read.sum + dram__bytes_write.sum per level-0 call (restage 121.2 + 73.7 MB, tcgen05 kernel 281.7 + 36.7 MB), ncu --set full
-NCU_TRAFFIC_L0 = 513.4e6
+# dram__bytes_read.sum + dram__bytes_write.sum of one DPVO.corr call = restage_kernel x2 + corr_tc5_kernel<2>, ncu --set full
+# (profiles/r1_stacked_ncu_summary.txt)
+NCU_TRAFFIC_CORR = 513.4e6
 WORKLOAD = ("configs[1]: 512x384 -> fmaps 96x128 + 24x32, C=128 fp16, pmem=36, M=96, tracker edge list E=45312, "
-            "radius 3; one update(): corr x2 levels + neighbors + BA(10 free poses, 2 GN iterations)")
+            "radius 3; one update(): DPVO.corr (both levels, stacked [1,E,882]) + neighbors + BA(10 free poses, 2 GN iterations)")
 
 
 def measured_peak_gbs():
@@ -164,8 +166,9 @@ def _ref_corr_worker(args):
     rc = build_ref.load("ref_cuda_corr")
     g = _REF_SHARED
     t = time.perf_counter()
-    for fm, div in ((g["f0"], 1.0), (g["f1"], 4.0)):
-        rc.forward(g["gmap"], fm, (g["coords"][:, lo:hi] / div).contiguous(), g["ii"][lo:hi], g["jj"][lo:hi], 3)
+    cs = [rc.forward(g["gmap"], fm, (g["coords"][:, lo:hi] / div).contiguous(), g["ii"][lo:hi], g["jj"][lo:hi], 3)[0].permute(0, 1, 3, 2, 4, 5)
+          for fm, div in ((g["f0"], 1.0), (g["f1"], 4.0))]
+    torch.stack(cs, -1).view(1, hi - lo, -1)   # dpvo/altcorr/correlation.py:30 + dpvo/dpvo.py:333
     return time.perf_counter() - t
 
 
@@ -273,6 +276,7 @@ def run_b200(args):
         dist.init_process_group("nccl", device_id=dev)
     pkg = importlib.import_module(PKG)
     cc, cb = pkg.native_modules()
+    altcorr = importlib.import_module(PKG + ".altcorr.correlation")
     lib = pkg.capi()
     assert lib.wv_device_supported() == 1, "libwvb200 has sm_100a code only"
 
@@ -295,19 +299,17 @@ def run_b200(args):
         # state reset + L2 flush are outside the timed events
         poses.copy_(D["poses"]); patches.copy_(D["patches"])
         flush.fill_(1)
-        e = [ev() for _ in range(5)]
+        e = [ev() for _ in range(4)]
         e[0].record()
-        c0, = cc.forward(D["gmap"], D["f0"], D["c0"], D["ii1"], D["jj1"], 3)
+        corr = altcorr.corr_stacked(D["gmap"], (D["f0"], D["f1"]), D["c0"], D["ii1"], D["jj1"], 3)   # DPVO.corr, one call
         e[1].record()
-        c1, = cc.forward(D["gmap"], D["f1"], D["c1"], D["ii1"], D["jj1"], 3)
-        e[2].record()
         ix, jx = cb.neighbors(D["kk"], D["jj"])
-        e[3].record()
+        e[2].record()
         cb.forward(poses, patches, D["intr"], D["target"], D["weight"], D["lmbda"], D["ii"], D["jj"], D["kk"], t0, t1, 2)
-        e[4].record()
+        e[3].record()
         if timed:
             marks.setdefault("ev", []).append(e)
-        return c0, c1, ix
+        return corr, ix
 
     def barrier():
         if world > 1:
@@ -325,7 +327,7 @@ def run_b200(args):
     barrier()
     wall = time.perf_counter() - wall0
     clocks = sampler.stop()
-    seg = np.array([[a.elapsed_time(b) for a, b in zip(e[:-1], e[1:])] for e in marks["ev"]])  # ms: L0, L1, neighbors, BA
+    seg = np.array([[a.elapsed_time(b) for a, b in zip(e[:-1], e[1:])] for e in marks["ev"]])  # ms: corr (both levels, stacked), neighbors, BA
     t_dev = float(seg.sum())  # ms over the K timed steps, flush/reset excluded
     tt = torch.tensor([t_dev], device=dev, dtype=torch.float64)
     if world > 1:
@@ -334,7 +336,7 @@ def run_b200(args):
     # per-rank segment times and clocks, for the record (the value above is the max over ranks)
     per_rank = None
     if world > 1:
-        mine = torch.tensor(list(seg.sum(0) / args.steps) + [clocks["sm_mhz"] or 0.0, float(len(clocks["reasons"]))], device=dev,
+        mine = torch.tensor([float(seg[:, 0].mean()), 0.0, float(seg[:, 1].mean()), float(seg[:, 2].mean())] + [clocks["sm_mhz"] or 0.0, float(len(clocks["reasons"]))], device=dev,
                             dtype=torch.float64)
         allr = [torch.empty_like(mine) for _ in range(world)]
         dist.all_gather(allr, mine)
@@ -344,6 +346,8 @@ def run_b200(args):
     # ---- end to end through the C ABI with HOST buffers (pinned), copies inside the timed region -----------------
     # the call a non-torch embedder makes: hostapi.Session.update == wv_session_update_host (include/wvb200.h)
     T = 7
+    # per-level outputs here: the coarse level's volume goes back to the host while the level-0 ring is still being uploaded
+    # (the stacked layout interleaves the levels, so its download can only start after everything: 231 vs 286 frames/s)
     out0 = torch.empty((1, E, T, T, 3, 3), dtype=torch.half).pin_memory()
     out1 = torch.empty_like(out0).pin_memory()
     hp, hq = H["poses"].clone().pin_memory(), H["patches"].clone().pin_memory()
@@ -363,9 +367,15 @@ def run_b200(args):
     for _ in range(3):
         e2e_step()
     # the e2e result is the product's result: check it once against the device-resident path of the timed loop above
-    c0d, c1d, ixd = step(False)
+    cd, ixd = step(False)
     torch.cuda.synchronize()
-    assert torch.equal(out0, c0d.cpu()) and torch.equal(out1, c1d.cpu()) and torch.equal(nbx, ixd.cpu()), "e2e != device path"
+    cdl = cd.view(1, E, T, T, 3, 3, 2)
+    assert torch.equal(out0, cdl[..., 0].cpu()) and torch.equal(out1, cdl[..., 1].cpu()) and torch.equal(nbx, ixd.cpu()), "e2e != device path"
+    # ... and the stacked volume is the two per-level calls the reference makes, stacked (dpvo/dpvo.py:331-333)
+    two = torch.stack([cc.forward(D["gmap"], D["f0"], D["c0"], D["ii1"], D["jj1"], 3)[0],
+                       cc.forward(D["gmap"], D["f1"], D["c1"], D["ii1"], D["jj1"], 3)[0]], -1).view(1, E, -1)
+    assert torch.equal(cd, two), "stacked corr != two-call form"
+    del two
     assert torch.equal(hp, poses.cpu()), "e2e BA != device path"
     barrier()
     te = time.perf_counter()
@@ -382,28 +392,29 @@ def run_b200(args):
     if rank == 0:
         K = args.steps
         peak, peak_src = measured_peak_gbs()
-        l0_ms = float(seg[:, 0].mean())
-        achieved = CORR_BYTES_L0 * E / (l0_ms * 1e-3) / 1e9
+        corr_ms = float(seg[:, 0].mean())
+        achieved = (CORR_BYTES_L0 + CORR_BYTES_L1) * E / (corr_ms * 1e-3) / 1e9
         line = {
             "metric": "dpvo_hotpath_frames_per_s", "value": world * K / (t_max * 1e-3), "unit": "frames/s", "n_gpus": world, "steps": K,
             "warmup": max(args.warmup, 3), "ms_per_step": t_max / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f16 maps / f32 accumulate+geometry", "data": "synthetic",
             "config": {"workload": WORKLOAD, "parallelism": f"replicas x{world} (one clip per GPU, no collective)",
                        "l2": "512 MB fill before every timed step (outside the CUDA-event intervals); maps+outputs are 210 MB > L2"},
-            "ms_breakdown": {"corr_l0": l0_ms, "corr_l1": float(seg[:, 1].mean()), "neighbors": float(seg[:, 2].mean()),
-                             "ba_2iters": float(seg[:, 3].mean())},
-            "corr_gbs": (CORR_BYTES_L0 + CORR_BYTES_L1) * E / (float(seg[:, :2].sum(1).mean()) * 1e-3) / 1e9,
-            "ba_iters_per_s": 2.0 / (float(seg[:, 3].mean()) * 1e-3),
+            "ms_breakdown": {"corr_both_levels_stacked": corr_ms, "neighbors": float(seg[:, 1].mean()),
+                             "ba_2iters": float(seg[:, 2].mean())},
+            "corr_gbs": achieved,
+            "ba_iters_per_s": 2.0 / (float(seg[:, 2].mean()) * 1e-3),
             "wall_ms_per_step_incl_flush": 1e3 * wall / K,
-            "roofline": {"kernel": "corr forward, level 0 (fp16 maps)", "bound": "hbm", "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": achieved / peak, "traffic": NCU_TRAFFIC_L0, "peak_source": peak_src,
-                         "traffic_source": "dram__bytes_read+write of restage_kernel + corr_tc5_kernel, ncu --set full, profiles/r1_final_ncu_summary.txt",
-                         "algorithmic_bytes_per_launch": CORR_BYTES_L0 * E},
+            "roofline": {"kernel": "DPVO.corr: corr forward on both levels, stacked (restage_kernel x2 + corr_tc5_kernel<2>, fp16 maps)",
+                         "bound": "hbm", "achieved": achieved, "peak": peak,
+                         "unit": "GB/s", "frac": achieved / peak, "traffic": NCU_TRAFFIC_CORR, "peak_source": peak_src,
+                         "traffic_source": "dram__bytes_read+write of restage_kernel x2 + corr_tc5_kernel<2>, ncu --set full, profiles/r1_stacked_ncu_summary.txt",
+                         "algorithmic_bytes_per_launch": (CORR_BYTES_L0 + CORR_BYTES_L1) * E},
             "e2e": {"value": world * K / te, "unit": "frames/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "api": "hostapi.Session.update -> wv_session_update_host (C ABI, pinned host buffers, 3 streams)"},
-            "per_rank": {"columns": ["corr_l0_ms", "corr_l1_ms", "neighbors_ms", "ba_ms", "sm_mhz", "n_throttle_reasons"], "rows": per_rank},
-            "gpu_launches": 6 * K,
-            "gpu_launches_per_step": "corr: (restage + tcgen05 tile kernel) x2 levels; plan kernel (neighbors; its plan is reused by BA); window kernel (BA) -- profiles/r1_launches_final.csv",
+            "per_rank": {"columns": ["corr_ms", "-", "neighbors_ms", "ba_ms", "sm_mhz", "n_throttle_reasons"], "rows": per_rank},
+            "gpu_launches": 5 * K,
+            "gpu_launches_per_step": "corr: restage x2 levels + ONE two-level tcgen05 tile kernel; plan kernel (neighbors; its plan is reused by BA); window kernel (BA) -- profiles/r1_launches_stacked.csv",
             "clocks": clocks,
         }
         if world == 1 and not args.no_cpu:

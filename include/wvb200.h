@@ -287,6 +287,9 @@ typedef struct {
   const float* patches_est; float mu;             /* nullable prior (see wv_ba_forward) */
   int64_t* nb_ix; int64_t* nb_jx;                 /* nullable: neighbors(kk, jj) */
   int status;                                     /* out: WV_STATUS_* bits */
+  /* nullable, nlevels == 2, tracker configuration only: both levels as ONE volume [B][E][2r+1][2r+1][P][P][2] (DPVO.corr's
+   * torch.stack layout, see wv_corr_forward_stacked) instead of corr_out[0..1]; WV_EUNSUPPORTED for other shapes */
+  void* corr_stacked_out;
 } wv_update_args;
 
 wv_session* wv_session_create(void);              /* on the current device; NULL on failure */

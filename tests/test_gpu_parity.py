@@ -475,6 +475,21 @@ def test_host_session_update_matches_device_path(syn):
         assert np.array_equal(ba["poses"].numpy(), poses) and np.array_equal(ba["patches"].numpy(), patches)
         oi, oj = oracle.neighbors(s["kk"], s["jj"])
         assert np.array_equal(ba["nb_ix"].numpy(), oi) and np.array_equal(ba["nb_jx"].numpy(), oj)
+    # the same update with both levels as one stacked volume (DPVO.corr's layout): out0 / out1 above came from the tiled kernel last? no --
+    # recompute the tiled per-level outputs and compare the interleaved pairs bit for bit
+    os.environ["WVB200_CORR_TILED"] = "1"
+    try:
+        c0 = run_corr(g16.float().numpy(), f0.float().numpy(), w["coords"], w["ii1"], w["jj1"], 3, torch.float16)
+        c1 = run_corr(g16.float().numpy(), f1.float().numpy(), (w["coords"] * 0.25).astype(np.float32), w["ii1"], w["jj1"], 3, torch.float16)
+    finally:
+        del os.environ["WVB200_CORR_TILED"]
+    st = torch.empty((1, E, 882), dtype=torch.half)
+    ba["poses"].copy_(T("poses")); ba["patches"].copy_(T("patches"))
+    sess.update(g16, [f0, f1], co, ii1, jj1, None, ba=ba, iterations=2, corr_stacked_out=st)
+    assert np.array_equal(st.float().numpy(), np.stack([c0, c1], -1).reshape(1, E, 882))
+    assert np.array_equal(ba["poses"].numpy(), poses)
+    with pytest.raises(RuntimeError):   # fp32 maps: the two-level kernel does not cover them, the session says so
+        sess.update(g16.float(), [f0.float(), f1.float()], co, ii1, jj1, None, corr_stacked_out=st.float(), ba=None)
     sess.close()
 
 

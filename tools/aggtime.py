@@ -33,6 +33,9 @@ for name, keys in (("kk", s["kk"]), ("ii*12345+jj", s["ii"] * 12345 + s["jj"])):
         return blocks.scatter_softmax_sum(f, g, plan)
     jx, plan = blocks.group_plan(ix, lo, hi)
     kernel_only = lambda: blocks.scatter_softmax_sum(f, g, plan)
+    if len(sys.argv) > 1 and sys.argv[1] == "kernel":       # sweep mode: the kernel alone
+        print(f"{name}: kernel alone {timeit(kernel_only):.4f} ms", flush=True)
+        continue
     t_c, t_f, t_k, t_n = timeit(composed), timeit(fused), timeit(kernel_only), timeit(fused_nosync)
     gbs = (2 * E * D * 2 + plan[3] * D * 2) / (t_k * 1e-3) / 1e9
     print(f"{name}: G={plan[3]}  composed torch ops {t_c:.4f} ms   plan+kernel {t_f:.4f} ms (no host read: {t_n:.4f} ms)   kernel alone {t_k:.4f} ms = {gbs:.0f} GB/s algorithmic", flush=True)

@@ -1,1 +1,1 @@
-from .correlation import corr, patchify, CorrLayer, PatchLayer  # noqa: F401
+from .correlation import corr, corr_stacked, patchify, CorrLayer, PatchLayer  # noqa: F401

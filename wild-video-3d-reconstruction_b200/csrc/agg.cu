@@ -11,9 +11,11 @@
 //                among the present keys (== torch.unique's sorted order), then member lists per group in ascending edge order
 //                (counting fill + a per-group rank sort), so that the reduction order is fixed: results are deterministic.
 //   soft_agg     ONE pass over f(x) and g(x): a CTA per group, a thread owns 16 bytes of channels and a share of the group's members
-//                and walks them twice (max, then exp / sum / weighted sum; the second walk hits L1/L2), fp32 arithmetic, one
-//                rounding at the end.
+//                and walks them once in chunks of four (online softmax: running max, rescaled sums), fp32 arithmetic, one rounding
+//                at the end.
 //                HBM-bound: algorithmic bytes = 2 * E * D * sizeof(T) read + G * D * sizeof(T) written.
+#include <cstdlib>
+
 #include "wv_common.cuh"
 
 namespace wv {
@@ -196,103 +198,106 @@ template <typename T> struct Vec<T, 1> {
   static __device__ __forceinline__ void store(T* p, const float* v) { *p = from_f32<T>(v[0]); }
 };
 
-// One CTA per (batch, group): thread (split, cl) owns V channels and a contiguous share of the group's members.  Walk 1 leaves each
-// split's per-channel maximum in shared memory; every thread then takes the maximum over the splits, walk 2 accumulates
-// sum(exp) and sum(f * exp) over its share (the rows come back from L1/L2), and split 0 adds the partial sums in split order.
-// The order of every addition is a function of (group size, splits) only: results are deterministic.
-template <typename T, int V>
-__global__ void __launch_bounds__(1024) soft_agg_kernel(const T* __restrict__ fx, const T* __restrict__ gx, const int* __restrict__ order,
+// A CTA works on GP (batch, group) rows at a time: thread (slot, split, cl) owns V channels and a contiguous share of its group's
+// members, which it walks ONCE in chunks of CH: the score rows and value rows of a chunk are loaded together with the member ids of
+// the NEXT chunk (2 CH + CH independent loads in flight per thread), the running maximum moves to the chunk's maximum and the partial
+// sums are rescaled by exp(old max - new max) (the online form of the same softmax).  With S > 1 the splits' (max, sum, weighted sum)
+// triples meet in shared memory and split 0 merges them in split order.  The order of every addition is a function of
+// (group size, S, CH) only: deterministic.
+template <typename T, int V, int CH>
+__global__ void __launch_bounds__(512) soft_agg_kernel(const T* __restrict__ fx, const T* __restrict__ gx, const int* __restrict__ order,
                                                         const int* __restrict__ offsets, const int* __restrict__ n_groups, T* __restrict__ y,
-                                                        int B, long long E, int D, long long Gcap, int tpc, int S) {
-  extern __shared__ float red[];                          // [2][S][tpc * V]
-  const int cpb = tpc * V;                               // channels per pass of the block
-  float* red0 = red;
-  float* red1 = red + (size_t)S * cpb;
-  const int split = threadIdx.x / tpc, cl = threadIdx.x - split * tpc;
+                                                        int B, long long E, int D, long long Gcap, int tpc, int S, int GP) {
+  extern __shared__ float red[];                          // [3][GP][S][tpc * V]
+  const int cpb = tpc * V;                               // channels per pass of a slot
+  const int slot = threadIdx.x / (S * tpc), ts = threadIdx.x - slot * (S * tpc);
+  const int split = ts / tpc, cl = ts - split * tpc;
+  const size_t plane = (size_t)GP * S * cpb;
+  float* r0 = red + (size_t)slot * S * cpb + cl * V;     // split 0's triple of this (slot, channel vector)
+  float* rm = r0 + (size_t)split * cpb;                  // this thread's; + plane: sums; + 2 * plane: weighted sums
   const int G = (int)min((long long)*n_groups, Gcap);
-  for (long long bg = blockIdx.x; bg < (long long)B * Gcap; bg += gridDim.x) {
-    const int g = (int)(bg % Gcap), b = (int)(bg / Gcap);
+  const long long rows = (long long)B * Gcap;
+  for (long long bg0 = (long long)blockIdx.x * GP; bg0 < rows; bg0 += (long long)gridDim.x * GP) {
+    const long long bg = bg0 + slot;
+    const bool live = bg < rows;
+    const int g = live ? (int)(bg % Gcap) : 0, b = live ? (int)(bg / Gcap) : 0;
     T* yrow = y + ((long long)b * Gcap + g) * D;
-    if (g >= G) {                                         // rows beyond the groups present: defined (zero), never gathered
-      for (int c = threadIdx.x; c < D; c += blockDim.x) yrow[c] = from_f32<T>(0.f);
-      continue;
+    const bool grp = live && g < G;
+    if (live && !grp) {                                   // rows beyond the groups present: defined (zero), never gathered
+      for (int c = ts; c < D; c += S * tpc) yrow[c] = from_f32<T>(0.f);
     }
-    const int lo = offsets[g], n = offsets[g + 1] - lo;
-    const int m0 = lo + (int)((long long)n * split / S), m1 = lo + (int)((long long)n * (split + 1) / S);
+    int m0 = 0, m1 = 0;
+    if (grp) {
+      const int lo = offsets[g], n = offsets[g + 1] - lo;
+      m0 = lo + (int)((long long)n * split / S); m1 = lo + (int)((long long)n * (split + 1) / S);
+    }
     for (int c0 = 0; c0 < D; c0 += cpb) {
       const int c = c0 + cl * V;
-      const bool act = c < D;
+      const bool act = grp && c < D;
       const T* fb = fx + ((long long)b * E) * D + c;
       const T* gb = gx + ((long long)b * E) * D + c;
       float mx[V], s[V], a[V];
 #pragma unroll
       for (int i = 0; i < V; i++) { mx[i] = -INFINITY; s[i] = 0.f; a[i] = 0.f; }
-      if (act) {
-        int m = m0;
-        for (; m + 4 <= m1; m += 4) {
-          Vec<T, V> r[4];
+      if (act && m0 < m1) {
+        int en[CH];
 #pragma unroll
-          for (int u = 0; u < 4; u++) r[u].load(gb + (long long)order[m + u] * D);
+        for (int u = 0; u < CH; u++) en[u] = order[m0 + (m0 + u < m1 ? u : 0)];   // a short chunk repeats its first member (masked below)
+        for (int m = m0; m < m1; m += CH) {
+          const int cnt = min(CH, m1 - m);
+          Vec<T, V> rg[CH], rf[CH];
 #pragma unroll
-          for (int u = 0; u < 4; u++) {
+          for (int u = 0; u < CH; u++) { rg[u].load(gb + (long long)en[u] * D); rf[u].load(fb + (long long)en[u] * D); }
+          if (m + CH < m1) {
+#pragma unroll
+            for (int u = 0; u < CH; u++) en[u] = order[m + CH + (m + CH + u < m1 ? u : 0)];
+          }
+          float nm[V];
+#pragma unroll
+          for (int i = 0; i < V; i++) nm[i] = mx[i];
+#pragma unroll
+          for (int u = 0; u < CH; u++) {
             float v[V];
-            r[u].get(v);
+            rg[u].get(v);
 #pragma unroll
-            for (int i = 0; i < V; i++) mx[i] = fmaxf(mx[i], v[i]);
+            for (int i = 0; i < V; i++) nm[i] = fmaxf(nm[i], v[i]);       // (a repeated member cannot raise the maximum)
           }
-        }
-        for (; m < m1; m++) {
-          Vec<T, V> r;
-          r.load(gb + (long long)order[m] * D);
-          float v[V];
-          r.get(v);
 #pragma unroll
-          for (int i = 0; i < V; i++) mx[i] = fmaxf(mx[i], v[i]);
+          for (int i = 0; i < V; i++) {
+            const float k = soft_exp<T>(mx[i] - nm[i]);                    // first chunk: exp(-inf) = 0 on zero sums
+            s[i] *= k; a[i] *= k; mx[i] = nm[i];
+          }
+#pragma unroll
+          for (int u = 0; u < CH; u++) {
+            if (u < cnt) {
+              float v[V], f[V];
+              rg[u].get(v); rf[u].get(f);
+#pragma unroll
+              for (int i = 0; i < V; i++) { const float w = soft_exp<T>(v[i] - mx[i]); s[i] += w; a[i] = fmaf(f[i], w, a[i]); }
+            }
+          }
         }
       }
       if (S > 1) {
 #pragma unroll
-        for (int i = 0; i < V; i++) red0[(size_t)split * cpb + cl * V + i] = mx[i];
-        __syncthreads();
-        for (int sp = 0; sp < S; sp++)
-#pragma unroll
-          for (int i = 0; i < V; i++) mx[i] = fmaxf(mx[i], red0[(size_t)sp * cpb + cl * V + i]);
-        __syncthreads();
-      }
-      if (act) {
-        int m = m0;
-        for (; m + 2 <= m1; m += 2) {
-          Vec<T, V> rg[2], rf[2];
-#pragma unroll
-          for (int u = 0; u < 2; u++) { const long long e = order[m + u]; rg[u].load(gb + e * D); rf[u].load(fb + e * D); }
-#pragma unroll
-          for (int u = 0; u < 2; u++) {
-            float v[V], f[V];
-            rg[u].get(v); rf[u].get(f);
-#pragma unroll
-            for (int i = 0; i < V; i++) { const float w = soft_exp<T>(v[i] - mx[i]); s[i] += w; a[i] = fmaf(f[i], w, a[i]); }
-          }
-        }
-        for (; m < m1; m++) {
-          const long long e = order[m];
-          Vec<T, V> rg, rf;
-          rg.load(gb + e * D); rf.load(fb + e * D);
-          float v[V], f[V];
-          rg.get(v); rf.get(f);
-#pragma unroll
-          for (int i = 0; i < V; i++) { const float w = soft_exp<T>(v[i] - mx[i]); s[i] += w; a[i] = fmaf(f[i], w, a[i]); }
-        }
-      }
-      if (S > 1) {
-        if (split > 0) {
-#pragma unroll
-          for (int i = 0; i < V; i++) { red0[(size_t)split * cpb + cl * V + i] = s[i]; red1[(size_t)split * cpb + cl * V + i] = a[i]; }
-        }
+        for (int i = 0; i < V; i++) { rm[i] = mx[i]; rm[plane + i] = s[i]; rm[2 * plane + i] = a[i]; }
         __syncthreads();
         if (split == 0) {
-          for (int sp = 1; sp < S; sp++)
 #pragma unroll
-            for (int i = 0; i < V; i++) { s[i] += red0[(size_t)sp * cpb + cl * V + i]; a[i] += red1[(size_t)sp * cpb + cl * V + i]; }
+          for (int i = 0; i < V; i++) {
+            float M = mx[i];
+            for (int sp = 1; sp < S; sp++) M = fmaxf(M, r0[(size_t)sp * cpb + i]);
+            float ss = 0.f, aa = 0.f;
+            for (int sp = 0; sp < S; sp++) {
+              const float ms = r0[(size_t)sp * cpb + i];
+              if (ms > -INFINITY) {                                        // (a split with no members holds no sum)
+                const float k = soft_exp<T>(ms - M);
+                ss = fmaf(r0[plane + (size_t)sp * cpb + i], k, ss);
+                aa = fmaf(r0[2 * plane + (size_t)sp * cpb + i], k, aa);
+              }
+            }
+            s[i] = ss; a[i] = aa;
+          }
         }
       }
       if (split == 0 && act) {
@@ -355,21 +360,38 @@ int group_plan(const int64_t* keys, long long E, int64_t key_min, long long rang
   return WV_OK;
 }
 
+int agg_env(const char* name, int dflt) {
+  const char* s = getenv(name);
+  return (s && s[0]) ? atoi(s) : dflt;
+}
+
 template <typename T, int V>
 int launch_soft_agg(const void* fx, const void* gx, const int* order, const int* offsets, const int* n_groups, void* y, int B, long long E,
                     int D, long long Gcap, cudaStream_t st) {
   const int cv = (D + V - 1) / V;                        // channel vectors per row
   const int tpc = cv < 128 ? cv : 128;
-  // splits: ~4 members per thread at the average group size, bounded by the block size and 48 KB of partials
+  // splits: one thread walks up to ~`per` members of an average group; groups per CTA: fill 256+ threads, keep >= 2 CTAs per SM
   const long long avg = Gcap > 0 ? (E + Gcap - 1) / Gcap : 1;
-  long long S = (avg + 3) / 4;
+  // (defaults from a sweep on B200 at E = 45 312, D = 384 fp16, groups of ~21 and ~96 members: profiles/r1_softagg_sweep.txt)
+  const int per = agg_env("WVB200_AGG_PER", 48), smax = agg_env("WVB200_AGG_SMAX", 4), ch = agg_env("WVB200_AGG_CHUNK", 4);
+  const int tmax = agg_env("WVB200_AGG_THREADS", 192);
+  long long S = (avg + per - 1) / per;
   S = S < 1 ? 1 : S;
-  S = S > 8 ? 8 : S;
-  while (S > 1 && (S * tpc > 1024 || S * tpc * V * 8 > 48 * 1024)) S--;
-  const long long blocks = (long long)B * Gcap;
+  S = S > smax ? smax : S;
+  while (S > 1 && S * tpc > 512) S--;
+  const long long rows = (long long)B * Gcap;
+  long long GP = tmax / (S * tpc);
+  GP = GP < 1 ? 1 : GP;
+  while (GP > 1 && (rows + GP - 1) / GP < 2LL * sm_count()) GP--;
+  while ((S > 1 || GP > 1) && S * GP * tpc * V * 12 > 48 * 1024) { if (GP > 1) GP--; else S--; }
+  const long long blocks = (rows + GP - 1) / GP;
   const int grid = (int)(blocks < (long long)sm_count() * 64 ? blocks : (long long)sm_count() * 64);
-  const size_t smem = S > 1 ? (size_t)S * tpc * V * 8 : 0;
-  soft_agg_kernel<T, V><<<grid, (int)(S * tpc), smem, st>>>((const T*)fx, (const T*)gx, order, offsets, n_groups, (T*)y, B, E, D, Gcap, tpc, (int)S);
+  const size_t smem = S > 1 ? (size_t)S * GP * tpc * V * 12 : 0;
+  const int threads = (int)(S * GP * tpc);
+  if (ch == 4)
+    soft_agg_kernel<T, V, 4><<<grid, threads, smem, st>>>((const T*)fx, (const T*)gx, order, offsets, n_groups, (T*)y, B, E, D, Gcap, tpc, (int)S, (int)GP);
+  else
+    soft_agg_kernel<T, V, 2><<<grid, threads, smem, st>>>((const T*)fx, (const T*)gx, order, offsets, n_groups, (T*)y, B, E, D, Gcap, tpc, (int)S, (int)GP);
   WV_LAUNCH_CHECK();
   return WV_OK;
 }

@@ -241,6 +241,12 @@ int wv_session_update_host(wv_session* s, wv_update_args* a) {
     bw[l] = wv_corr_workspace_bytes(a->dtype, a->B, a->E, a->C, a->P, a->P, a->n1, a->n2, a->H2[l], a->W2[l], a->radius);
     of[l] = take(b2[l]); ocs[l] = take(bc); oo[l] = take(bo); ow[l] = take(bw[l] + 1024);
   }
+  // two levels into ONE stacked volume (DPVO.corr's layout) when the caller asks for it and the two-level kernel covers the shape
+  const size_t bws = (a->corr_stacked_out && a->nlevels == 2)
+                         ? wv_corr_stacked_workspace_bytes(a->dtype, a->B, a->E, a->C, a->P, a->P, a->n1, a->n2, a->H2[0], a->W2[0], a->H2[1], a->W2[1], a->radius)
+                         : 0;
+  if (a->corr_stacked_out && bws == 0) return WV_EUNSUPPORTED;
+  const size_t ows = bws ? take(bws + 1024) : 0, oos = bws ? take(2 * bo) : 0;
   const size_t bp = (size_t)a->n_poses * 7 * 4, bq = (size_t)a->n_patches * 3 * PP * 4, bn = (size_t)a->n_poses * 4 * 4, bt = (size_t)a->E * 2 * 4;
   const size_t bwb = do_ba ? std::max(wv_ba_workspace_bytes(a->E, a->n_patches, a->t1 - a->t0), wv_ba_workspace_bytes(a->E, (int64_t)1 << 22, a->t1 - a->t0)) : 0;
   size_t op = 0, oq = 0, oe = 0, on = 0, otg = 0, owt = 0, ol = 0, oi = 0, oj = 0, ok = 0, owb = 0, onx = 0, onj = 0;
@@ -310,7 +316,18 @@ int wv_session_update_host(wv_session* s, wv_update_args* a) {
       SS_TRY(cudaMemcpyAsync(a->nb_jx, d + onj, bi, cudaMemcpyDeviceToHost, s->s_out));
     }
   }
-  for (int l = a->nlevels - 1; l >= 0; l--) {
+  if (bws) {
+    SS_TRY(cudaStreamWaitEvent(s->s_cmp, s->ev_f[0], 0));  // level 0 is uploaded last
+    char* wsp = (char*)(((uintptr_t)(d + ows) + 1023) & ~(uintptr_t)1023);
+    rc = wv_corr_forward_stacked(d + o1, d + of[0], d + of[1], (const float*)(d + oc), a->coord_scale[0], a->coord_scale[1],
+                                 (const int64_t*)(d + oii), (const int64_t*)(d + ojj), d + oos, a->dtype, a->B, a->E, a->C, a->P, a->P,
+                                 a->n1, a->n2, a->H2[0], a->W2[0], a->H2[1], a->W2[1], a->radius, wsp, bws, dstatus, (wv_stream_t)s->s_cmp);
+    if (rc != WV_OK) goto fail;
+    SS_TRY(cudaEventRecord(s->ev_c[0], s->s_cmp));
+    SS_TRY(cudaStreamWaitEvent(s->s_out, s->ev_c[0], 0));
+    SS_TRY(cudaMemcpyAsync(a->corr_stacked_out, d + oos, 2 * bo, cudaMemcpyDeviceToHost, s->s_out));
+  }
+  for (int l = a->nlevels - 1; l >= 0 && !bws; l--) {
     SS_TRY(cudaStreamWaitEvent(s->s_cmp, s->ev_f[l], 0));
     const float* cl = (const float*)(d + oc);
     if (a->coord_scale[l] != 1.0f) {

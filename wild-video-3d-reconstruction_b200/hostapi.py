@@ -2,6 +2,7 @@
 
     s = hostapi.Session()
     s.update(gmap, [fmap_l0, fmap_l1], coords, ii1, jj1, corr_out=[out0, out1], ba=dict(poses=..., patches=..., ...))
+    s.update(gmap, [fmap_l0, fmap_l1], coords, ii1, jj1, None, corr_stacked_out=out882, ba=...)     # DPVO.corr's stacked layout
 
 One call = one tracker update() on the replaced path (dpvo/dpvo.py:711-749): altcorr.corr on every pyramid level,
 fastba.neighbors and fastba.BA on the same edge list.  All arrays are HOST arrays (numpy, or pinned torch CPU tensors);
@@ -29,6 +30,7 @@ class UpdateArgs(ctypes.Structure):
         ("kk", ctypes.c_void_p), ("n_poses", ctypes.c_int64), ("n_patches", ctypes.c_int64), ("t0", ctypes.c_int),
         ("t1", ctypes.c_int), ("iterations", ctypes.c_int), ("patches_est", ctypes.c_void_p), ("mu", ctypes.c_float),
         ("nb_ix", ctypes.c_void_p), ("nb_jx", ctypes.c_void_p), ("status", ctypes.c_int),
+        ("corr_stacked_out", ctypes.c_void_p),
     ]
 
 
@@ -63,7 +65,10 @@ class Session:
 
     __del__ = close
 
-    def make_args(self, fmap1, fmap2_levels, coords, ii1, jj1, corr_out, radius=3, coord_scale=None, ba=None, iterations=2):
+    def make_args(self, fmap1, fmap2_levels, coords, ii1, jj1, corr_out, radius=3, coord_scale=None, ba=None, iterations=2,
+                  corr_stacked_out=None):
+        """corr_out: one [B,E,7,7,P,P] array per level -- or None with corr_stacked_out = ONE [B,E,7*7*P*P*2] array in DPVO.corr's
+        stacked layout (two levels, tracker configuration)"""
         a = UpdateArgs()
         B, n1, C, P, _ = fmap1.shape
         a.dtype = WV_F16 if _is_half(fmap1) else WV_F32
@@ -75,7 +80,10 @@ class Session:
             a.fmap2[l] = _ptr(f).value
             a.H2[l], a.W2[l] = f.shape[3], f.shape[4]
             a.coord_scale[l] = (coord_scale[l] if coord_scale is not None else 0.25 ** l)
-            a.corr_out[l] = _ptr(corr_out[l]).value
+            if corr_out is not None:
+                a.corr_out[l] = _ptr(corr_out[l]).value
+        a.corr_stacked_out = _ptr(corr_stacked_out)
+        assert corr_out is not None or corr_stacked_out is not None
         a.coords, a.ii1, a.jj1 = _ptr(coords), _ptr(ii1), _ptr(jj1)
         a.iterations = 0
         if ba is not None:
