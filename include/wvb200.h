@@ -240,6 +240,17 @@ int wv_solve_system_host(const float* J_i, const float* J_j, const int64_t* ii, 
                          const float* res, int64_t r, float ep, float lm, int freen, float* delta,
                          int64_t* n_out);
 
+/* ---- COLMAP text export (dpvo/plot_utils.py:58-93) -- HOST pointers, synchronous, no device work ----------
+ * The rows of points3D.txt / images.txt exactly as the reference's f-strings produce them (numbers in CPython's float repr),
+ * written in one pass instead of Python `+=` per row.  Return the number of bytes written, WV_EWORKSPACE when `cap` is too
+ * small (180 bytes per point row, 260 + name length per image row always suffice), or WV_EINVAL.
+ *   wv_format_f64: repr(float(v)) into out32 (>= 32 bytes), returns its length -- the formatter itself, exported for tests.
+ *   points: xyz [n][3] (the float32 point cloud widened to double, as .tolist() does), rgb [n][3] uint8, ids first_id ...
+ *   images: pose7 [n][7] = (qw, qx, qy, qz, x, y, z) camera-from-world, names = n NUL-terminated strings back to back. */
+int wv_format_f64(double v, char* out32);
+int64_t wv_colmap_points3d_text(const double* xyz, const uint8_t* rgb, int64_t n, int64_t first_id, char* out, int64_t cap);
+int64_t wv_colmap_images_text(const double* pose7, const char* names, int64_t n, char* out, int64_t cap);
+
 /* ---------------------------------------------------------------------------------------------
  * host-buffer entry points (pinned or pageable HOST memory in, HOST memory out): the call a
  * non-torch embedder makes; copies are enqueued on `stream` around the same kernels and the call

@@ -228,3 +228,65 @@ def test_ba_sharded_host_logic_gloo_two_ranks():
         builds = [c for c in res[3] if c[0] == "build"]
         assert [b[1:3] for b in builds] == [(rank, 2), (rank, 2)] and [b[3] for b in builds] == [True, False]
         assert [c[1:] for c in res[3] if c[0] == "dz"] == [(rank, 2), (rank, 2)]
+
+
+# ------------------------------------------------------------------------------------------------- COLMAP text export
+def test_float_formatter_is_cpython_repr():
+    """every number of the export goes through wv_format_f64; the reference formats with f-strings / str(): CPython's float repr"""
+    import random
+    import struct
+    lib = ctypes.CDLL(os.path.join(ROOT, PKG, "libwvb200.so"))
+    lib.wv_format_f64.argtypes = [ctypes.c_double, ctypes.c_char_p]
+    buf = ctypes.create_string_buffer(64)
+    rnd = random.Random(7)
+    vals = [0.0, -0.0, 1.0, -1.5, 1e16, 1e15, 9999999999999998.0, 1e17, 1e-4, 1e-5, 0.0001234, 123456.789, 5e-324, 1.7976931348623157e308,
+            float("inf"), float("-inf"), float("nan"), 0.1, 1 / 3, 2.5e-7, 1e22, 1e21, 123456789012345678.0]
+    vals += [struct.unpack("d", struct.pack("Q", rnd.getrandbits(64)))[0] for _ in range(20000)]
+    vals += [float(np.float32(rnd.uniform(-100, 100))) for _ in range(20000)]
+    vals += [rnd.uniform(-1, 1) * 10 ** rnd.randint(-8, 20) for _ in range(20000)]
+    for v in vals:
+        n = lib.wv_format_f64(v, buf)
+        assert buf.raw[:n].decode() == repr(v), v
+    for v in vals[:5000]:   # the pose columns are numpy float64 scalars in an f-string: same text
+        assert f"{np.float64(v)}" == repr(v)
+
+
+@pytest.mark.parametrize("case", ["plain", "named"])
+def test_colmap_export_is_byte_identical_to_the_reference(case, tmp_path):
+    """tests/golden/colmap_ref/*.npz: inputs + the three files written by the reference's own save_output_for_COLMAP
+    (oracle/make_golden_colmap.py)"""
+    ce = importlib.import_module(PKG + ".colmap_export")
+    g = np.load(os.path.join(ROOT, "tests", "golden", "colmap_ref", case + ".npz"))
+    poses, tstamps = g["poses"], g["tstamps"]
+    if bool(g["with_images"]):
+        os.makedirs(tmp_path / "images")
+        for i in range(len(poses)):
+            open(tmp_path / "images" / f"frame_{i:05d}.{'png' if i % 2 else 'jpg'}", "w").close()
+    traj = ce.Trajectory(positions_xyz=poses[:, :3], orientations_quat_wxyz=poses[:, [6, 3, 4, 5]], timestamps=tstamps)   # dpvo_demo.py:187-192
+    ce.save_output_for_COLMAP(str(tmp_path / "colmap"), tstamps, traj, g["points"], g["colors"], False, *g["calib"], 384, 512)
+    for f in ("images.txt", "points3D.txt", "cameras.txt"):
+        want = bytes(g[f.replace(".", "_")])
+        got = open(tmp_path / "colmap" / f, "rb").read()
+        assert got == want, f
+    with pytest.raises(NotImplementedError):
+        ce.save_output_for_COLMAP(str(tmp_path / "colmap"), tstamps, traj, g["points"], g["colors"], True, *g["calib"], 384, 512)
+
+
+def test_colmap_export_large_and_edge_cases(tmp_path):
+    ce = importlib.import_module(PKG + ".colmap_export")
+    rng = np.random.default_rng(0)
+    n = 200000
+    pts = (rng.standard_normal((n, 3)) * 50).astype(np.float32)
+    col = rng.integers(0, 256, (n, 3)).astype(np.uint8)
+    txt = ce.points3d_text(pts, col)
+    lines = txt.split("\n")
+    assert len(lines) == n + 1 and lines[-1] == ""
+    for i in (0, 1, 777, n - 1):    # the reference's row expression, plot_utils.py:91-92
+        p, c = pts[i].tolist(), col[i].tolist()
+        assert lines[i] == f"{i + 1} " + " ".join(map(str, p + c)) + " 0.0 0 0 0 0 0 0"
+    assert ce.points3d_text(np.zeros((0, 3), np.float32), np.zeros((0, 3), np.uint8)) == ""
+    assert ce.images_text(np.zeros((0, 4)), np.zeros((0, 3)), []) == ""
+    q = rng.standard_normal(4); q /= np.linalg.norm(q)
+    M = ce.quaternion_matrix(q)
+    q2 = ce.quaternion_from_matrix(M)
+    assert np.allclose(q2, q if q[0] >= 0 else -q, atol=1e-12)
