@@ -185,6 +185,22 @@ template <> struct Vec<__half, 8> {
     *reinterpret_cast<uint4*>(p) = w;
   }
 };
+template <> struct Vec<__half, 4> {
+  uint2 r;
+  __device__ __forceinline__ void load(const __half* p) { r = *reinterpret_cast<const uint2*>(p); }
+  __device__ __forceinline__ void get(float* o) const {
+    const __half2* h = reinterpret_cast<const __half2*>(&r);
+#pragma unroll
+    for (int i = 0; i < 2; i++) { const float2 f = __half22float2(h[i]); o[2 * i] = f.x; o[2 * i + 1] = f.y; }
+  }
+  static __device__ __forceinline__ void store(__half* p, const float* v) {
+    uint2 w;
+    __half2* h = reinterpret_cast<__half2*>(&w);
+#pragma unroll
+    for (int i = 0; i < 2; i++) h[i] = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
+    *reinterpret_cast<uint2*>(p) = w;
+  }
+};
 template <> struct Vec<float, 4> {
   float4 r;
   __device__ __forceinline__ void load(const float* p) { r = *reinterpret_cast<const float4*>(p); }
@@ -374,7 +390,7 @@ int launch_soft_agg(const void* fx, const void* gx, const int* order, const int*
   const long long avg = Gcap > 0 ? (E + Gcap - 1) / Gcap : 1;
   // (defaults from a sweep on B200 at E = 45 312, D = 384 fp16, groups of ~21 and ~96 members: profiles/r1_softagg_sweep.txt)
   const int per = agg_env("WVB200_AGG_PER", 48), smax = agg_env("WVB200_AGG_SMAX", 4), ch = agg_env("WVB200_AGG_CHUNK", 4);
-  const int tmax = agg_env("WVB200_AGG_THREADS", 192);
+  const int tmax = agg_env("WVB200_AGG_THREADS", 96);
   long long S = (avg + per - 1) / per;
   S = S < 1 ? 1 : S;
   S = S > smax ? smax : S;
@@ -401,7 +417,8 @@ int soft_agg_forward(const void* fx, const void* gx, const int* order, const int
   const bool al16 = ((reinterpret_cast<uintptr_t>(fx) | reinterpret_cast<uintptr_t>(gx) | reinterpret_cast<uintptr_t>(y)) & 15) == 0;
   if ((long long)B * Gcap == 0) return WV_OK;
   if (dtype == WV_F16) {
-    if (D % 8 == 0 && al16) return launch_soft_agg<__half, 8>(fx, gx, order, offsets, n_groups, y, B, E, D, Gcap, st);
+    if (D % 8 == 0 && al16 && agg_env("WVB200_AGG_VEC", 8) == 8) return launch_soft_agg<__half, 8>(fx, gx, order, offsets, n_groups, y, B, E, D, Gcap, st);
+    if (D % 4 == 0 && al16) return launch_soft_agg<__half, 4>(fx, gx, order, offsets, n_groups, y, B, E, D, Gcap, st);
     return launch_soft_agg<__half, 1>(fx, gx, order, offsets, n_groups, y, B, E, D, Gcap, st);
   }
   if (D % 4 == 0 && al16) return launch_soft_agg<float, 4>(fx, gx, order, offsets, n_groups, y, B, E, D, Gcap, st);
