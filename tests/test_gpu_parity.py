@@ -342,6 +342,22 @@ def test_corr_tiled_magnified_patches_and_odd_map(syn):
     assert np.abs(out).max() > 0.1
 
 
+def test_corr_tiled_every_window_needs_two_slots(syn):
+    """spacing 1.6 px: every edge is a 12x12 box in two half tiles, so a producer batch of 16 edges wants 32 record slots --
+    more than the record ring may hand out at once (the batch is cut; see the producer)"""
+    rng = np.random.default_rng(21)
+    n1, n2, H, W, E = 30, 4, 48, 64, 1500
+    g = (0.25 * rng.standard_normal((1, n1, 128, 3, 3))).astype(np.float32)
+    f = (0.25 * rng.standard_normal((1, n2, 128, H, W))).astype(np.float32)
+    f1 = (0.25 * rng.standard_normal((1, n2, 128, H // 4, W // 4))).astype(np.float32)
+    ctr = np.stack([rng.uniform(4, W - 4, E), rng.uniform(4, H - 4, E)], -1)
+    gy, gx = np.meshgrid(np.arange(-1, 2), np.arange(-1, 2), indexing="ij")
+    co = np.stack([ctr[:, 0, None, None] + 1.6 * gx, ctr[:, 1, None, None] + 1.6 * gy], 1)[None].astype(np.float32)
+    ii = rng.integers(0, n1, E).astype(np.int64); jj = rng.integers(0, n2, E).astype(np.int64)
+    _check_tiled(g, f, co, ii, jj)
+    _check_stacked(g, f, f1, co, ii, jj)
+
+
 def test_corr_tiled_batch_and_few_edges(syn):
     """B = 2 and fewer edges than consumer warps"""
     rng = np.random.default_rng(8)

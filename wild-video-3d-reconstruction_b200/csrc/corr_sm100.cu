@@ -617,10 +617,9 @@ corr_tc5_kernel(const __grid_constant__ CorrMaps maps, const CorrParams P) {
     // ================================================================= producer
     int sbase = 0;  // slots issued so far (warp-uniform)
     const int nitems = NL * cnt;                      // item = (edge, level), an edge's levels back to back
-    const int nbatch = (nitems + 15) >> 4;
-    for (int bt = 0; bt <= nbatch; bt++) {
-      const int k = 16 * bt + lane;
-      const bool last = bt == nbatch;                 // the batch after the last one carries the end-of-stream slot in lane 0
+    for (int kbase = 0;;) {
+      const int k = kbase + lane;
+      const bool last = kbase >= nitems;              // the batch after the last one carries the end-of-stream slot in lane 0
       const bool valid = !last && lane < 16 && k < nitems;
       const int level = NL == 1 ? 0 : (k & 1);
       const int LH = level ? P.H1 : P.H, LW = level ? P.W1 : P.W;
@@ -670,8 +669,13 @@ corr_tc5_kernel(const __grid_constant__ CorrMaps maps, const CorrParams P) {
       int incl = nsl;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+      // Records of the last 6 slots issued may still be in use (2 stages + 4 accumulators in flight): a batch writes at most
+      // kT5Rec - 6 records; the lanes beyond that (only when most of the 16 windows need two slots) go to the next batch.
+      const unsigned cutmask = __ballot_sync(0xffffffffu, incl > kT5Rec - 6);
+      const int kept = cutmask ? __ffs(cutmask) - 1 : 32;   // >= 13
+      if (lane >= kept) nsl = 0;
       const int myslot = sbase + incl - nsl;
-      const int total = __shfl_sync(0xffffffffu, incl, 31);
+      const int total = __shfl_sync(0xffffffffu, incl, kept - 1);
       for (int part = 0; part < nsl; part++) {
         T5Rec* r = reinterpret_cast<T5Rec*>(recs + ((myslot + part) % kT5Rec) * kT5RecBytes);
         r->kind = kind; r->part = (short)part; r->nparts = (short)nsl; r->level = level; r->be = (int)be;
@@ -706,6 +710,8 @@ corr_tc5_kernel(const __grid_constant__ CorrMaps maps, const CorrParams P) {
         __syncwarp();
       }
       sbase += total;
+      if (last) break;
+      kbase += kept < 16 ? kept : 16;
     }
   } else if (role == 1) {
     // ================================================================= MMA issue (one lane)
