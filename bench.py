@@ -409,7 +409,12 @@ def run_b200(args):
                          "bound": "hbm", "achieved": achieved, "peak": peak,
                          "unit": "GB/s", "frac": achieved / peak, "traffic": NCU_TRAFFIC_CORR, "peak_source": peak_src,
                          "traffic_source": "dram__bytes_read+write of restage_kernel x2 + corr_tc5_kernel<2>, ncu --set full, profiles/r1_stacked_ncu_summary.txt",
-                         "algorithmic_bytes_per_launch": (CORR_BYTES_L0 + CORR_BYTES_L1) * E},
+                         "algorithmic_bytes_per_launch": (CORR_BYTES_L0 + CORR_BYTES_L1) * E,
+                         "dram_gbs_from_traffic": NCU_TRAFFIC_CORR / (corr_ms * 1e-3) / 1e9,
+                         "note": "frac > 1: the SURVEY 8(d) per-edge bytes count every edge's window as an HBM read; neighbouring "
+                                 "windows overlap and the L2 serves them (hit rate 76 %), so DRAM moves traffic/achieved of it. "
+                                 "The tile kernel's own ceiling is the L2->SM tile stream: 90.6 k items x 28 KB per call "
+                                 "(DESIGN.md 3.7)"},
             "e2e": {"value": world * K / te, "unit": "frames/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "api": "hostapi.Session.update -> wv_session_update_host (C ABI, pinned host buffers, 3 streams)"},
             "per_rank": {"columns": ["corr_ms", "-", "neighbors_ms", "ba_ms", "sm_mhz", "n_throttle_reasons"], "rows": per_rank},

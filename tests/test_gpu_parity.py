@@ -817,8 +817,18 @@ def _keys(syn, kind, **kw):
     return (s["kk"] if kind == "kk" else s["ii"] * 12345 + s["jj"]).astype(np.int64)   # dpvo/net.py:88-89
 
 
+@pytest.fixture(params=["coop", "bitmap"])
+def plan_path(request):
+    """both group-plan implementations: the cooperative counting sort shared with the BA (default) and the bitmap + popcount-rank
+    path that serves key ranges beyond 2^22"""
+    if request.param == "bitmap":
+        os.environ["WVB200_AGG_BITMAP_PLAN"] = "1"
+    yield request.param
+    os.environ.pop("WVB200_AGG_BITMAP_PLAN", None)
+
+
 @pytest.mark.parametrize("kind", ["kk", "ij"])
-def test_group_plan_bit_exact_vs_torch_unique(syn, kind):
+def test_group_plan_bit_exact_vs_torch_unique(syn, kind, plan_path):
     agg = pkg().native_agg()
     for kw in (dict(seed=5, n=12, M=6, edges="tracker", lifetime=4, removal=6), dict(seed=2, n=40, M=96, edges="tracker")):
         ix = dev(_keys(syn, kind, **kw))
@@ -832,7 +842,7 @@ def test_group_plan_bit_exact_vs_torch_unique(syn, kind):
             assert np.array_equal(order, np.argsort(j, kind="stable"))   # grouped, ascending edge index inside a group
 
 
-def test_group_plan_edge_cases(syn):
+def test_group_plan_edge_cases(syn, plan_path):
     agg = pkg().native_agg()
     jx, order, offsets, ng, G = agg.group_plan(torch.zeros(0, dtype=torch.long, device="cuda"))
     assert G == 0 and jx.numel() == 0
@@ -847,6 +857,9 @@ def test_group_plan_edge_cases(syn):
     assert agg.group_plan(ix)[4] == 3                           # the failure left nothing behind
     with pytest.raises(RuntimeError):
         agg.group_plan(torch.tensor([0, 1 << 40], device="cuda"))
+    wide = torch.tensor([3, (1 << 27) + 5, 3, 17, (1 << 27) + 5], device="cuda")     # range > 2^22: always the bitmap path
+    jx, order, offsets, ng, G = agg.group_plan(wide)
+    assert G == 3 and jx.tolist() == [0, 2, 0, 1, 2] and order.tolist() == [0, 2, 3, 1, 4]
 
 
 @pytest.mark.parametrize("dtype,D,tol", [(torch.float16, 384, 2.0 ** -10), (torch.float32, 384, 2e-6), (torch.float16, 20, 2.0 ** -10),
@@ -895,7 +908,7 @@ def test_soft_agg_module_matches_composed_reference_form(syn):
     assert xg.grad is not None and torch.isfinite(xg.grad).all() and m.g.weight.grad.abs().sum() > 0
 
 
-def test_soft_agg_full_size_properties(syn):
+def test_soft_agg_full_size_properties(syn, plan_path):
     """E = 45 312, D = 384 fp16 (the tracker's update operator): size-independent properties + an oracle sample"""
     blocks = importlib.import_module(PKG + ".blocks")
     rng = np.random.default_rng(33)

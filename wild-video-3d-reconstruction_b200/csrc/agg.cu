@@ -16,6 +16,7 @@
 //                HBM-bound: algorithmic bytes = 2 * E * D * sizeof(T) read + G * D * sizeof(T) written.
 #include <cstdlib>
 
+#include "ba_plan.cuh"
 #include "wv_common.cuh"
 
 namespace wv {
@@ -327,6 +328,11 @@ __global__ void __launch_bounds__(512) soft_agg_kernel(const T* __restrict__ fx,
   }
 }
 
+int agg_env(const char* name, int dflt) {
+  const char* s = getenv(name);
+  return (s && s[0]) ? atoi(s) : dflt;
+}
+
 inline size_t al256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct PlanWs {
@@ -351,11 +357,28 @@ PlanWs carve(void* ws, long long E, long long range) {
 
 }  // namespace
 
-size_t group_plan_workspace_bytes(long long E, long long range) { return carve(nullptr, E, range).bytes; }
+// Key ranges up to this go through the counting-sort edge plan shared with the BA (ba_plan.cu: ONE cooperative launch; the
+// secondary sort key is the key itself, so a group's members come out in ascending edge order); wider ranges take the bitmap +
+// popcount-rank path below (11 small launches, 1 bit per possible key instead of 16 bytes).
+constexpr long long kCoopRangeMax = 1LL << 22;
+
+size_t group_plan_workspace_bytes(long long E, long long range) {
+  const size_t a = carve(nullptr, E, range).bytes;
+  const size_t b = range <= kCoopRangeMax ? plan_bytes(E, range, plan_grid()) + 256 : 0;
+  return a > b ? a : b;
+}
 
 int group_plan(const int64_t* keys, long long E, int64_t key_min, long long range, int64_t* jx, int* order, int* offsets, int* n_groups,
                void* workspace, size_t workspace_bytes, int* status, cudaStream_t st) {
   if (workspace_bytes < group_plan_workspace_bytes(E, range)) return WV_EWORKSPACE;
+  if (range <= kCoopRangeMax && agg_env("WVB200_AGG_BITMAP_PLAN", 0) == 0) {
+    Plan pl;
+    plan_carve(&pl, reinterpret_cast<void*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~(uintptr_t)255), E, range, plan_grid());
+    pl.eperm = order;       // the caller's arrays receive the member lists directly
+    pl.seg_off = offsets;
+    WV_CUDA_TRY(cudaMemsetAsync(jx, 0, (size_t)E * sizeof(int64_t), st));   // (keys outside the range belong to no group)
+    return plan_build_groups(pl, keys, key_min, keys, nullptr, 0, nullptr, nullptr, jx, n_groups, status, st);
+  }
   const PlanWs p = carve(workspace, E, range);
   const long long W = (range + 31) / 32;
   WV_CUDA_TRY(cudaMemsetAsync(p.bitmap, 0, (size_t)(reinterpret_cast<char*>(p.word_prefix) - reinterpret_cast<char*>(p.bitmap)), st));
@@ -376,10 +399,6 @@ int group_plan(const int64_t* keys, long long E, int64_t key_min, long long rang
   return WV_OK;
 }
 
-int agg_env(const char* name, int dflt) {
-  const char* s = getenv(name);
-  return (s && s[0]) ? atoi(s) : dflt;
-}
 
 template <typename T, int V>
 int launch_soft_agg(const void* fx, const void* gx, const int* order, const int* offsets, const int* n_groups, void* y, int B, long long E,

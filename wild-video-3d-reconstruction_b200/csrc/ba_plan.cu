@@ -46,10 +46,17 @@ struct PlanArgs {
   int64_t* ix;
   int64_t* jx;
   int* status;
+  // group-plan form (SoftAgg, agg.cu): keys are g[e] - goff; rank_out[e] = dense rank of e's key (== torch.unique's inverse
+  // index), mp_out = number of distinct keys
+  int64_t goff;
+  int64_t* rank_out;
+  int* mp_out;
 };
 
+__device__ __forceinline__ int64_t gkey(const PlanArgs& a, int64_t e) { return a.g[e] - a.goff; }
+
 __device__ __forceinline__ bool edge_valid(const PlanArgs& a, int64_t e) {
-  const int64_t gv = a.g[e];
+  const int64_t gv = gkey(a, e);
   if (gv < 0 || gv >= a.p.n_groups) return false;
   if (a.ii) {
     const int64_t i = a.ii[e], j = a.jj[e];
@@ -63,7 +70,7 @@ __device__ void plan_phase_minmax(const PlanArgs& a) {
   int mx = 0, mn = 0, bad = 0;
   for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < a.p.E; e += (int64_t)gridDim.x * blockDim.x) {
     if (!edge_valid(a, e)) { bad = 1; continue; }
-    const int gv = (int)a.g[e];
+    const int gv = (int)gkey(a, e);
     mx = max(mx, gv + 1);
     mn = max(mn, (int)a.p.n_groups - gv);
   }
@@ -97,7 +104,7 @@ __device__ void plan_phase_zero(const PlanArgs& a) {
 __device__ void plan_phase_count(const PlanArgs& a) {
   int gmin, range; plan_window(a, gmin, range);
   for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < a.p.E; e += (int64_t)gridDim.x * blockDim.x)
-    if (edge_valid(a, e)) atomicAdd(&a.p.cnt[(int)a.g[e] - gmin], 1);
+    if (edge_valid(a, e)) atomicAdd(&a.p.cnt[(int)gkey(a, e) - gmin], 1);
 }
 
 // block-wide exclusive scan of (v0, v1); returns totals through t0/t1.  blockDim.x == kPlanThreads.
@@ -172,6 +179,7 @@ __device__ void plan_phase_fill(const PlanArgs& a, int* sh_off /*[gridDim+1]*/, 
     }
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     a.p.hdr->Mp = sh_rank[gridDim.x];
+    if (a.mp_out) *a.mp_out = sh_rank[gridDim.x];
     a.p.seg_off[sh_rank[gridDim.x]] = sh_off[gridDim.x];
   }
   for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < a.p.E; e += (int64_t)gridDim.x * blockDim.x) {
@@ -179,7 +187,7 @@ __device__ void plan_phase_fill(const PlanArgs& a, int* sh_off /*[gridDim+1]*/, 
       if (a.ix) { a.ix[e] = -1; a.jx[e] = -1; }
       continue;
     }
-    const int i = (int)a.g[e] - gmin;
+    const int i = (int)gkey(a, e) - gmin;
     const int off = sh_off[i / chunk] + a.p.loc_off[i];
     const int pos = atomicAdd(&a.p.cursor[i], 1);
     a.p.tmp[off + pos] = (int)e;
@@ -219,6 +227,8 @@ __device__ void plan_phase_order(const PlanArgs& a) {
         a.jx[e] = s + 1 < n ? (int64_t)a.p.eperm[off + s + 1] : -1;
       }
     }
+    if (a.rank_out)
+      for (int s = lane; s < n; s += 32) a.rank_out[a.p.tmp[off + s]] = r;
   }
 }
 
@@ -255,7 +265,12 @@ int plan_grid() { return sm_count(); }
 
 int plan_build(const Plan& p, const int64_t* g, const int64_t* jj, const int64_t* ii, int64_t n_poses, int64_t* ix,
                int64_t* jx, int* status, cudaStream_t st) {
-  PlanArgs a{p, g, jj, ii, n_poses, ix, jx, status};
+  return plan_build_groups(p, g, 0, jj, ii, n_poses, ix, jx, nullptr, nullptr, status, st);
+}
+
+int plan_build_groups(const Plan& p, const int64_t* g, int64_t goff, const int64_t* jj, const int64_t* ii, int64_t n_poses,
+                      int64_t* ix, int64_t* jx, int64_t* rank_out, int* mp_out, int* status, cudaStream_t st) {
+  PlanArgs a{p, g, jj, ii, n_poses, ix, jx, status, goff, rank_out, mp_out};
   WV_CUDA_TRY(cudaMemsetAsync(p.hdr, 0, sizeof(PlanHeader), st));
   const int grid = plan_grid();
   const size_t sh = sizeof(int) * (size_t)(2 * (grid + 1) + 72);

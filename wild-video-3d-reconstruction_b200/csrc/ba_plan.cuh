@@ -49,4 +49,10 @@ size_t plan_carve(Plan* p, void* ws, int64_t E, int64_t n_groups, int max_ctas);
 int plan_build(const Plan& p, const int64_t* g, const int64_t* jj, const int64_t* ii, int64_t n_poses,
                int64_t* ix, int64_t* jx, int* status, cudaStream_t st);
 
+// The same plan for any int64 keys g[e] - goff in [0, n_groups) (SoftAgg's group plan, agg.cu): additionally rank_out[e] = dense
+// rank of e's key among the distinct keys (nullable) and *mp_out = their number (nullable).
+int plan_build_groups(const Plan& p, const int64_t* g, int64_t goff, const int64_t* jj, const int64_t* ii, int64_t n_poses,
+                      int64_t* ix, int64_t* jx, int64_t* rank_out, int* mp_out, int* status, cudaStream_t st);
+int plan_grid();
+
 }  // namespace wv
