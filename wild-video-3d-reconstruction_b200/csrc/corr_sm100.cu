@@ -234,9 +234,10 @@ struct CorrParams {
   float cmul0, cmul1;
 };
 
-struct CorrMaps {  // [level][small | half]
-  CUtensorMap m[4];
+struct CorrMaps {  // [level][10x10 | 12x6 half | 9x9]
+  CUtensorMap m[6];
 };
+constexpr int kBoxTiny = 9;   // windows whose patch pixels fall within one pixel of each other (the coarse level): 81 instead of 100 rows
 
 __device__ __forceinline__ void bulk_copy_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
@@ -531,7 +532,7 @@ corr_tiled_kernel(const __grid_constant__ CUtensorMap map_small, const __grid_co
 namespace {
 
 constexpr int kT5Pipes = 3, kT5Stages = 2, kT5Acc = 4, kT5Rec = 32;
-constexpr int kT5RawStride = 149;                             // odd: the 9 pixel rows start in 9 different banks
+constexpr int kT5RawStride = 161;                             // chosen by a bank simulation of the blend's reads on tracker geometry (2 wavefronts per load)
 constexpr int kT5RawBytes = kPP * kT5RawStride * 4;
 constexpr int kT5Warps = 6;                                   // per pipeline: producer, MMA, 4 consumers
 constexpr int kT5Threads = 32 * kT5Pipes * kT5Warps;          // 384
@@ -623,7 +624,7 @@ corr_tc5_kernel(const __grid_constant__ CorrMaps maps, const CorrParams P) {
       const bool valid = !last && lane < 16 && k < nitems;
       const int level = NL == 1 ? 0 : (k & 1);
       const int LH = level ? P.H1 : P.H, LW = level ? P.W1 : P.W;
-      int kind = 3, x0 = 0, y0 = 0, slot = 0, nsl = 0;
+      int kind = 3, x0 = 0, y0 = 0, slot = 0, nsl = 0, bxs = kD;
       long long pid = -1, be = 0;
       unsigned char org[12];
       float dxv[kPP], dyv[kPP];
@@ -655,9 +656,11 @@ corr_tc5_kernel(const __grid_constant__ CorrMaps maps, const CorrParams P) {
         if (bad) set_status(P.status, WV_STATUS_BAD_INDEX);
         int BX = kD;
         if (bad || outside) kind = 3;
+        else if (wdt <= kBoxTiny && hgt <= kBoxTiny) { kind = 0; BX = kBoxTiny; }
         else if (wdt <= kBoxSmall && hgt <= kBoxSmall) { kind = 0; BX = kBoxSmall; }
         else if (wdt <= kBoxLarge && hgt <= kBoxLarge) { kind = 1; BX = kBoxLarge; }
         else kind = 2;
+        bxs = BX;
         slot = bad ? 0 : b * P.n2 + (int)jx;
         if (kind <= 2) pid = (long long)b * P.n1 + ix;
 #pragma unroll
@@ -678,7 +681,7 @@ corr_tc5_kernel(const __grid_constant__ CorrMaps maps, const CorrParams P) {
       const int total = __shfl_sync(0xffffffffu, incl, kept - 1);
       for (int part = 0; part < nsl; part++) {
         T5Rec* r = reinterpret_cast<T5Rec*>(recs + ((myslot + part) % kT5Rec) * kT5RecBytes);
-        r->kind = kind; r->part = (short)part; r->nparts = (short)nsl; r->level = level; r->be = (int)be;
+        r->kind = kind; r->part = (short)part; r->nparts = (short)nsl; r->level = level | (bxs << 8); r->be = (int)be;
 #pragma unroll
         for (int p = 0; p < kPP; p++) { r->org[p] = org[p]; r->dx[p] = dxv[p]; r->dy[p] = dyv[p]; }
       }
@@ -691,11 +694,11 @@ corr_tc5_kernel(const __grid_constant__ CorrMaps maps, const CorrParams P) {
             const int sidx = myslot + part, stage = sidx % kT5Stages;
             mbar_wait(empty0 + 8 * stage, ((sidx / kT5Stages) & 1) ^ 1);
             const uint32_t bar = full0 + 8 * stage, dst = smem_u32(stages + (size_t)stage * kT5StageBytes);
-            const int npix = kind == 0 ? kBoxSmall * kBoxSmall : kBoxLarge * kBoxLargeRows;
+            const int npix = kind == 0 ? bxs * bxs : kBoxLarge * kBoxLargeRows;
             const uint32_t bytes = (kind <= 1 ? 2u * npix * 128u : 0u) + (kind <= 2 ? 2u * kT5PatchCopy : 0u);
             if (bytes) mbar_arrive_expect_tx(bar, bytes); else mbar_arrive(bar);
             if (kind <= 1) {
-              const CUtensorMap* map = &maps.m[2 * level + (kind == 0 ? 0 : 1)];
+              const CUtensorMap* map = &maps.m[3 * level + (kind == 1 ? 1 : (bxs == kBoxTiny ? 2 : 0))];
               const int yy = y0 + part * kBoxLargeRows;
               tma_load_4d(dst, map, bar, 0, x0, yy, slot);
               tma_load_4d(dst + kHalfBytes, map, bar, 64, x0, yy, slot);
@@ -745,15 +748,11 @@ corr_tc5_kernel(const __grid_constant__ CorrMaps maps, const CorrParams P) {
     // ================================================================= consumers: one warpgroup per pipeline
     const int q = warp & 3;                       // the TMEM lane quarter this warp may read
     const int wt = (role - 2) * 32 + lane;        // thread index in the warpgroup
-    // outputs of an edge: out[tap = x-tap b * 7 + y-tap a][p].  Thread wt < 126 owns patch pixel p = wt % 9 and the taps
-    // wt / 9 + 14 j (j = 0..3): its geometry is read once per edge, and for a fixed j the 126 threads write 126 consecutive halves.
-    const int o_p = wt % kPP, tap0 = wt / kPP;
-    int o_a[4], o_b[4];
-#pragma unroll
-    for (int j = 0; j < 4; j++) {
-      const int tap = min(tap0 + 14 * j, kT * kT - 1);
-      o_b[j] = tap / kT; o_a[j] = tap - kT * (tap / kT);
-    }
+    // outputs of an edge: out[x-tap b][y-tap a][p].  Thread wt < 126 owns patch pixel p, y-tap a and the x-taps 4 bh .. 4 bh + 3
+    // (bh = 1: three of them): it reads 2 rows x 5 adjacent columns of p's window once (10 loads for 4 outputs instead of 16), and
+    // for a fixed x-tap the 63 threads (a, p) write 63 consecutive outputs.  The kernel is bound by shared-memory bandwidth (TMA
+    // writes + UMMA operand reads + this epilogue), so loads saved here are time saved.
+    const int o_bh = wt / 63, o_r = wt - 63 * o_bh, o_a = o_r / kPP, o_p = o_r - kPP * o_a;
     int eidx = 0;
     __half keep[4];                               // two-level form: this thread's level-0 outputs of the edge in flight
 #pragma unroll
@@ -764,7 +763,7 @@ corr_tc5_kernel(const __grid_constant__ CorrMaps maps, const CorrParams P) {
       const T5Rec* rec = reinterpret_cast<const T5Rec*>(recs + (sidx % kT5Rec) * kT5RecBytes);
       const int kind = rec->kind;
       if (kind == 4) break;
-      const int part = rec->part, nparts = rec->nparts, level = NL == 1 ? 0 : rec->level;
+      const int part = rec->part, nparts = rec->nparts, lvbx = rec->level, level = NL == 1 ? 0 : (lvbx & 1), bxs = lvbx >> 8;
       const long long be = rec->be;
       float* rawD = raw0 + (eidx & 1) * (kT5RawBytes / 4);
       if (part == 0 && wt < kPP) {
@@ -781,7 +780,7 @@ corr_tc5_kernel(const __grid_constant__ CorrMaps maps, const CorrParams P) {
               "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
             : "r"(taddr));
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-        const int row = 32 * q + lane, npix = kind == 0 ? kBoxSmall * kBoxSmall : kBoxLarge * kBoxLargeRows;
+        const int row = 32 * q + lane, npix = kind == 0 ? bxs * bxs : kBoxLarge * kBoxLargeRows;
         if (row < npix) {
           float* d = rawD + part * (kBoxLarge * kBoxLargeRows) + row;
 #pragma unroll
@@ -820,22 +819,25 @@ corr_tc5_kernel(const __grid_constant__ CorrMaps maps, const CorrParams P) {
       asm volatile("bar.sync %0, 128;" ::"r"(1 + pl) : "memory");  // the edge's D scratch is complete
       if (kind == 2 && wt == 0) mbar_arrive(empty0 + 8 * stage);
       // ---- the 441 outputs of the edge: out[x-tap b][y-tap a][p], 4-tap bilinear from pixel p's own 8x8 window
-      const int BX = kind == 0 ? kBoxSmall : (kind == 1 ? kBoxLarge : kD);
+      const int BX = kind <= 1 ? bxs : kD;
       __half* o = P.out + be * (NL * kT * kT * kPP);
-      if (wt < 14 * kPP) {
+      if (wt < 2 * 63) {
         const float* row = rawD + o_p * kT5RawStride;
         const float dx = row[kMaxPix + 1], dy = row[kMaxPix + 2];
-        const float* r0 = row + __float_as_int(row[kMaxPix]);
+        const float* rr = row + __float_as_int(row[kMaxPix]) + o_a * BX + 4 * o_bh;
+        float t0[5], t1[5];
+#pragma unroll
+        for (int c = 0; c < 4; c++) { t0[c] = rr[c]; t1[c] = rr[BX + c]; }
+        if (o_bh == 0) { t0[4] = rr[4]; t1[4] = rr[BX + 4]; } else { t0[4] = 0.f; t1[4] = 0.f; }   // column 8 is outside the window
 #pragma unroll
         for (int j = 0; j < 4; j++) {
-          if (tap0 + 14 * j < kT * kT) {
-            const float* rr = r0 + o_a[j] * BX + o_b[j];
-            const float r00 = rr[0], r01 = rr[1], r10 = rr[BX], r11 = rr[BX + 1];
-            const float h0 = fmaf(dx, r01 - r00, r00), h1 = fmaf(dx, r11 - r10, r10);
+          if (j < 3 || o_bh == 0) {
+            const float h0 = fmaf(dx, t0[j + 1] - t0[j], t0[j]), h1 = fmaf(dx, t1[j + 1] - t1[j], t1[j]);
             const __half val = __float2half_rn(fmaf(dy, h1 - h0, h0));
-            if (NL == 1) o[wt + 14 * kPP * j] = val;
+            const int idx = (4 * o_bh + j) * 63 + o_r;
+            if (NL == 1) o[idx] = val;
             else if (level == 0) keep[j] = val;
-            else reinterpret_cast<__half2*>(o)[wt + 14 * kPP * j] = __halves2half2(keep[j], val);  // (level 0, level 1) pair
+            else reinterpret_cast<__half2*>(o)[idx] = __halves2half2(keep[j], val);  // (level 0, level 1) pair
           }
         }
       }
@@ -953,7 +955,8 @@ int corr_forward_tiled(const void* fmap1, const void* fmap2, const float* coords
       t5_attr_set = true;
     }
     CorrMaps maps;
-    maps.m[0] = ms; maps.m[1] = mh; maps.m[2] = ms; maps.m[3] = mh;
+    if (!make_map(&maps.m[2], nhwc, W2, H2, slots, kBoxTiny, kBoxTiny)) return WV_EUNSUPPORTED;
+    maps.m[0] = ms; maps.m[1] = mh; maps.m[3] = ms; maps.m[4] = mh; maps.m[5] = maps.m[2];
     const long long want5 = (BE + 7) / 8;
     corr_tc5_kernel<1><<<(int)(want5 < sm_count() ? want5 : sm_count()), kT5Threads, kT5Smem, st>>>(maps, P);
     WV_LAUNCH_CHECK();
@@ -1002,7 +1005,9 @@ int corr_forward_stacked(const void* fmap1, const void* fmap2_l0, const void* fm
   __half* gT = reinterpret_cast<__half*>(reinterpret_cast<char*>(nhwc1) + al1k((size_t)slots * H1 * W1 * kC * 2));
   CorrMaps maps;
   if (!make_map(&maps.m[0], nhwc0, W0, H0, slots, kBoxSmall, kBoxSmall) || !make_map(&maps.m[1], nhwc0, W0, H0, slots, kBoxLarge, kBoxLargeRows) ||
-      !make_map(&maps.m[2], nhwc1, W1, H1, slots, kBoxSmall, kBoxSmall) || !make_map(&maps.m[3], nhwc1, W1, H1, slots, kBoxLarge, kBoxLargeRows))
+      !make_map(&maps.m[2], nhwc0, W0, H0, slots, kBoxTiny, kBoxTiny) ||
+      !make_map(&maps.m[3], nhwc1, W1, H1, slots, kBoxSmall, kBoxSmall) || !make_map(&maps.m[4], nhwc1, W1, H1, slots, kBoxLarge, kBoxLargeRows) ||
+      !make_map(&maps.m[5], nhwc1, W1, H1, slots, kBoxTiny, kBoxTiny))
     return WV_EUNSUPPORTED;
 
   // pass 1: level 0 together with the patches, then level 1
