@@ -17,6 +17,7 @@
 // Summation order is a pure function of the edge list, so results are bitwise reproducible run to run
 // (the reference's atomics are not).  fp32 throughout, like the reference.
 #include <cooperative_groups.h>
+#include <stdlib.h>
 
 #include <algorithm>
 
@@ -502,7 +503,9 @@ int ba_forward_window(float* poses, float* patches, const float* intr, const flo
   if (smem > 48 * 1024)
     WV_CUDA_TRY(cudaFuncSetAttribute(ba_window_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   void* args[] = {&a};
-  WV_CUDA_TRY(cudaLaunchCooperativeKernel((const void*)ba_window_kernel, dim3(G), dim3(kBaThreads), args, smem, st));
+  int Gb = G;   // CTAs of the BA kernel itself (<= the plan's grid: the partial-sum array is sized for G)
+  if (const char* e = getenv("WVB200_BA_GRID")) { const int v = atoi(e); if (v > 0 && v < G) Gb = v; }
+  WV_CUDA_TRY(cudaLaunchCooperativeKernel((const void*)ba_window_kernel, dim3(Gb), dim3(kBaThreads), args, smem, st));
   return WV_OK;
 }
 
