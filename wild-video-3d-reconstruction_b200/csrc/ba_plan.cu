@@ -51,6 +51,10 @@ struct PlanArgs {
   int64_t goff;
   int64_t* rank_out;
   int* mp_out;
+  // small id spaces (n_groups <= 65 536: the tracker's patch buffer): the host memset that clears the header also clears cnt /
+  // cursor for ALL ids, the window is the whole id space, and validation rides along with the count: phases A and B and their
+  // two grid syncs disappear
+  int small;
 };
 
 __device__ __forceinline__ int64_t gkey(const PlanArgs& a, int64_t e) { return a.g[e] - a.goff; }
@@ -87,6 +91,7 @@ __device__ void plan_phase_minmax(const PlanArgs& a) {
 }
 
 __device__ __forceinline__ void plan_window(const PlanArgs& a, int& gmin, int& range) {
+  if (a.small) { gmin = 0; range = (int)a.p.n_groups; return; }
   const int mxp1 = a.p.hdr->gmax_p1;
   gmin = (int)a.p.n_groups - a.p.hdr->gmin_neg;
   range = mxp1 > 0 ? mxp1 - gmin : 0;
@@ -103,8 +108,14 @@ __device__ void plan_phase_zero(const PlanArgs& a) {
 // C: count
 __device__ void plan_phase_count(const PlanArgs& a) {
   int gmin, range; plan_window(a, gmin, range);
-  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < a.p.E; e += (int64_t)gridDim.x * blockDim.x)
+  int bad = 0;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < a.p.E; e += (int64_t)gridDim.x * blockDim.x) {
     if (edge_valid(a, e)) atomicAdd(&a.p.cnt[(int)gkey(a, e) - gmin], 1);
+    else bad = 1;
+  }
+  if (a.small && __any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) {   // (otherwise phase A reported it)
+    atomicOr(&a.p.hdr->bad, 1); set_status(a.status, WV_STATUS_BAD_INDEX);
+  }
 }
 
 // block-wide exclusive scan of (v0, v1); returns totals through t0/t1.  blockDim.x == kPlanThreads.
@@ -236,10 +247,12 @@ __device__ void plan_phase_order(const PlanArgs& a) {
 __global__ void __launch_bounds__(kPlanThreads) plan_coop_kernel(PlanArgs a) {
   extern __shared__ int sh[];
   cg::grid_group grid = cg::this_grid();
-  plan_phase_minmax(a);
-  grid.sync();
-  plan_phase_zero(a);
-  grid.sync();
+  if (!a.small) {
+    plan_phase_minmax(a);
+    grid.sync();
+    plan_phase_zero(a);
+    grid.sync();
+  }
   plan_phase_count(a);
   grid.sync();
   plan_phase_scan(a, sh);
@@ -270,8 +283,14 @@ int plan_build(const Plan& p, const int64_t* g, const int64_t* jj, const int64_t
 
 int plan_build_groups(const Plan& p, const int64_t* g, int64_t goff, const int64_t* jj, const int64_t* ii, int64_t n_poses,
                       int64_t* ix, int64_t* jx, int64_t* rank_out, int* mp_out, int* status, cudaStream_t st) {
-  PlanArgs a{p, g, jj, ii, n_poses, ix, jx, status, goff, rank_out, mp_out};
-  WV_CUDA_TRY(cudaMemsetAsync(p.hdr, 0, sizeof(PlanHeader), st));
+  PlanArgs a{p, g, jj, ii, n_poses, ix, jx, status, goff, rank_out, mp_out, 0};
+  // hdr, cnt and cursor are adjacent in the workspace (plan_carve): one memset clears all three for a small id space
+  const char* nosmall = getenv("WVB200_PLAN_WINDOWED");
+  a.small = (p.n_groups <= 65536 && !(nosmall && nosmall[0] == '1') &&
+             reinterpret_cast<char*>(p.cursor) + sizeof(int) * (size_t)p.n_groups <= reinterpret_cast<char*>(p.loc_off)) ? 1 : 0;
+  const size_t clear = a.small ? (size_t)(reinterpret_cast<char*>(p.cursor) - reinterpret_cast<char*>(p.hdr)) + sizeof(int) * (size_t)p.n_groups
+                               : sizeof(PlanHeader);
+  WV_CUDA_TRY(cudaMemsetAsync(p.hdr, 0, clear, st));
   const int grid = plan_grid();
   const size_t sh = sizeof(int) * (size_t)(2 * (grid + 1) + 72);
   if (use_cooperative()) {
@@ -280,8 +299,10 @@ int plan_build_groups(const Plan& p, const int64_t* g, int64_t goff, const int64
     if (e == cudaSuccess) return WV_OK;
     (void)cudaGetLastError();  // fall through to the multi-launch form
   }
-  plan_k_minmax<<<grid, kPlanThreads, 0, st>>>(a);
-  plan_k_zero<<<grid, kPlanThreads, 0, st>>>(a);
+  if (!a.small) {
+    plan_k_minmax<<<grid, kPlanThreads, 0, st>>>(a);
+    plan_k_zero<<<grid, kPlanThreads, 0, st>>>(a);
+  }
   plan_k_count<<<grid, kPlanThreads, 0, st>>>(a);
   plan_k_scan<<<grid, kPlanThreads, sh, st>>>(a);
   plan_k_fill<<<grid, kPlanThreads, sh, st>>>(a);
