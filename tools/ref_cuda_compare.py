@@ -15,8 +15,15 @@ assert rc is not None and rb is not None, "oracle/_ref/refgpu_*.so missing: run 
 pkg = importlib.import_module(bench.PKG)
 cc, cb = pkg.native_modules()
 altcorr = pkg.altcorr
-w, s = bench.make_inputs(0)
+M = int(sys.argv[1]) if len(sys.argv) > 1 else 96      # 96: bench.py's configs[1] step; 384: dpvo_configs/default.yaml (configs[2])
+if M == 96:
+    w, s = bench.make_inputs(0)
+else:
+    w = pkg.synthetic.make_corr_workload(seed=1, M=M)
+    s = pkg.synthetic.make_ba_scene(seed=2, n=40, M=M, edges="tracker")
 E = w["E"]
+assert E == len(s["kk"])
+print(f"M = {M} patches per frame, E = {E} edges")
 dev = torch.device("cuda")
 H = lambda a, dt=None: (torch.from_numpy(np.ascontiguousarray(a)).to(dt) if dt else torch.from_numpy(np.ascontiguousarray(a))).to(dev)  # noqa: E731
 D = dict(gmap=H(w["gmap"], torch.half), f0=H(w["fmap0"], torch.half), f1=H(w["fmap1"], torch.half), c0=H(w["coords"]), ii1=H(w["ii1"]),
