@@ -7,9 +7,11 @@
 // The reference runs a device sort + host sync (unique), then scatter_max, gather, sub, exp, scatter_sum, gather, div, mul and a
 // second scatter_sum: ten passes over [E][384] tensors and two atomics-based scatters (torch-scatter 2.1.2, composite/softmax.py).
 // Here:
-//   group plan   the inverse index without a sort: presence bitmap over the key range -> popcount prefix -> jx = rank of the key
-//                among the present keys (== torch.unique's sorted order), then member lists per group in ascending edge order
-//                (counting fill + a per-group rank sort), so that the reduction order is fixed: results are deterministic.
+//   group plan   the inverse index without a sort.  Key ranges up to 2^22 (the tracker's kk and ii*12345+jj) go through the
+//                counting-sort edge plan shared with the BA (ba_plan.cu, one cooperative launch) with the key itself as the
+//                secondary sort key: dense rank of a key among the present keys == torch.unique's sorted order == jx, segments ==
+//                member lists in ascending edge order.  Wider ranges: presence bitmap -> popcount prefix -> rank, then counting
+//                fill + a per-group rank sort (the kernels right below).  Either way the reduction order is fixed: deterministic.
 //   soft_agg     ONE pass over f(x) and g(x): a CTA per group, a thread owns 16 bytes of channels and a share of the group's members
 //                and walks them once in chunks of four (online softmax: running max, rescaled sums), fp32 arithmetic, one rounding
 //                at the end.

@@ -20,6 +20,9 @@
 //             4 consumer warps  tcgen05.ld of their TMEM lane quarter, the 9 real columns scattered to a per-edge fp32
 //                             scratch, then the 4-corner bilinear blend of every patch pixel's own 8x8 sub-window and
 //                             the permuted [x-tap][y-tap][3][3] fp16 store (correlation_kernel.cu:221-232), fused.
+//           Tiles are 9x9 px when the window fits (always at the coarse level), else 10x10, else 12x12 in two halves.
+//           corr_tc5_kernel<2> is the two-level form (DPVO.corr, dpvo/dpvo.py:325-333): level 0 and level 1 of an edge go through
+//           the pipeline back to back and the (level 0, level 1) pairs are stored once in the torch.stack layout.
 //           corr_tiled_kernel (WVB200_CORR_TC5=0) is the earlier form of pass 2 with the contraction on mma.sync m16n8k16
 //           inside 8 consumer warps; it is kept as a cross-check of the tcgen05 path (tests run both).
 //
