@@ -433,6 +433,12 @@ def test_corr_stacked_composed_form_and_bad_index(golden):
     assert (comp - fused.float()).abs().max() < 2e-2
     empty = altcorr.corr_stacked(g.half(), (f0.half(), f1.half()), co[:, :0], ii[:0], jj[:0], 3)
     assert empty.shape == (1, 0, 882)
+    # non-finite and far-out-of-map coordinates: zeros for that edge like the two-call form, the other edges untouched
+    cb = co.clone(); cb[0, 1] = float("inf"); cb[0, 2, 0] = 1e9
+    with _tiled(True):
+        two = torch.stack([cc.forward(g.half(), f0.half(), cb / 1, ii, jj, 3)[0], cc.forward(g.half(), f1.half(), cb / 4, ii, jj, 3)[0]], -1).view(1, 3, -1)
+    st = altcorr.corr_stacked(g.half(), (f0.half(), f1.half()), cb, ii, jj, 3)
+    assert torch.isfinite(st[0, 0]).all() and torch.equal(st[0, 0], fused[0, 0]) and torch.equal(torch.nan_to_num(st), torch.nan_to_num(two))
     os.environ["WVB200_CHECK_INDICES"] = "1"
     try:
         with pytest.raises(IndexError):
