@@ -92,10 +92,10 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   do {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"   // %3: suspend-time hint (ns): fewer polls compete for issue slots
         "selp.u32 %0, 1, 0, p;\n\t}"
         : "=r"(ok)
-        : "r"(bar), "r"(parity)
+        : "r"(bar), "r"(parity), "r"(4000u)
         : "memory");
     // watchdog: a protocol bug must surface as a CUDA error in seconds, not as a hung GPU (4e9 cycles ~ 2 s)
     if (!ok && (++spins & 0x3ff) == 0) {
