@@ -37,7 +37,7 @@ CORR_BYTES_L0 = 2 * 128 * 9 + 2 * 128 * 100 + 72 + 16 + 2 * 49 * 9   # 28 874
 CORR_BYTES_L1 = 2 * 128 * 9 + 2 * 128 * 81 + 72 + 16 + 2 * 49 * 9    # 24 010
 # dram__bytes_read.sum + dram__bytes_write.sum of one DPVO.corr call = restage_kernel x2 + corr_tc5_kernel<2>, ncu --set full
 # (profiles/r1_stacked_ncu_summary.txt)
-NCU_TRAFFIC_CORR = 630.7e6
+NCU_TRAFFIC_CORR = 643.0e6
 WORKLOAD = ("configs[1]: 512x384 -> fmaps 96x128 + 24x32, C=128 fp16, pmem=36, M=96, tracker edge list E=45312, "
             "radius 3; one update(): DPVO.corr (both levels, stacked [1,E,882]) + neighbors + BA(10 free poses, 2 GN iterations)")
 
