@@ -418,8 +418,8 @@ def run_b200(args):
             "e2e": {"value": world * K / te, "unit": "frames/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "api": "hostapi.Session.update -> wv_session_update_host (C ABI, pinned host buffers, 3 streams)"},
             "per_rank": {"columns": ["corr_ms", "-", "neighbors_ms", "ba_ms", "sm_mhz", "n_throttle_reasons"], "rows": per_rank},
-            "gpu_launches": 5 * K,
-            "gpu_launches_per_step": "corr: restage x2 levels + ONE two-level tcgen05 tile kernel; plan kernel (neighbors; its plan is reused by BA); window kernel (BA) -- profiles/r1_launches_stacked.csv",
+            "gpu_launches": 6 * K,
+            "gpu_launches_per_step": "corr: restage x2 levels + ONE two-level tcgen05 tile kernel; plan kernel (neighbors; its plan is reused by BA); window kernel (BA) + the one-thread kernel that mirrors BA's status word to mapped host memory -- profiles/r1_launches_stacked.csv",
             "clocks": clocks,
         }
         if world == 1 and not args.no_cpu:

@@ -103,26 +103,44 @@ int wv_words_read(const int* words, int n, int* values, wv_stream_t stream) {
   return word_read(const_cast<int*>(words), n, values, stream, false);
 }
 
+// The words travel through a host-MAPPED buffer written by a one-thread kernel that follows the caller's work on the stream, and
+// the host spins on a sequence number in that buffer: the result is visible ~4 us after the preceding kernel ends (launch + one
+// PCIe write), against ~23 us for cudaMemcpyAsync + event record + event polling (measured on the BA call of bench.py).
+__global__ void mirror_words_kernel(const int* __restrict__ src, int n, volatile int* dst, int seq) {
+  for (int i = 0; i < n; i++) dst[i] = src[i];
+  __threadfence_system();
+  dst[16] = seq;
+}
+
 static int word_read(int* status, int n, int* value, wv_stream_t stream, bool clear) {
   if (!status || !value || n < 1 || n > 16) return WV_EINVAL;
-  // one pinned word + one event per device, created on first use (callers hold the GIL / serialise per device)
-  struct Chan { int* host = nullptr; cudaEvent_t ev = nullptr; };
+  // one mapped buffer per device, created on first use (callers hold the GIL / serialise per device)
+  struct Chan { volatile int* host = nullptr; int* devp = nullptr; int seq = 0; };
   static Chan chans[64];
   int dev = 0;
   WV_CUDA_TRY(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64) return WV_EUNSUPPORTED;
   Chan& c = chans[dev];
   if (!c.host) {
-    WV_CUDA_TRY(cudaHostAlloc(reinterpret_cast<void**>(&c.host), 16 * sizeof(int), cudaHostAllocDefault));
-    WV_CUDA_TRY(cudaEventCreateWithFlags(&c.ev, cudaEventDisableTiming));
+    int* h = nullptr;
+    WV_CUDA_TRY(cudaHostAlloc(reinterpret_cast<void**>(&h), 32 * sizeof(int), cudaHostAllocMapped));
+    for (int i = 0; i < 32; i++) h[i] = 0;
+    WV_CUDA_TRY(cudaHostGetDevicePointer(reinterpret_cast<void**>(&c.devp), h, 0));
+    c.host = h;
   }
   cudaStream_t st = as_stream(stream);
-  WV_CUDA_TRY(cudaMemcpyAsync(c.host, status, n * sizeof(int), cudaMemcpyDeviceToHost, st));
-  WV_CUDA_TRY(cudaEventRecord(c.ev, st));
-  cudaError_t q = cudaErrorNotReady;
-  for (int spin = 0; spin < 200000 && q == cudaErrorNotReady; spin++) q = cudaEventQuery(c.ev);  // ~ a few hundred us at most
-  if (q == cudaErrorNotReady) q = cudaEventSynchronize(c.ev);
-  WV_CUDA_TRY(q);
+  const int seq = ++c.seq == 0 ? ++c.seq : c.seq;  // never 0 (the buffer's initial value)
+  mirror_words_kernel<<<1, 1, 0, st>>>(status, n, c.devp, seq);
+  WV_LAUNCH_CHECK();
+  bool seen = false;
+  for (long spin = 0; spin < 4000000L; spin++) {        // ~10 ms of polling at most, then a blocking wait (which also surfaces a
+    if (c.host[16] == seq) { seen = true; break; }       // device fault of the preceding kernels)
+    if ((spin & 0xffff) == 0xffff && cudaStreamQuery(st) != cudaErrorNotReady) break;
+  }
+  if (!seen) {
+    WV_CUDA_TRY(cudaStreamSynchronize(st));
+    if (c.host[16] != seq) return cuda_fail(cudaErrorUnknown);
+  }
   for (int i = 0; i < n; i++) value[i] = c.host[i];
   if (clear && *value != 0) WV_CUDA_TRY(cudaMemsetAsync(status, 0, sizeof(int), st));
   return WV_OK;
