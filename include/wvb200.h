@@ -5,6 +5,8 @@
  *
  *   cuda_corr.forward / backward / patchify_forward / patchify_backward   dpvo/altcorr/correlation.cpp:57-63
  *   cuda_ba.forward / neighbors / reproject / solve_system                dpvo/fastba/ba.cpp:236-241
+ *   lietorch_backends.{expm, logm, inv, mul, adj, adjT, act, act4}[_backward], as_matrix, projector, Jinv
+ *                                                                          dpvo/lietorch/src/lietorch.cpp:286-316
  *
  * Conventions
  *   - plain pointers and sizes only; no torch types.  Unless a function says "host", every pointer is a
@@ -29,7 +31,7 @@ extern "C" {
 
 typedef struct CUstream_st* wv_stream_t; /* == cudaStream_t */
 
-enum { WV_F16 = 0, WV_F32 = 1 };
+enum { WV_F16 = 0, WV_F32 = 1, WV_F64 = 2 /* lietorch only */ };
 
 enum {
   WV_OK = 0,
@@ -306,6 +308,38 @@ typedef struct {
 wv_session* wv_session_create(void);              /* on the current device; NULL on failure */
 void wv_session_destroy(wv_session* s);
 int wv_session_update_host(wv_session* s, wv_update_args* a);
+
+/* ---------------------------------------------------------------------------------------------
+ * lietorch_backends -- the third module the tracker's host code imports by name (dpvo/lietorch/group_ops.py:1)
+ * ------------------------------------------------------------------------------------------- */
+
+/* group ids are the reference's (dpvo/lietorch/groups.py:236, 252, 268, 290) */
+enum { WV_LIE_SO3 = 1, WV_LIE_RXSO3 = 2, WV_LIE_SE3 = 3, WV_LIE_SIM3 = 4 };
+/* one id per m.def pair of dpvo/lietorch/src/lietorch.cpp:286-316 */
+enum {
+  WV_LIE_EXP = 0,       /* expm:  a [n][K]            -> X [n][N]                       lietorch_gpu.cu:20-43    */
+  WV_LIE_LOG = 1,       /* logm:  X [n][N]            -> a [n][K]                                    :45-70    */
+  WV_LIE_INV = 2,       /* inv:   X                   -> X^-1                                        :72-98    */
+  WV_LIE_MUL = 3,       /* mul:   X, Y                -> X Y                                         :101-127  */
+  WV_LIE_ADJ = 4,       /* adj:   X, a [n][K]         -> Adj(X) a                                    :129-158  */
+  WV_LIE_ADJT = 5,      /* adjT:  X, a                -> Adj(X)^T a                                  :161-189  */
+  WV_LIE_ACT = 6,       /* act:   X, p [n][3]         -> X p                                         :191-222  */
+  WV_LIE_ACT4 = 7,      /* act4:  X, p [n][4]         -> X p (homogeneous)                           :225-257  */
+  WV_LIE_MATRIX = 8,    /* as_matrix: X               -> [n][4][4] row-major                         :259-270  */
+  WV_LIE_PROJECTOR = 9, /* projector: X               -> [n][N][N] row-major                         :272-281  */
+  WV_LIE_JINV = 10      /* Jinv:  X, a                -> J_l^-1(Log X) a                             :283-294  */
+};
+/* Embedding N / tangent K per group: SO3 4/3, RxSO3 5/4, SE3 7/6, Sim3 8/7; storage (tx ty tz) (qx qy qz qw) (s).
+ * dtype WV_F32 or WV_F64.  x_stride / y_stride: distance in SCALARS between consecutive batch items of the first / second
+ * operand -- the dense value (N, K, 3 or 4) or 0 to broadcast one element over the batch (the reference materialises that with
+ * repeat(), dpvo/lietorch/broadcasting.py:26-29).  on_host != 0: the pointers are HOST pointers and the call computes
+ * synchronously on the calling thread (the reference's lietorch_cpu.cpp; same arithmetic, `stream` ignored).
+ * wv_lie_backward follows the reference's gradient convention (row vectors over the first K entries of an N-wide row,
+ * lietorch_gpu.cu:33-43); it writes dX [n][N] ([n][K] for expm) and, for binary ops, dY shaped like Y, all dense. */
+int wv_lie_forward(int op, int group, int dtype, const void* X, int64_t x_stride, const void* Y, int64_t y_stride, void* out,
+                   int64_t n, int on_host, wv_stream_t stream);
+int wv_lie_backward(int op, int group, int dtype, const void* grad, const void* X, int64_t x_stride, const void* Y,
+                    int64_t y_stride, void* dX, void* dY, int64_t n, int on_host, wv_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -5,6 +5,7 @@ Compiles, from where they lie under /root/reference (never copied into the repo)
 
   refgpu_cuda_corr   dpvo/altcorr/correlation.cpp + correlation_kernel.cu
   refgpu_cuda_ba     dpvo/fastba/ba.cpp + ba_cuda.cu            (Eigen: thirdparty/eigen)
+  refgpu_lietorch_backends   dpvo/lietorch/src/{lietorch.cpp, lietorch_cpu.cpp, lietorch_gpu.cu}   (Eigen: thirdparty/eigen)
 
 into oracle/_ref/*.so (git-ignored; they travel to the GPU box with the snapshot).  The only additions are the two
 source-compatibility shims of oracle/ref_shim/cuda_gpu_compat.h (pre-included); no line of the reference is edited.  The
@@ -62,6 +63,10 @@ def build(force=False):
     os.makedirs(OUT, exist_ok=True)
     _build("refgpu_cuda_corr", [f"{REF}/dpvo/altcorr/correlation_kernel.cu", f"{REF}/dpvo/altcorr/correlation.cpp"], [], force)
     _build("refgpu_cuda_ba", [f"{REF}/dpvo/fastba/ba_cuda.cu", f"{REF}/dpvo/fastba/ba.cpp"], [f"{REF}/thirdparty/eigen"], force)
+    # lietorch_backends (dpvo/lietorch/group_ops.py:1 imports it by name; the tracker's reprojection runs on it)
+    lt = f"{REF}/dpvo/lietorch"
+    _build("refgpu_lietorch_backends", [f"{lt}/src/lietorch_gpu.cu", f"{lt}/src/lietorch_cpu.cpp", f"{lt}/src/lietorch.cpp"],
+           [f"{lt}/include", f"{REF}/thirdparty/eigen"], force)
     return True
 
 

@@ -4,6 +4,7 @@
   cuda_corr.*.so      g++, torch extension with the reference's module name / m.def table (correlation.cpp:57-63)
   cuda_ba.*.so        g++, torch extension with the reference's module name / m.def table (ba.cpp:236-241)
   cuda_agg.*.so       g++, torch extension for the update operator's SoftAgg (the reference uses torch_scatter there, blocks.py:41-43)
+  lietorch_backends.*.so   g++, torch extension with the reference's module name / m.def table (lietorch.cpp:286-316)
 
 python build.py [--force] [--verbose]
 """
@@ -19,7 +20,7 @@ CUDA_HOME = os.environ.get("CUDA_HOME", "/usr/local/cuda")
 NVCC = os.path.join(CUDA_HOME, "bin", "nvcc")
 HOST_CXX = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
 
-CU_SOURCES = ["abi.cu", "host_entry.cu", "corr_generic.cu", "corr_sm100.cu", "ba_plan.cu", "ba_window.cu", "ba_global.cu", "pops.cu", "agg.cu", "colmap_text.cu"]
+CU_SOURCES = ["abi.cu", "host_entry.cu", "corr_generic.cu", "corr_sm100.cu", "ba_plan.cu", "ba_window.cu", "ba_global.cu", "pops.cu", "agg.cu", "colmap_text.cu", "lie_ops.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",
               "-ccbin", HOST_CXX, "--expt-relaxed-constexpr"]
 EXT_SUFFIX = sysconfig.get_config_var("EXT_SUFFIX")
@@ -77,7 +78,7 @@ def build_ext(name, force=False, verbose=False):
 
 def build_all(force=False, verbose=False):
     lib = build_lib(force, verbose)
-    exts = [build_ext(n, force, verbose) for n in ("cuda_corr", "cuda_ba", "cuda_agg")]
+    exts = [build_ext(n, force, verbose) for n in ("cuda_corr", "cuda_ba", "cuda_agg", "lietorch_backends")]
     return [lib] + exts
 
 
