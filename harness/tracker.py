@@ -152,12 +152,65 @@ class TeacherNet(torch.nn.Module):
         return net, (delta, wgt, None)
 
 
+class PhaseTimer:
+    """per-phase wall time of the tracker with a device synchronisation on both sides of every phase (attribution, not throughput:
+    the synchronisations remove the CPU/GPU overlap, so the phases sum to more than an un-instrumented frame).  Wraps attributes
+    the unchanged host code looks up at call time; nothing on disk changes."""
+    PHASES = ("patchify_net", "reproject", "corr", "update_operator", "teacher_gt", "ba", "point_cloud", "keyframe", "motion_probe")
+
+    def __init__(self):
+        self.t = {k: 0.0 for k in self.PHASES}
+        self.n = {k: 0 for k in self.PHASES}
+        self.stack = []
+
+    def wrap(self, name, fn):
+        def timed(*a, **k):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            self.stack.append(0.0)
+            try:
+                return fn(*a, **k)
+            finally:
+                torch.cuda.synchronize()
+                dt = time.perf_counter() - t0
+                inner = self.stack.pop()
+                self.t[name] += dt - inner          # exclusive time: nested phases are charged to themselves
+                self.n[name] += 1
+                if self.stack:
+                    self.stack[-1] += dt
+        return timed
+
+    def install(self, slam, net):
+        import dpvo.fastba as F
+        import dpvo.projective_ops as P
+        net.base.patchify.forward = self.wrap("patchify_net", net.base.patchify.forward)
+        net.base.update.forward = self.wrap("update_operator", net.base.update.forward)
+        net.update = self.wrap("teacher_gt", net.update)
+        slam.reproject = self.wrap("reproject", slam.reproject)
+        slam.corr = self.wrap("corr", slam.corr)
+        slam.keyframe = self.wrap("keyframe", slam.keyframe)
+        slam.motion_probe = self.wrap("motion_probe", slam.motion_probe)
+        self._F, self._P, self._old = F, P, (F.BA, P.point_cloud)
+        F.BA = self.wrap("ba", F.BA)
+        P.point_cloud = self.wrap("point_cloud", P.point_cloud)
+
+    def uninstall(self):
+        self._F.BA, self._P.point_cloud = self._old
+
+    def report(self, frames, total_s):
+        out = {k: round(1e3 * v / max(frames, 1), 4) for k, v in self.t.items()}
+        out["other_host_code"] = round(1e3 * (total_s - sum(self.t.values())) / max(frames, 1), 4)
+        out["total"] = round(1e3 * total_s / max(frames, 1), 4)
+        out["calls_per_frame"] = {k: round(v / max(frames, 1), 3) for k, v in self.n.items()}
+        return out
+
+
 def crc(t):
     return zlib.crc32(t.detach().cpu().numpy().tobytes())
 
 
 def run_clip(world, backend="b200", n_frames=None, cfg=None, use_depth=True, use_mask=True, log=False, frames_on_host=False,
-             seed=1234, noise_px=0.25, final_updates=12, hooks=None, pre_rendered=None):
+             seed=1234, noise_px=0.25, final_updates=12, hooks=None, pre_rendered=None, breakdown=False):
     """the loop of dpvo_demo.py:62-141 on the synthetic clip.  Returns a dict with the trajectory (terminate()), per-frame log
     (log=True: n, m, E and CRCs of ii/jj/kk after every frame -- one D2H sync per frame, off for timing), timings, ATE."""
     T = load_tracker(backend)
@@ -188,6 +241,9 @@ def run_clip(world, backend="b200", n_frames=None, cfg=None, use_depth=True, use
                 net.bind(slam)
                 if hooks:
                     hooks(slam)
+                if breakdown:
+                    phases = PhaseTimer()
+                    phases.install(slam, net)
             net.frame = t
             slam(t, image, depth if use_depth else None, mask if use_mask else None, K)
             if frames_on_host:   # the per-frame result a caller reads: the newest pose
@@ -202,11 +258,15 @@ def run_clip(world, backend="b200", n_frames=None, cfg=None, use_depth=True, use
         torch.cuda.synchronize()
         t_track = time.perf_counter() - t_start
         n_kf, E_final = int(slam.n), int(slam.pg.ii.numel())
+        ms_breakdown = None
+        if breakdown:
+            phases.uninstall()
+            ms_breakdown = phases.report(n_frames, t_track)
         poses, tstamps = slam.terminate()
     est = np.asarray(poses)[:, :3]
     gt = world.gt_cam_positions()[:len(est)]
     return dict(poses=np.asarray(poses), tstamps=np.asarray(tstamps), frame_log=frame_log, seconds=t_track, frames=n_frames,
-                fps=n_frames / t_track, device_ms=ev0.elapsed_time(ev1), ate=ate_rmse_safe(est, gt), keyframes=n_kf, edges=E_final,
+                ms_breakdown=ms_breakdown, fps=n_frames / t_track, device_ms=ev0.elapsed_time(ev1), ate=ate_rmse_safe(est, gt), keyframes=n_kf, edges=E_final,
                 h2d_bytes_per_frame=h2d / max(n_frames, 1), d2h_bytes_per_frame=d2h / max(n_frames, 1), slam=slam, net=net)
 
 
@@ -215,3 +275,80 @@ def ate_rmse_safe(est, gt):
     if len(est) < 3 or not np.isfinite(est).all():
         return float("nan")
     return ate_rmse(est, gt)
+
+
+def run_clip_windows(world, backend, warmup, steps, breakdown_frames=0, cfg=None, frames=None, frames_on_host=False, seed=1234,
+                     noise_px=0.25, barrier=None, sampler=None, net=None):
+    """bench form of run_clip: ONE tracker instance fed `warmup` untimed frames (they cover the tracker's initialisation: 10 frames
+    + 12 updates, dpvo/dpvo.py:858-863), then exactly `steps` timed frames bracketed by barrier() + torch.cuda.synchronize() and a
+    pair of CUDA events, then `breakdown_frames` more frames under the PhaseTimer.  frames_on_host: every frame starts in pinned host
+    memory and is uploaded inside the timed region (dpvo_demo.py:55-60), and the newest pose is read back after every frame.
+    -> dict(timed_ms, wall_s, h2d/d2h bytes per frame, ms_breakdown, ate, keyframes, edges, launches_per_frame)"""
+    T = load_tracker(backend)
+    DPVO = T["dpvo"].DPVO
+    cfg = cfg if cfg is not None else make_cfg()
+    dev = torch.device("cuda")
+    total = warmup + steps + breakdown_frames
+    assert total <= world.n_frames
+    torch.manual_seed(seed); torch.cuda.manual_seed_all(seed); np.random.seed(seed)
+    if net is None:
+        net = TeacherNet(world, seed=seed, noise_px=noise_px, patches_per_frame=cfg.PATCHES_PER_FRAME)
+    frames = frames if frames is not None else [world.frame(t) for t in range(total)]
+    if frames_on_host:
+        frames = [(t, im.cpu().pin_memory(), dp.cpu().pin_memory(), mk.cpu().pin_memory(), K.cpu().pin_memory()) for (t, im, dp, mk, K) in frames[:total]]
+    sync = barrier if barrier is not None else torch.cuda.synchronize
+    pose_host = torch.empty(7, dtype=torch.float32).pin_memory()
+    slam, phases = None, None
+    h2d = d2h = 0
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    wall = 0.0
+    with torch.no_grad():
+        for (t, image, depth, mask, K) in frames[:total]:
+            if t == warmup:
+                sync()
+                if sampler is not None:
+                    sampler.start()
+                wall = time.perf_counter()
+                ev0.record()
+            if t == warmup + steps:
+                ev1.record()
+                sync()
+                wall = time.perf_counter() - wall
+                if sampler is not None:
+                    sampler.stop()
+                if breakdown_frames:
+                    phases = PhaseTimer()
+                    phases.install(slam, net)
+                    t_bd = time.perf_counter()
+            if frames_on_host:
+                if warmup <= t < warmup + steps:
+                    h2d += image.numel() + depth.numel() * 4 + mask.numel() + K.numel() * 8
+                image, depth, mask, K = (x.to(dev, non_blocking=True) for x in (image, depth, mask, K))
+            if slam is None:
+                slam = DPVO(cfg, net, ht=image.shape[1], wd=image.shape[2], viz=False)
+                net.bind(slam)
+            net.frame = t
+            slam(t, image, depth, mask, K)
+            if frames_on_host:
+                pose_host.copy_(slam.pg.poses_[max(slam.n - 1, 0)], non_blocking=False)   # blocks until the frame's BA is done
+                if warmup <= t < warmup + steps:
+                    d2h += 28
+        if breakdown_frames == 0:
+            ev1.record()
+            sync()
+            wall = time.perf_counter() - wall
+            if sampler is not None:
+                sampler.stop()
+        torch.cuda.synchronize()
+        ms_breakdown = None
+        if phases is not None:
+            phases.uninstall()
+            ms_breakdown = phases.report(breakdown_frames, time.perf_counter() - t_bd)
+        n_kf, E_final = int(slam.n), int(slam.pg.ii.numel())
+        for _ in range(12):
+            slam.update()
+        poses, _ = slam.terminate()
+    est = np.asarray(poses)[:, :3]
+    return dict(timed_ms=ev0.elapsed_time(ev1), wall_s=wall, h2d_bytes_per_frame=h2d / max(steps, 1), d2h_bytes_per_frame=d2h / max(steps, 1),
+                ms_breakdown=ms_breakdown, ate=ate_rmse_safe(est, world.gt_cam_positions()[:len(est)]), keyframes=n_kf, edges=E_final,
+                frames_total=total, net=net)

@@ -51,6 +51,12 @@ enum {
 
 const char* wv_strerror(int code);
 int wv_last_cuda_error(void);
+/* number of kernels this library has launched in this process so far (every launch site counts itself); bench.py reports the
+ * difference over its timed region as "gpu_launches" */
+unsigned long long wv_launch_count(void);
+/* measurement aid: enqueue an empty cooperative grid of `n_ctas` CTAs (<= 0: the BA kernel's grid) that executes `iters`
+ * grid-wide barriers; timing it gives the per-barrier latency the windowed BA's latency model uses (bench.py roofline_ba) */
+int wv_gridsync_probe(int n_ctas, int iters, wv_stream_t stream);
 /* 1 when a device of compute capability 10.x is current, else 0 (the library has sm_100a code only) */
 int wv_device_supported(void);
 /* Read a device status word back to the host after everything enqueued on `stream` so far, and clear it when non-zero.

@@ -1,0 +1,106 @@
+"""The reference's UNCHANGED tracker (baseline/_ref/dpvo/dpvo.py: DPVO.__call__ / update / keyframe / terminate) on this
+repository's cuda_corr + cuda_ba + lietorch_backends versus the same host code on the reference's own CUDA build (REF-CUDA,
+oracle/_ref/refgpu_*.so) -- BASELINE.json configs[2], SURVEY 8(c) tolerances:
+
+  * bit-exact: patch-graph indexing, edge lists and keyframe selection -- per frame (n, m, E, crc32(ii), crc32(jj), crc32(kk),
+    initialised) over the whole clip; fastba.neighbors on every call the tracker makes;
+  * teacher-forced per call (>= 200 update() calls): every altcorr.corr and fastba.BA call is repeated by REF-CUDA on clones of
+    the same inputs; corr within the reference's fp16-accumulation error (2e-2 of max(1, |ref|)); BA poses / depths within
+    max(stated fp32 tolerance, 6 x the reference's OWN run-to-run spread on that call) -- its atomics make it non-deterministic;
+  * closed loop: ATE (Sim(3)-aligned translation RMSE, the recipe of evaluation/dpvo_eva_tum.py:174-176) within 5 % of REF-CUDA's.
+
+Each arm runs in its own process (the native modules are imported by name).  Skips when the REF-CUDA modules or the reference
+install were not shipped with the snapshot."""
+import json
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+FRAMES = 220     # 10 init frames + 12 init updates + ~210 per-frame updates + 12 final ones: > 200 update() calls
+
+
+def _need():
+    miss = [p for p in [os.path.join(ROOT, "baseline", "_ref", "dpvo", "dpvo.py")] +
+            [os.path.join(ROOT, "oracle", "_ref", f"refgpu_{n}.so") for n in ("cuda_corr", "cuda_ba", "lietorch_backends")] if not os.path.exists(p)]
+    if miss:
+        pytest.skip("not shipped with this snapshot: " + ", ".join(os.path.relpath(m, ROOT) for m in miss))
+
+
+def _run(backend, tmp, *extra):
+    out = os.path.join(tmp, f"track_{backend}.json")
+    poses = os.path.join(tmp, f"poses_{backend}.npz")
+    cmd = [sys.executable, os.path.join(ROOT, "tools", "track.py"), "--backend", backend, "--frames", str(FRAMES), "--log", "--out", out,
+           "--save-poses", poses, *extra]
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=1500)
+    assert p.returncode == 0, p.stderr[-3000:]
+    with open(out) as f:
+        return json.load(f), np.load(poses)
+
+
+@pytest.fixture(scope="module")
+def arms(tmp_path_factory):
+    _need()
+    tmp = str(tmp_path_factory.mktemp("tracker"))
+    ref, ref_p = _run("refcuda", tmp)
+    our, our_p = _run("b200", tmp, "--calls")
+    return ref, ref_p, our, our_p
+
+
+@pytest.mark.gpu
+def test_native_modules_are_this_repositorys(arms):
+    ref, _, our, _ = arms
+    pk = os.path.join(ROOT, "wild-video-3d-reconstruction_b200")
+    assert all(os.path.dirname(m) == pk for m in our["native"]) and os.path.dirname(our["lietorch"]) == pk, our["native"]
+    assert all("backends_refcuda" in m for m in ref["native"])
+    assert our["finite"] and ref["finite"] and our["n_poses"] == FRAMES == ref["n_poses"]
+
+
+@pytest.mark.gpu
+def test_edge_lists_and_keyframe_selection_bit_exact(arms):
+    ref, _, our, _ = arms
+    assert len(our["frame_log"]) == FRAMES == len(ref["frame_log"])
+    diff = [i for i, (a, b) in enumerate(zip(our["frame_log"], ref["frame_log"])) if a != b]
+    assert not diff, f"first differing frame {diff[0]}: ours {our['frame_log'][diff[0]]} vs REF-CUDA {ref['frame_log'][diff[0]]}"
+    assert our["keyframes"] == ref["keyframes"] and our["edges"] == ref["edges"]
+    # the clip exercises both decisions: some frames were kept as keyframes, some removed
+    ns = [f[0] for f in our["frame_log"]]
+    assert max(ns) > 30 and any(b == a for a, b in zip(ns[20:], ns[21:])) and any(b == a + 1 for a, b in zip(ns[20:], ns[21:]))
+
+
+@pytest.mark.gpu
+def test_teacher_forced_calls_match_refcuda(arms):
+    _, _, our, _ = arms
+    c = our["calls"]
+    assert c["ba_calls"] >= 200 and c["corr_calls"] >= 400 and c["nb_calls"] >= 200
+    assert c["nb_mismatch"] == 0                                      # neighbors: bit-exact on every call
+    assert c["corr_max_rel_to_peak"] <= 2e-2, c["corr_max_rel_to_peak"]   # |new - ref| <= 2e-2 max(1, |ref|) for fp16 maps
+    bad = []
+    for r in c["ba_per_call"]:
+        windowed = r["t1"] - r["t0"] <= 10 and r["t0"] > 1            # steady state; the 12 initialisation calls (t0 = 1) are gauge-free
+        tol_t = max(1e-4 if windowed else 5e-2, 6 * r["ref_dt"])
+        tol_q = max(2e-5 if windowed else 2e-4, 6 * r["ref_dq"])
+        if r["dt"] > tol_t * max(1.0, r["tmag"]) or r["dq"] > tol_q:
+            bad.append(r)
+    assert not bad, bad[:3]
+    # depths: the median patch agrees to 5e-4 relative on every steady-state call (most to fp32 round-off); single unconstrained patches (C ~ lambda) wander in the
+    # reference as well (its own spread is recorded beside ours)
+    assert max(r["dd_med"] for r in c["ba_per_call"] if r["t0"] > 1) <= 5e-4
+    assert max(r["dd_med"] for r in c["ba_per_call"]) <= 5e-2           # the gauge-free initialisation calls
+    st = [r for r in c["ba_per_call"] if r["t0"] > 1]
+    assert np.median([r["dd"] for r in st]) <= 10 * max(np.median([r["ref_dd"] for r in st]), 1e-5)
+
+
+@pytest.mark.gpu
+def test_closed_loop_ate_within_5_percent_of_refcuda(arms):
+    ref, ref_p, our, our_p = arms
+    assert np.isfinite(our["ate"]) and np.isfinite(ref["ate"])
+    assert our["ate"] < 0.05, our["ate"]                              # metres on a ~60 m path: the loop actually tracks
+    assert abs(our["ate"] - ref["ate"]) <= 0.05 * ref["ate"] + 1e-4, (our["ate"], ref["ate"])
+    sys.path.insert(0, ROOT)
+    from harness.world import ate_rmse
+    # the two arms' trajectories agree with each other far better than either agrees with the ground truth
+    assert ate_rmse(our_p["poses"][:, :3], ref_p["poses"][:, :3]) <= 0.2 * ref["ate"]

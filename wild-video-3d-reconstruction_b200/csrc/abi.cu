@@ -12,13 +12,16 @@
 
 namespace wv {
 int g_last_cuda_error = 0;
+unsigned long long g_launches = 0;
 
 int sm_count() {
-  static int n = 0;
+  static int per_device[64] = {0};   // one process may drive several GPUs (clip batches in threads): cache per device
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  int n = per_device[dev];
   if (n == 0) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
-      n = 148;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    per_device[dev] = n;
   }
   return n;
 }
@@ -44,6 +47,7 @@ int corr_forward_stacked(const void*, const void*, const void*, const float*, fl
 int corr_forward_tiled(const void*, const void*, const float*, const int64_t*, const int64_t*, void*, int, int, int, int,
                        int, int, int, int, int, int, int, void*, size_t, int*, cudaStream_t);
 // ba_window.cu
+int gridsync_probe(int n_ctas, int iters, cudaStream_t st);
 size_t ba_workspace_bytes(int64_t E, int64_t n_patches, int N);
 int ba_forward_window(float*, float*, const float*, const float*, const float*, const float*, const int64_t*,
                       const int64_t*, const int64_t*, int64_t, int64_t, int64_t, int, int, int, int, const float*, float,
@@ -88,6 +92,8 @@ const char* wv_strerror(int code) {
 }
 
 int wv_last_cuda_error(void) { return g_last_cuda_error; }
+unsigned long long wv_launch_count(void) { return g_launches; }
+int wv_gridsync_probe(int n_ctas, int iters, wv_stream_t stream) { return wv::gridsync_probe(n_ctas, iters, wv::as_stream(stream)); }
 
 int wv_device_supported(void) {
   int dev = 0, major = 0;

@@ -301,7 +301,7 @@ int plan_build_groups(const Plan& p, const int64_t* g, int64_t goff, const int64
   if (use_cooperative()) {
     void* args[] = {&a};
     cudaError_t e = cudaLaunchCooperativeKernel((const void*)plan_coop_kernel, dim3(grid), dim3(kPlanThreads), args, sh, st);
-    if (e == cudaSuccess) return WV_OK;
+    if (e == cudaSuccess) { ++g_launches; return WV_OK; }
     (void)cudaGetLastError();  // fall through to the multi-launch form
   }
   if (!a.small) {

@@ -506,6 +506,28 @@ int ba_forward_window(float* poses, float* patches, const float* intr, const flo
   int Gb = G;   // CTAs of the BA kernel itself (<= the plan's grid: the partial-sum array is sized for G)
   if (const char* e = getenv("WVB200_BA_GRID")) { const int v = atoi(e); if (v > 0 && v < G) Gb = v; }
   WV_CUDA_TRY(cudaLaunchCooperativeKernel((const void*)ba_window_kernel, dim3(Gb), dim3(kBaThreads), args, smem, st));
+  ++g_launches;
+  return WV_OK;
+}
+
+// latency probe for the windowed BA's roofline model (bench.py roofline_ba): `iters` grid-wide barriers of an otherwise empty
+// cooperative grid of the BA kernel's shape; the caller times the launch.
+__global__ void __launch_bounds__(kBaThreads) gridsync_probe_kernel(int iters, int* sink) {
+  cg::grid_group grid = cg::this_grid();
+  int acc = 0;
+  for (int i = 0; i < iters; ++i) {
+    grid.sync();
+    acc += i;
+  }
+  if (sink && acc == -1) *sink = acc;
+}
+
+int gridsync_probe(int n_ctas, int iters, cudaStream_t st) {
+  if (n_ctas <= 0) n_ctas = plan_grid();
+  int* sink = nullptr;
+  void* args[] = {&iters, &sink};
+  WV_CUDA_TRY(cudaLaunchCooperativeKernel((const void*)gridsync_probe_kernel, dim3(n_ctas), dim3(kBaThreads), args, 0, st));
+  ++g_launches;
   return WV_OK;
 }
 

@@ -863,6 +863,17 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize is per device: remember per (kernel, device) whether it has been raised, so that one
+// process driving several GPUs (clip batches in threads) opts in on each of them.  Returns the previous state and marks it set.
+bool smem_opted_in(int kernel) {
+  static bool done[3][64] = {};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return false;   // unknown device: set the attribute every call
+  const bool was = done[kernel][dev];
+  done[kernel][dev] = true;
+  return was;
+}
+
 EncodeTiledFn encode_tiled_fn() {
   static EncodeTiledFn fn = nullptr;
   static bool tried = false;
@@ -952,11 +963,7 @@ int corr_forward_tiled(const void* fmap1, const void* fmap2, const float* coords
   CorrParams P{gT, (const __half*)fmap2, coords, ii, jj, (__half*)out, B, E, n1, n2, H2, W2, status, nullptr, 0, 0, 1.f, 1.f};
   const long long BE = (long long)B * E;
   if (use_tc5) {
-    static bool t5_attr_set = false;
-    if (!t5_attr_set) {
-      WV_CUDA_TRY(cudaFuncSetAttribute(corr_tc5_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kT5Smem));
-      t5_attr_set = true;
-    }
+    if (!smem_opted_in(0)) WV_CUDA_TRY(cudaFuncSetAttribute(corr_tc5_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, kT5Smem));
     CorrMaps maps;
     if (!make_map(&maps.m[2], nhwc, W2, H2, slots, kBoxTiny, kBoxTiny)) return WV_EUNSUPPORTED;
     maps.m[0] = ms; maps.m[1] = mh; maps.m[3] = ms; maps.m[4] = mh; maps.m[5] = maps.m[2];
@@ -965,11 +972,7 @@ int corr_forward_tiled(const void* fmap1, const void* fmap2, const float* coords
     WV_LAUNCH_CHECK();
     return WV_OK;
   }
-  static bool attr_set = false;
-  if (!attr_set) {
-    WV_CUDA_TRY(cudaFuncSetAttribute(corr_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    attr_set = true;
-  }
+  if (!smem_opted_in(1)) WV_CUDA_TRY(cudaFuncSetAttribute(corr_tiled_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
   const long long want = (BE + kConsumers - 1) / kConsumers;
   const int grid = (int)(want < sm_count() ? want : sm_count());
   corr_tiled_kernel<<<grid, kThreads, kSmemBytes, st>>>(ms, mh, P);
@@ -1032,11 +1035,7 @@ int corr_forward_stacked(const void* fmap1, const void* fmap2_l0, const void* fm
 
   CorrParams P{gT, (const __half*)fmap2_l0, coords, ii, jj, (__half*)out, B, E, n1, n2, H0, W0, status,
                (const __half*)fmap2_l1, H1, W1, cmul0, cmul1};
-  static bool attr_set2 = false;
-  if (!attr_set2) {
-    WV_CUDA_TRY(cudaFuncSetAttribute(corr_tc5_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kT5Smem));
-    attr_set2 = true;
-  }
+  if (!smem_opted_in(2)) WV_CUDA_TRY(cudaFuncSetAttribute(corr_tc5_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kT5Smem));
   const long long want = ((long long)B * E + 7) / 8;
   corr_tc5_kernel<2><<<(int)(want < sm_count() ? want : sm_count()), kT5Threads, kT5Smem, st>>>(maps, P);
   WV_LAUNCH_CHECK();

@@ -9,6 +9,7 @@
 namespace wv {
 
 extern int g_last_cuda_error;  // abi.cu
+extern unsigned long long g_launches;  // abi.cu: kernels this library has launched (wv_launch_count)
 
 inline int cuda_fail(cudaError_t e) {
   g_last_cuda_error = (int)e;
@@ -21,7 +22,11 @@ inline int cuda_fail(cudaError_t e) {
     if (_e != cudaSuccess) return ::wv::cuda_fail(_e);      \
   } while (0)
 
-#define WV_LAUNCH_CHECK() WV_CUDA_TRY(cudaGetLastError())
+#define WV_LAUNCH_CHECK()               \
+  do {                                  \
+    ++::wv::g_launches;                 \
+    WV_CUDA_TRY(cudaGetLastError());    \
+  } while (0)
 
 inline cudaStream_t as_stream(wv_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
 
