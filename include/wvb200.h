@@ -206,6 +206,12 @@ int wv_ba_reproject(const float* poses, const float* patches, const float* intri
 int wv_pops_transform(const float* poses, const float* patches, const float* intrinsics, const int64_t* ii,
                       const int64_t* jj, const int64_t* kk, int64_t E, int64_t n_poses, int64_t n_patches, int P,
                       int tonly, int depth, float* coords, float* valid, int* status, wv_stream_t stream);
+/* the jacobian=True outputs of transform (projective_ops.py:71-99), centre pixel of every edge:
+ *   Ji [E][2][6] = -Adj(Gij)^T Jj, Jj [E][2][6] = Jp Ja, Jz [E][2] = Jp Gij.matrix()[:, 3], validc [E] = (Z > 0.2);
+ *   d = 1 / Z where |Z| > 0.2 else 0 (projective_ops.py:79-80), intrinsics of frame jj. */
+int wv_pops_jacobian(const float* poses, const float* patches, const float* intrinsics, const int64_t* ii,
+                     const int64_t* jj, const int64_t* kk, int64_t E, int64_t n_poses, int64_t n_patches, int P,
+                     int tonly, float* Ji, float* Jj, float* Jz, float* validc, int* status, wv_stream_t stream);
 int wv_pops_flow_mag(const float* poses, const float* patches, const float* intrinsics, const int64_t* ii,
                      const int64_t* jj, const int64_t* kk, int64_t E, int64_t n_poses, int64_t n_patches, int P,
                      float beta, float* out, int* status, wv_stream_t stream);

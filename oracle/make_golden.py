@@ -165,6 +165,9 @@ def pops_cases():
         co, val = pops.transform(G, pt, K, ii, jj, kk, depth=True, valid=True)
         out[f"{name}_transform_depth"] = co[0].numpy(); out[f"{name}_valid"] = val[0].numpy()
         out[f"{name}_transform_tonly"] = pops.transform(G, pt, K, ii, jj, kk, tonly=True)[0].numpy()
+        xj, vj, (Ji, Jj, Jz) = pops.transform(G, pt, K, ii, jj, kk, jacobian=True)       # projective_ops.py:71-99
+        out.update({f"{name}_jac_x1": xj[0].numpy(), f"{name}_jac_valid": vj[0].numpy(), f"{name}_jac_Ji": Ji[0].numpy(),
+                    f"{name}_jac_Jj": Jj[0].numpy(), f"{name}_jac_Jz": Jz[0].numpy()})
         for beta in (0.3, 0.5):
             out[f"{name}_flow_mag_{beta}"] = pops.flow_mag(G, pt, K, ii, jj, kk, beta=beta)[0].numpy()
         n, M = s["n"], s["M"]

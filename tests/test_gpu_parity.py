@@ -761,8 +761,15 @@ def test_pops_matches_reference_python(golden, name):
         assert np.abs(pops.flow_mag(*a, beta=beta)[0].cpu().numpy() - g[f"{name}_flow_mag_{beta}"]).max() < 2e-4
     pc = pops.point_cloud(a[0], a[1], a[2], dev(g[f"{name}_ix"]))[0].cpu().numpy()
     assert np.abs(pc - g[f"{name}_point_cloud"]).max() < 2e-6 * max(1.0, np.abs(g[f"{name}_point_cloud"]).max())
-    with pytest.raises(NotImplementedError):
-        pops.transform(*a, jacobian=True)
+    # jacobian=True (projective_ops.py:71-99): centre-pixel Jacobians; entries reach ~1e3 (fx X d^2 with small Z), so the stated
+    # tolerance is relative to each tensor's peak: 2e-5
+    xj, vj, (Ji, Jj, Jz) = pops.transform(*a, jacobian=True)
+    assert np.abs(xj[0].cpu().numpy() - g[f"{name}_jac_x1"]).max() < 2e-4
+    assert np.array_equal(vj[0].cpu().numpy(), g[f"{name}_jac_valid"])
+    for got, key in ((Ji, "Ji"), (Jj, "Jj"), (Jz, "Jz")):
+        want = g[f"{name}_jac_{key}"]
+        assert tuple(got.shape) == (1,) + want.shape
+        assert np.abs(got[0].cpu().numpy() - want).max() <= 2e-5 * max(1.0, np.abs(want).max()), key
 
     class FakeSE3:  # anything with .data, like lietorch's SE3
         data = a[0]

@@ -104,3 +104,29 @@ def test_closed_loop_ate_within_5_percent_of_refcuda(arms):
     from harness.world import ate_rmse
     # the two arms' trajectories agree with each other far better than either agrees with the ground truth
     assert ate_rmse(our_p["poses"][:, :3], ref_p["poses"][:, :3]) <= 0.2 * ref["ate"]
+
+
+@pytest.mark.gpu
+def test_clip_batch_export_is_independent_of_the_sharding(tmp_path):
+    """configs[4]: the same clips tracked by ONE process and sharded over TWO processes (gloo rendezvous, so
+    that both ranks can share the single GPU of a test box) export the same COLMAP text: images.txt ID / camera / name columns
+    byte-identical, pose and point columns within 1e-4."""
+    if not os.path.exists(os.path.join(ROOT, "baseline", "_ref", "dpvo", "dpvo.py")):
+        pytest.skip("baseline/_ref not shipped with this snapshot")
+    a, b = str(tmp_path / "one"), str(tmp_path / "two")
+    common = ["--clips", "4", "--frames", "50", "--M", "96"]
+    tool = os.path.join(ROOT, "tools", "run_clips.py")
+    p = subprocess.run([sys.executable, tool, *common, "--out", a], capture_output=True, text=True, timeout=900)
+    assert p.returncode == 0, p.stderr[-3000:]
+    one = json.loads(p.stdout.strip().splitlines()[-1])
+    env = dict(os.environ, WV_DIST_BACKEND="gloo")
+    p = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+                        "--master-port", "29533", tool, *common, "--out", b], capture_output=True, text=True, timeout=900, env=env)
+    assert p.returncode == 0, p.stderr[-3000:]
+    two = json.loads(p.stdout.strip().splitlines()[-1])
+    assert one["clips"] == two["clips"] == 4 and two["n_gpus"] == 2 and two["clips_per_rank"] == [2, 2]
+    assert all(np.isfinite(c["ate"]) and c["ate"] < 0.05 for c in one["per_clip"] + two["per_clip"])
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import run_clips
+    res = run_clips.compare_trees(a, b, tol=1e-4)
+    assert res["clips"] == 4

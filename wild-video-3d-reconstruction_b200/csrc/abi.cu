@@ -67,6 +67,8 @@ int ba_global_dz(float*, float*, const float*, const float*, const float*, const
                  cudaStream_t);
 int ba_global_retract(float*, float*, int64_t, int64_t, int64_t, int, int, int, const float*, const float*, void*, size_t,
                       cudaStream_t);
+int pops_jacobian(const float*, const float*, const float*, const int64_t*, const int64_t*, const int64_t*, int64_t, int64_t, int64_t, int, int,
+                  float*, float*, float*, float*, int*, cudaStream_t);
 int pops_transform(const float*, const float*, const float*, const int64_t*, const int64_t*, const int64_t*, int64_t, int64_t, int64_t,
                    int, int, int, float*, float*, int*, cudaStream_t);
 int pops_flow_mag(const float*, const float*, const float*, const int64_t*, const int64_t*, const int64_t*, int64_t, int64_t, int64_t,
@@ -346,6 +348,15 @@ int wv_pops_transform(const float* poses, const float* patches, const float* int
   if (!poses || !patches || !intrinsics || !ii || !jj || !kk || !coords) return WV_EINVAL;
   return pops_transform(poses, patches, intrinsics, ii, jj, kk, E, n_poses, n_patches, P, tonly != 0, depth != 0, coords, valid, status,
                         as_stream(stream));
+}
+
+int wv_pops_jacobian(const float* poses, const float* patches, const float* intrinsics, const int64_t* ii, const int64_t* jj,
+                     const int64_t* kk, int64_t E, int64_t n_poses, int64_t n_patches, int P, int tonly, float* Ji, float* Jj, float* Jz,
+                     float* validc, int* status, wv_stream_t stream) {
+  if (E < 0 || n_poses <= 0 || n_patches <= 0 || P <= 0) return WV_EINVAL;
+  if (E == 0) return WV_OK;
+  if (!poses || !patches || !intrinsics || !ii || !jj || !kk || !Ji || !Jj || !Jz || !validc) return WV_EINVAL;
+  return pops_jacobian(poses, patches, intrinsics, ii, jj, kk, E, n_poses, n_patches, P, tonly != 0, Ji, Jj, Jz, validc, status, as_stream(stream));
 }
 
 int wv_pops_flow_mag(const float* poses, const float* patches, const float* intrinsics, const int64_t* ii, const int64_t* jj,

@@ -288,6 +288,27 @@ std::vector<torch::Tensor> pops_transform(torch::Tensor poses, torch::Tensor pat
   return {coords};
 }
 
+// transform(..., jacobian=True): [x1, validc, Ji, Jj, Jz] (projective_ops.py:71-99)
+std::vector<torch::Tensor> pops_transform_jacobian(torch::Tensor poses, torch::Tensor patches, torch::Tensor intrinsics, torch::Tensor ii,
+                                                   torch::Tensor jj, torch::Tensor kk, bool depth, bool tonly) {
+  c10::cuda::CUDAGuard guard(poses.device());
+  PopsIn x = pops_inputs(poses, patches, intrinsics, ii, jj, kk);
+  torch::Tensor coords = torch::empty({1, x.E, x.P, x.P, depth ? 3 : 2}, x.po.options());
+  torch::Tensor Ji = torch::empty({1, x.E, 2, 6}, x.po.options()), Jj = torch::empty({1, x.E, 2, 6}, x.po.options());
+  torch::Tensor Jz = torch::empty({1, x.E, 2, 1}, x.po.options()), val = torch::empty({1, x.E}, x.po.options());
+  int* st = status_word(x.po.device()).data_ptr<int>();
+  check_rc(wv_pops_transform(x.po.data_ptr<float>(), x.pa.data_ptr<float>(), x.in.data_ptr<float>(), x.ii.data_ptr<int64_t>(),
+                             x.jj.data_ptr<int64_t>(), x.kk.data_ptr<int64_t>(), x.E, x.n_poses, x.n_patches, x.P, tonly, depth,
+                             coords.data_ptr<float>(), nullptr, st, current_stream()),
+           "cuda_ba.transform_jacobian");
+  check_rc(wv_pops_jacobian(x.po.data_ptr<float>(), x.pa.data_ptr<float>(), x.in.data_ptr<float>(), x.ii.data_ptr<int64_t>(),
+                            x.jj.data_ptr<int64_t>(), x.kk.data_ptr<int64_t>(), x.E, x.n_poses, x.n_patches, x.P, tonly,
+                            Ji.data_ptr<float>(), Jj.data_ptr<float>(), Jz.data_ptr<float>(), val.data_ptr<float>(), st, current_stream()),
+           "cuda_ba.transform_jacobian");
+  if (env_flag("WVB200_CHECK_INDICES")) raise_on_status(x.po.device(), "cuda_ba.transform_jacobian");
+  return {coords, val, Ji, Jj, Jz};
+}
+
 torch::Tensor pops_flow_mag(torch::Tensor poses, torch::Tensor patches, torch::Tensor intrinsics, torch::Tensor ii, torch::Tensor jj,
                             torch::Tensor kk, double beta) {
   c10::cuda::CUDAGuard guard(poses.device());
@@ -371,6 +392,9 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.def("transform", &pops_transform, "fused projective transform (projective_ops.transform, jacobian=False)", py::arg("poses"),
         py::arg("patches"), py::arg("intrinsics"), py::arg("ii"), py::arg("jj"), py::arg("kk"), py::arg("depth") = false,
         py::arg("valid") = false, py::arg("tonly") = false);
+  m.def("transform_jacobian", &pops_transform_jacobian, "fused projective_ops.transform(jacobian=True): [x1, valid, Ji, Jj, Jz]",
+        py::arg("poses"), py::arg("patches"), py::arg("intrinsics"), py::arg("ii"), py::arg("jj"), py::arg("kk"), py::arg("depth") = false,
+        py::arg("tonly") = false);
   m.def("flow_mag", &pops_flow_mag, "fused projective_ops.flow_mag", py::arg("poses"), py::arg("patches"), py::arg("intrinsics"),
         py::arg("ii"), py::arg("jj"), py::arg("kk"), py::arg("beta") = 0.3);
   m.def("point_cloud", &pops_point_cloud, "fused projective_ops.point_cloud");

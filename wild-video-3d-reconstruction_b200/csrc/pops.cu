@@ -108,6 +108,49 @@ __global__ void pops_edge_kernel(PopsArgs a) {
   }
 }
 
+// transform(..., jacobian=True) (projective_ops.py:71-99): derivatives of the CENTRE pixel's projection with respect to the pose of
+// frame j (Jj), of frame i (Ji = -Adj(Gij)^T Jj rows, lietorch adjT) and to the patch's inverse depth (Jz = Jp * Gij.matrix()[:, 3]),
+// plus validc = (Z_centre > 0.2).  One thread per edge.
+__global__ void pops_jacobian_kernel(PopsArgs a, float* __restrict__ Ji, float* __restrict__ Jj, float* __restrict__ Jz,
+                                     float* __restrict__ validc) {
+  const int PP = a.P * a.P, c = (a.P / 2) * a.P + a.P / 2;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < a.E; e += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t i = a.ii[e], j = a.jj[e], k = a.kk[e];
+    float* oi = Ji + e * 12; float* oj = Jj + e * 12; float* oz = Jz + e * 2;
+    if (i < 0 || i >= a.n_poses || j < 0 || j >= a.n_poses || k < 0 || k >= a.n_patches) {
+      set_status(a.status, WV_STATUS_BAD_INDEX);
+      for (int t = 0; t < 12; t++) { oi[t] = 0.f; oj[t] = 0.f; }
+      oz[0] = oz[1] = 0.f; validc[e] = 0.f;
+      continue;
+    }
+    const float* pc = a.patches + k * 3 * PP + c;
+    const float* Ki = a.intr + 4 * i;
+    const float* Kj = a.intr + 4 * j;
+    const float xn = (pc[0] - Ki[2]) / Ki[0], yn = (pc[PP] - Ki[3]) / Ki[1], H = pc[2 * PP];
+    Rigid G = lie_relative(a.poses + 7 * i, a.poses + 7 * j);
+    if (a.tonly) G.q = {0.f, 0.f, 0.f, 1.f};
+    const Quat q = qnormalize(G.q);
+    const Vec3 r = rotate(q, {xn, yn, 1.f});
+    const float X = r.x + G.t.x * H, Y = r.y + G.t.y * H, Z = r.z + G.t.z * H;
+    const float d = fabsf(Z) > 0.2f ? 1.0f / Z : 0.f;
+    const float fx = Kj[0], fy = Kj[1];
+    // Jp (2x4) * Ja (4x6): rows of the projection derivative with respect to a left perturbation of Gj
+    const float px0 = fx * d, px2 = -fx * X * d * d, py1 = fy * d, py2 = -fy * Y * d * d;
+    float row[2][6] = {{px0 * H, 0.f, px2 * H, px2 * Y, px0 * Z - px2 * X, -px0 * Y},
+                       {0.f, py1 * H, py2 * H, -py1 * Z + py2 * Y, -py2 * X, py1 * X}};
+#pragma unroll
+    for (int rr = 0; rr < 2; rr++) {
+      float back[6];
+      adjoint_T(G.t, q, row[rr], back);           // Adj(Gij)^T row
+#pragma unroll
+      for (int t = 0; t < 6; t++) { oj[rr * 6 + t] = row[rr][t]; oi[rr * 6 + t] = -back[t]; }
+    }
+    oz[0] = px0 * G.t.x + px2 * G.t.z;
+    oz[1] = py1 * G.t.y + py2 * G.t.z;
+    validc[e] = Z > 0.2f ? 1.f : 0.f;
+  }
+}
+
 __global__ void pops_point_cloud_kernel(const float* __restrict__ poses, const float* __restrict__ patches,
                                         const float* __restrict__ intr, const int64_t* __restrict__ ix, int64_t n, int64_t n_poses,
                                         int P, float* __restrict__ out, int* status) {
@@ -187,6 +230,16 @@ int pops_transform(const float* poses, const float* patches, const float* intr, 
   if (E == 0) return WV_OK;
   PopsArgs a{poses, patches, intr, ii, jj, kk, E, n_poses, n_patches, P, tonly, depth, 0.f, coords, valid, status};
   pops_edge_kernel<0><<<edge_grid(E * P * P), 256, 0, st>>>(a);
+  WV_LAUNCH_CHECK();
+  return WV_OK;
+}
+
+int pops_jacobian(const float* poses, const float* patches, const float* intr, const int64_t* ii, const int64_t* jj, const int64_t* kk,
+                  int64_t E, int64_t n_poses, int64_t n_patches, int P, int tonly, float* Ji, float* Jj, float* Jz, float* validc, int* status,
+                  cudaStream_t st) {
+  if (E == 0) return WV_OK;
+  PopsArgs a{poses, patches, intr, ii, jj, kk, E, n_poses, n_patches, P, tonly, 0, 0.f, nullptr, nullptr, status};
+  pops_jacobian_kernel<<<edge_grid(E), 256, 0, st>>>(a, Ji, Jj, Jz, validc);
   WV_LAUNCH_CHECK();
   return WV_OK;
 }

@@ -5,7 +5,7 @@ pops` call sites (DPVO.reproject dpvo/dpvo.py:318-321, motionmag / compute_keyfr
 work unchanged.  `poses` may be a lietorch SE3 (anything with a `.data` tensor [1, N, 7]) or that tensor itself.  One kernel per
 call replaces ~12 lietorch / elementwise launches and the repeat()-materialised broadcast of Gij (lietorch/broadcasting.py:26-29).
 
-jacobian=True (used only by the Python BA, dpvo/ba.py:95, which is the reference's CPU path and not part of this build) raises.
+jacobian=True (used by the Python BA, dpvo/ba.py:95) returns the centre-pixel Jacobians Ji, Jj, Jz from one more kernel.
 """
 import torch
 
@@ -48,8 +48,9 @@ def proj(X, intrinsics, depth=False):
 
 def transform(poses, patches, intrinsics, ii, jj, kk, depth=False, valid=False, jacobian=False, tonly=False):
     """projective transform (projective_ops.py:53-104): coords [1, E, P, P, 2|3] (, valid [1, E, P, P])"""
-    if jacobian:
-        raise NotImplementedError("transform(jacobian=True) belongs to the reference's Python BA (dpvo/ba.py); use fastba.BA")
+    if jacobian:   # projective_ops.py:71-99: (x1, (Z_centre > 0.2).float(), (Ji, Jj, Jz))
+        x1, val, Ji, Jj, Jz = cuda_ba.transform_jacobian(_pose_data(poses), patches, intrinsics, ii, jj, kk, depth, tonly)
+        return x1, val, (Ji, Jj, Jz)
     out = cuda_ba.transform(_pose_data(poses), patches, intrinsics, ii, jj, kk, depth, valid, tonly)
     return (out[0], out[1]) if valid else out[0]
 
