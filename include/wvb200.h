@@ -38,7 +38,8 @@ enum {
   WV_EINVAL = -1,      /* bad argument (null pointer, negative size, unsupported dtype/shape) */
   WV_ECUDA = -2,       /* a CUDA runtime/driver call failed; wv_last_cuda_error() has the code */
   WV_EWORKSPACE = -3,  /* workspace too small */
-  WV_EUNSUPPORTED = -4 /* shape outside what this build supports */
+  WV_EUNSUPPORTED = -4, /* shape outside what this build supports */
+  WV_ELIMIT = -5        /* a size exceeds the fixed maximum of a no-allocation entry point (wv_neighbors_static) */
 };
 
 /* bits of the device status word */
@@ -244,6 +245,18 @@ int wv_soft_agg_forward(const void* fx, const void* gx, const int32_t* order, co
  * order, -1 at the ends.  ii values must lie in [0, n_groups). */
 int wv_neighbors(const int64_t* ii, const int64_t* jj, int64_t E, int64_t n_groups, int64_t* ix,
                  int64_t* jx, void* workspace, size_t workspace_bytes, int* status, wv_stream_t stream);
+
+/* wv_neighbors without a workspace argument, for callers that may not allocate (CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same inputs, outputs and results as wv_neighbors; the plan's scratch is a fixed 21 MiB static device array inside the library
+ * (every GPU that loads it holds the array until the process exits), so the call allocates and frees nothing.
+ *   limits: E <= WV_NEIGHBORS_STATIC_MAX_EDGES and n_groups <= WV_NEIGHBORS_STATIC_MAX_GROUPS, else WV_ELIMIT (nothing enqueued).
+ *   all calls on one device share that array: calls that overlap on the GPU (different streams without an ordering between
+ *   them) race -- serialise them.  The array keeps the previous call's contents; the call itself clears what must start at zero. */
+#define WV_NEIGHBORS_STATIC_MAX_EDGES 262144
+#define WV_NEIGHBORS_STATIC_MAX_GROUPS 1048576
+int wv_neighbors_static(const int64_t* ii, const int64_t* jj, int64_t E, int64_t n_groups, int64_t* ix,
+                        int64_t* jx, int* status, wv_stream_t stream);
 
 /* cuda_ba.solve_system (dpvo/fastba/ba.cpp:156-234) -- HOST pointers, synchronous, fp64 like the
  * reference's Eigen::SimplicialCholesky<double>.  J_i / J_j [r][7][7], res [r][7] -> delta [n][7] with

@@ -88,6 +88,7 @@ const char* wv_strerror(int code) {
     case WV_ECUDA: return "CUDA call failed";
     case WV_EWORKSPACE: return "workspace too small";
     case WV_EUNSUPPORTED: return "shape not supported by this build";
+    case WV_ELIMIT: return "size beyond the fixed maximum of a no-allocation entry point";
     case 1: return "matrix not positive definite";
     default: return "unknown error";
   }
