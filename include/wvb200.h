@@ -177,6 +177,31 @@ int wv_ba_global_build(float* poses, float* patches, const float* intrinsics, co
                        const int64_t* kk, int64_t E, int64_t n_poses, int64_t n_patches, int P, int t0, int t1,
                        const float* patches_est, float mu, int shard, int nshards, int build_plan, float* S,
                        float* y, void* workspace, size_t workspace_bytes, int* status, wv_stream_t stream);
+/* ---- banded reduced system (csrc/ba_band.cu) -------------------------------------------------------------
+ * S couples two free poses only if some patch is observed by both.  wv_ba_global_span reports the widest frame span of any
+ * patch's observations among the free poses (after building the edge plan in `workspace` when build_plan != 0).  When
+ * span <= bs <= wv_ba_band_max_bs() (bs >= 2), S is banded with a half-width of bs pose blocks:
+ *   wv_ba_global_build_band accumulates it into a band buffer of wv_ba_band_floats(n6, bs) floats (about 6N * 6 (bs + 2) instead
+ *   of (6N)^2 -- also what an all-reduce over ranks then moves); element (r, c), r >= c, lives at Sband[r * ld + c],
+ *   ld = 6 (bs + 2) rounded up to a multiple of 4;
+ *   wv_ba_band_solve factorises and solves it on the device (two launches, no host sync): damping S_dd <- S_dd (1 + 1e-4) + 1
+ *   when damp != 0 (ba_cuda.cu:517-518), band Cholesky, dX = S^-1 y.  It replaces torch::linalg::cholesky + cholesky_solve on the
+ *   dense matrix (ba_cuda.cu:521-523).  `factors`: wv_ba_band_factor_floats(n6, bs) floats of scratch, 16-byte aligned.
+ *   A non-positive pivot sets WV_STATUS_NOT_SPD.  Everything else of an iteration (dz, retract) is unchanged. */
+int wv_ba_band_max_bs(void);
+size_t wv_ba_band_floats(int n6, int bs);
+size_t wv_ba_band_factor_floats(int n6, int bs);
+int wv_ba_global_span(const int64_t* ii, const int64_t* jj, const int64_t* kk, int64_t E, int64_t n_poses,
+                      int64_t n_patches, int t0, int t1, int build_plan, int* span_out, void* workspace,
+                      size_t workspace_bytes, int* status, wv_stream_t stream);
+int wv_ba_global_build_band(float* poses, float* patches, const float* intrinsics, const float* target,
+                            const float* weight, const float* lmbda, const int64_t* ii, const int64_t* jj,
+                            const int64_t* kk, int64_t E, int64_t n_poses, int64_t n_patches, int P, int t0,
+                            int t1, const float* patches_est, float mu, int shard, int nshards, int build_plan,
+                            int bs, float* Sband, float* y, void* workspace, size_t workspace_bytes, int* status,
+                            wv_stream_t stream);
+int wv_ba_band_solve(const float* Sband, const float* y, int n6, int bs, int damp, float* factors, float* dX,
+                     int* status, wv_stream_t stream);
 /* S_dd <- S_dd * (1 + 1e-4) + 1 (ba_cuda.cu:517-518); n6 = 6 * (t1 - t0) */
 int wv_ba_global_damp(float* S, int n6, wv_stream_t stream);
 int wv_ba_global_dz(float* poses, float* patches, const float* intrinsics, const float* target,

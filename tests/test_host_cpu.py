@@ -119,8 +119,31 @@ def test_two_ranks_gloo_replicas():
 # CPU stand-in for the four cuda_ba.global_* pieces (a linear toy problem with the same build -> solve -> dz -> retract algebra).
 # ----------------------------------------------------------------------------------------------------------
 class _ToyGlobalBA:
-    def __init__(self):
+    def __init__(self, band=0):
         self.calls = []
+        self.band = band                        # what band_block answers: 0 = dense route, > 0 = band route
+
+    def global_span(self, poses, patches, ii, jj, kk, t0, t1, build_plan):
+        self.calls.append(("span", bool(build_plan)))
+        return 5
+
+    def band_block(self, span):
+        assert span == 5
+        return self.band
+
+    def global_build_band(self, poses, patches, intr, target, weight, lmbda, ii, jj, kk, t0, t1, shard, nshards, bs, est, mu):
+        # the toy problem is dense; its "band buffer" is the dense one -- what is under test is which calls BA_sharded makes
+        assert bs == self.band
+        self.calls.append(("build_band", shard, nshards, bs))
+        self.calls, keep = [], self.calls
+        out = self.global_build(poses, patches, intr, target, weight, lmbda, ii, jj, kk, t0, t1, shard, nshards, False, est, mu)
+        self.calls = keep
+        return out
+
+    def global_solve_band(self, Sy, n_free, bs):
+        assert bs == self.band
+        self.calls.append(("solve_band", bs))
+        return self.global_solve(Sy, n_free)
 
     @staticmethod
     def _patch_terms(k, depth, n6):
@@ -180,7 +203,7 @@ class _ToyGlobalBA:
         patches[kx, 2] += dZ[: len(kx), None, None]
 
 
-def _sharded_worker(rank, world, port, q):
+def _sharded_worker(rank, world, port, q, band=0):
     os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     import sys
     sys.path.insert(0, ROOT)
@@ -189,7 +212,7 @@ def _sharded_worker(rank, world, port, q):
     if world > 1:
         pkg.dist.init("gloo")
     ba = importlib.import_module(PKG + ".fastba.ba")
-    toy = _ToyGlobalBA()
+    toy = _ToyGlobalBA(band)
     ba.cuda_ba = toy                                   # the CPU stand-in; the product path is the CUDA extension
     n, M = 9, 5
     ii, jj, kk = pkg.synthetic.global_edges(n, M)
@@ -204,7 +227,8 @@ def _sharded_worker(rank, world, port, q):
         pkg.dist.finalize()
 
 
-def test_ba_sharded_host_logic_gloo_two_ranks():
+@pytest.mark.parametrize("band", [0, 3])
+def test_ba_sharded_host_logic_gloo_two_ranks(band):
     import torch.multiprocessing as mp
     ctx = mp.get_context("spawn")
     results = {}
@@ -212,7 +236,7 @@ def test_ba_sharded_host_logic_gloo_two_ranks():
         with socket.socket() as s:
             s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]
         q = ctx.Queue()
-        ps = [ctx.Process(target=_sharded_worker, args=(r, world, port, q)) for r in range(world)]
+        ps = [ctx.Process(target=_sharded_worker, args=(r, world, port, q, band)) for r in range(world)]
         [p.start() for p in ps]
         results[world] = sorted((q.get(timeout=180) for _ in ps), key=lambda o: o[0])
         [p.join(60) for p in ps]
@@ -223,10 +247,18 @@ def test_ba_sharded_host_logic_gloo_two_ranks():
     np.testing.assert_allclose(r0[1], one[1], rtol=1e-5, atol=1e-6)
     np.testing.assert_allclose(r0[2], one[2], rtol=1e-5, atol=1e-6)
     assert not np.array_equal(one[1], results[1][0][1] * 0)  # something moved
-    # shard arguments and the plan flag: (rank, world) on every call, plan built on the first iteration only
+    # shard arguments and the plan flag: (rank, world) on every call; the span query builds the plan once, the builds reuse it;
+    # the band route is taken iff band_block says so, with the matching solve
     for rank, res in enumerate((r0, r1)):
-        builds = [c for c in res[3] if c[0] == "build"]
-        assert [b[1:3] for b in builds] == [(rank, 2), (rank, 2)] and [b[3] for b in builds] == [True, False]
+        assert [c for c in res[3] if c[0] == "span"] == [("span", True)]
+        if band:
+            assert [c for c in res[3] if c[0] == "build_band"] == [("build_band", rank, 2, band)] * 2
+            assert [c for c in res[3] if c[0] == "solve_band"] == [("solve_band", band)] * 2
+            assert not [c for c in res[3] if c[0] == "build"]
+        else:
+            builds = [c for c in res[3] if c[0] == "build"]
+            assert [b[1:3] for b in builds] == [(rank, 2), (rank, 2)] and [b[3] for b in builds] == [False, False]
+            assert not [c for c in res[3] if c[0] in ("build_band", "solve_band")]
         assert [c[1:] for c in res[3] if c[0] == "dz"] == [(rank, 2), (rank, 2)]
 
 

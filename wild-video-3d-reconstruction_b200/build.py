@@ -20,7 +20,7 @@ CUDA_HOME = os.environ.get("CUDA_HOME", "/usr/local/cuda")
 NVCC = os.path.join(CUDA_HOME, "bin", "nvcc")
 HOST_CXX = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
 
-CU_SOURCES = ["abi.cu", "host_entry.cu", "corr_generic.cu", "corr_sm100.cu", "ba_plan.cu", "ba_window.cu", "ba_global.cu", "pops.cu", "agg.cu", "colmap_text.cu", "lie_ops.cu", "neighbors_static.cu"]
+CU_SOURCES = ["abi.cu", "host_entry.cu", "corr_generic.cu", "corr_sm100.cu", "ba_plan.cu", "ba_window.cu", "ba_global.cu", "ba_band.cu", "pops.cu", "agg.cu", "colmap_text.cu", "lie_ops.cu", "neighbors_static.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",
               "-ccbin", HOST_CXX, "--expt-relaxed-constexpr"]
 EXT_SUFFIX = sysconfig.get_config_var("EXT_SUFFIX")

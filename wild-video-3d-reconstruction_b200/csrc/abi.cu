@@ -60,7 +60,10 @@ int plan_grid();
 size_t ba_global_workspace_bytes(int64_t E, int64_t n_patches);
 int ba_global_build(float*, float*, const float*, const float*, const float*, const float*, const int64_t*, const int64_t*,
                     const int64_t*, int64_t, int64_t, int64_t, int, int, int, const float*, float, int, int, int, float*, float*,
-                    void*, size_t, int*, cudaStream_t);
+                    void*, size_t, int*, cudaStream_t, int);
+int ba_global_span(const int64_t*, const int64_t*, const int64_t*, int64_t, int64_t, int64_t, int, int, int, int*, void*, size_t, int*, cudaStream_t);
+int band_ld(int); size_t band_floats(int, int); int band_max_bs(); size_t band_factor_floats(int, int);
+int ba_band_solve(const float*, const float*, int, int, int, float*, float*, int*, cudaStream_t);
 int ba_global_damp(float*, int, cudaStream_t);
 int ba_global_dz(float*, float*, const float*, const float*, const float*, const float*, const int64_t*, const int64_t*, int64_t,
                  int64_t, int64_t, int, int, int, const float*, float, int, int, const float*, float*, void*, size_t, int*,
@@ -304,7 +307,38 @@ int wv_ba_global_build(float* poses, float* patches, const float* intrinsics, co
   if (t1 > t0 && (!S || !y)) return WV_EINVAL;
   if ((reinterpret_cast<uintptr_t>(S) & 15) != 0) return WV_EINVAL;  // vector REDs into S
   return ba_global_build(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk, E, n_poses, n_patches, P, t0, t1,
-                         patches_est, mu, shard, nshards, build_plan, S, y, workspace, workspace_bytes, status, as_stream(stream));
+                         patches_est, mu, shard, nshards, build_plan, S, y, workspace, workspace_bytes, status, as_stream(stream), 0);
+}
+
+int wv_ba_band_max_bs(void) { return band_max_bs(); }
+size_t wv_ba_band_floats(int n6, int bs) { return band_floats(n6, bs); }
+size_t wv_ba_band_factor_floats(int n6, int bs) { return band_factor_floats(n6, bs); }
+
+int wv_ba_global_span(const int64_t* ii, const int64_t* jj, const int64_t* kk, int64_t E, int64_t n_poses, int64_t n_patches, int t0,
+                      int t1, int build_plan, int* span_out, void* workspace, size_t workspace_bytes, int* status, wv_stream_t stream) {
+  if (E <= 0 || n_poses <= 0 || n_patches <= 0 || !ii || !jj || !kk || !span_out || !workspace || t1 < t0) return WV_EINVAL;
+  if (E >= (int64_t)1 << 31 || n_patches >= (int64_t)1 << 31) return WV_EUNSUPPORTED;
+  return ba_global_span(ii, jj, kk, E, n_poses, n_patches, t0, t1, build_plan, span_out, workspace, workspace_bytes, status, as_stream(stream));
+}
+
+int wv_ba_global_build_band(float* poses, float* patches, const float* intrinsics, const float* target, const float* weight,
+                            const float* lmbda, const int64_t* ii, const int64_t* jj, const int64_t* kk, int64_t E, int64_t n_poses,
+                            int64_t n_patches, int P, int t0, int t1, const float* patches_est, float mu, int shard, int nshards,
+                            int build_plan, int bs, float* Sband, float* y, void* workspace, size_t workspace_bytes, int* status,
+                            wv_stream_t stream) {
+  const int rc = global_args_ok(E, n_poses, n_patches, P, t0, t1, shard, nshards);
+  if (rc != WV_OK) return rc;
+  if (!poses || !patches || !intrinsics || !target || !weight || !lmbda || !ii || !jj || !kk || !workspace || !Sband || !y) return WV_EINVAL;
+  if (bs < 2 || bs > band_max_bs() || (reinterpret_cast<uintptr_t>(Sband) & 15) != 0) return WV_EINVAL;
+  return ba_global_build(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk, E, n_poses, n_patches, P, t0, t1,
+                         patches_est, mu, shard, nshards, build_plan, Sband, y, workspace, workspace_bytes, status, as_stream(stream), bs);
+}
+
+int wv_ba_band_solve(const float* Sband, const float* y, int n6, int bs, int damp, float* factors, float* dX, int* status,
+                     wv_stream_t stream) {
+  if (n6 < 0 || (n6 > 0 && (!Sband || !y || !factors || !dX))) return WV_EINVAL;
+  if ((reinterpret_cast<uintptr_t>(factors) & 15) != 0 || (reinterpret_cast<uintptr_t>(Sband) & 15) != 0) return WV_EINVAL;
+  return ba_band_solve(Sband, y, n6, bs, damp, factors, dX, status, as_stream(stream));
 }
 
 int wv_ba_global_damp(float* S, int n6, wv_stream_t stream) {

@@ -35,7 +35,8 @@ struct GArgs {
   const float* patches_est; float mu;
   int P, t0, N, n_poses;
   Plan p;
-  float* S;         // [6N][6N] row-major, lower triangle (diagonal blocks: their lower triangle)
+  float* S;         // element (r, c), r >= c, at S[r * ld + c]: dense [6N][6N] (ld = 6N) or the band layout of ba_band.cu
+  int ld;
   float* y;         // [6N]
   const float* dX;  // [N][6]
   float* dZ;        // [Mp_cap], indexed by the plan's patch rank
@@ -66,21 +67,21 @@ static constexpr size_t kBuildSmem = kEntryBytes + sizeof(float) * (kChunk * kWi
 __device__ __forceinline__ void red2(float* p, float x, float y) { atomicAdd(reinterpret_cast<float2*>(p), make_float2(x, y)); }
 
 // block (fa, fb) of S with fa >= fb += s A B^T, straight to HBM (fa == fb: lower triangle of the block only)
-__device__ __forceinline__ void red_block(float* S, int n6, int fa, int fb, const float* A, const float* B, float s) {
-  float* base = S + (size_t)(6 * fa) * n6 + 6 * fb;
+__device__ __forceinline__ void red_block(float* S, int ld, int fa, int fb, const float* A, const float* B, float s) {
+  float* base = S + (size_t)(6 * fa) * ld + 6 * fb;
   if (fa != fb) {
 #pragma unroll
     for (int r = 0; r < 6; r++) {
       const float ar = s * A[r];
-      red2(base + (size_t)r * n6, ar * B[0], ar * B[1]);
-      red2(base + (size_t)r * n6 + 2, ar * B[2], ar * B[3]);
-      red2(base + (size_t)r * n6 + 4, ar * B[4], ar * B[5]);
+      red2(base + (size_t)r * ld, ar * B[0], ar * B[1]);
+      red2(base + (size_t)r * ld + 2, ar * B[2], ar * B[3]);
+      red2(base + (size_t)r * ld + 4, ar * B[4], ar * B[5]);
     }
   } else {
 #pragma unroll
     for (int r = 0; r < 6; r++)
 #pragma unroll
-      for (int c = 0; c <= r; c++) atomicAdd(base + (size_t)r * n6 + c, s * A[r] * B[c]);
+      for (int c = 0; c <= r; c++) atomicAdd(base + (size_t)r * ld + c, s * A[r] * B[c]);
   }
 }
 
@@ -99,38 +100,38 @@ __device__ __forceinline__ void lane_acc_reset(LaneAcc& A, int fi, int fj) {
   for (int t = 0; t < 6; t++) A.vj[t] = 0.f;
 }
 
-__device__ __forceinline__ void lane_acc_flush(const LaneAcc& A, float* S, float* y, int N, int n6) {
+__device__ __forceinline__ void lane_acc_flush(const LaneAcc& A, float* S, float* y, int N, int ld) {
   const bool free_i = A.fi >= 0 && A.fi < N, free_j = A.fj >= 0 && A.fj < N;
   if (!free_j) return;
   {
-    float* b = S + (size_t)(6 * A.fj) * n6 + 6 * A.fj;
+    float* b = S + (size_t)(6 * A.fj) * ld + 6 * A.fj;
     int t = 0;
 #pragma unroll
     for (int p = 0; p < 6; p++) {
 #pragma unroll
-      for (int c = 0; c <= p; c++) atomicAdd(b + (size_t)p * n6 + c, A.JJ[t++]);
+      for (int c = 0; c <= p; c++) atomicAdd(b + (size_t)p * ld + c, A.JJ[t++]);
       atomicAdd(y + 6 * A.fj + p, A.vj[p]);
     }
   }
   if (!free_i) return;
   if (A.fi > A.fj) {
-    float* b = S + (size_t)(6 * A.fi) * n6 + 6 * A.fj;
+    float* b = S + (size_t)(6 * A.fi) * ld + 6 * A.fj;
 #pragma unroll
     for (int p = 0; p < 6; p++)
 #pragma unroll
-      for (int c = 0; c < 6; c += 2) red2(b + (size_t)p * n6 + c, -A.IJ[6 * p + c], -A.IJ[6 * p + c + 1]);
+      for (int c = 0; c < 6; c += 2) red2(b + (size_t)p * ld + c, -A.IJ[6 * p + c], -A.IJ[6 * p + c + 1]);
   } else if (A.fi < A.fj) {
-    float* b = S + (size_t)(6 * A.fj) * n6 + 6 * A.fi;
+    float* b = S + (size_t)(6 * A.fj) * ld + 6 * A.fi;
 #pragma unroll
     for (int c = 0; c < 6; c++)
 #pragma unroll
-      for (int p = 0; p < 6; p += 2) red2(b + (size_t)c * n6 + p, -A.IJ[6 * p + c], -A.IJ[6 * (p + 1) + c]);
+      for (int p = 0; p < 6; p += 2) red2(b + (size_t)c * ld + p, -A.IJ[6 * p + c], -A.IJ[6 * (p + 1) + c]);
   } else {
-    float* b = S + (size_t)(6 * A.fi) * n6 + 6 * A.fi;
+    float* b = S + (size_t)(6 * A.fi) * ld + 6 * A.fi;
 #pragma unroll
     for (int p = 0; p < 6; p++)
 #pragma unroll
-      for (int c = 0; c <= p; c++) atomicAdd(b + (size_t)p * n6 + c, -(A.IJ[6 * p + c] + A.IJ[6 * c + p]));
+      for (int c = 0; c <= p; c++) atomicAdd(b + (size_t)p * ld + c, -(A.IJ[6 * p + c] + A.IJ[6 * c + p]));
   }
 }
 
@@ -143,6 +144,7 @@ __global__ void __launch_bounds__(kGThreads) ba_global_kernel(GArgs a) {
   __shared__ int s_wb;
   __shared__ int perm[kGWarps][32];
   const int N = a.N, n6 = 6 * N;
+  const int ld = a.ld;  // row stride of S: n6 (dense) or the band layout's (ba_band.cu)
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int PP = a.P * a.P, ctr = (a.P / 2) * a.P + a.P / 2;
   const float fx = a.intr[0], fy = a.intr[1], cx = a.intr[2], cy = a.intr[3];  // row 0 only (ba_cuda.cu:232-238)
@@ -240,7 +242,7 @@ __global__ void __launch_bounds__(kGThreads) ba_global_kernel(GArgs a) {
         if (BUILD) {
           // ---- (j,j), (i,j), v_j: run-length accumulation in this lane
           if (act && (free_j || free_i)) {
-            if (acc.fi != fi || acc.fj != fj) { lane_acc_flush(acc, a.S, a.y, N, n6); lane_acc_reset(acc, fi, fj); }
+            if (acc.fi != fi || acc.fj != fj) { lane_acc_flush(acc, a.S, a.y, N, ld); lane_acc_reset(acc, fi, fj); }
             int t = 0;
 #pragma unroll
             for (int p = 0; p < 6; p++) {
@@ -260,7 +262,7 @@ __global__ void __launch_bounds__(kGThreads) ba_global_kernel(GArgs a) {
 #pragma unroll
               for (int c = 0; c <= p; c++) {
                 const float v = warp_sum(II[t]);
-                if (lane == t) atomicAdd(a.S + (size_t)(6 * acc_f0 + p) * n6 + 6 * acc_f0 + c, v);
+                if (lane == t) atomicAdd(a.S + (size_t)(6 * acc_f0 + p) * ld + 6 * acc_f0 + c, v);
                 II[t] = 0.f;
                 t++;
               }
@@ -281,8 +283,8 @@ __global__ void __launch_bounds__(kGThreads) ba_global_kernel(GArgs a) {
               }
             }
           } else if (free_i) {  // mixed source frames inside one chunk of lanes: per-edge atomics
-            red_block(a.S, n6, fi, fi, T.Ji[0], T.Ji[0], T.w[0]);
-            red_block(a.S, n6, fi, fi, T.Ji[1], T.Ji[1], T.w[1]);
+            red_block(a.S, ld, fi, fi, T.Ji[0], T.Ji[0], T.w[0]);
+            red_block(a.S, ld, fi, fi, T.Ji[1], T.Ji[1], T.w[1]);
 #pragma unroll
             for (int p = 0; p < 6; p++) atomicAdd(a.y + 6 * fi + p, -(T.w[0] * T.r[0] * T.Ji[0][p] + T.w[1] * T.r[1] * T.Ji[1][p]));
           }
@@ -358,9 +360,9 @@ __global__ void __launch_bounds__(kGThreads) ba_global_kernel(GArgs a) {
               for (int eb = lane; eb < L; eb += 32) {
                 const int fb = ef[eb];
                 const bool in_b = fb >= wb && fb < wb + kWinFrames;
-                if (fa > fb) red_block(a.S, n6, fa, fb, ev[ea], ev[eb], -q);
-                else if (fa < fb) { if (in_b) red_block(a.S, n6, fb, fa, ev[eb], ev[ea], -q); }  // (out, out) is visited from the other side
-                else red_block(a.S, n6, fa, fa, ev[ea], ev[eb], -q);
+                if (fa > fb) red_block(a.S, ld, fa, fb, ev[ea], ev[eb], -q);
+                else if (fa < fb) { if (in_b) red_block(a.S, ld, fb, fa, ev[eb], ev[ea], -q); }  // (out, out) is visited from the other side
+                else red_block(a.S, ld, fa, fa, ev[ea], ev[eb], -q);
               }
             }
           }
@@ -375,7 +377,7 @@ __global__ void __launch_bounds__(kGThreads) ba_global_kernel(GArgs a) {
     }
     if (BUILD) {
       // flush the run-length accumulators
-      lane_acc_flush(acc, a.S, a.y, N, n6);
+      lane_acc_flush(acc, a.S, a.y, N, ld);
       if (acc_f0 >= 0) {
         int t = 0;
 #pragma unroll
@@ -383,7 +385,7 @@ __global__ void __launch_bounds__(kGThreads) ba_global_kernel(GArgs a) {
 #pragma unroll
           for (int c = 0; c <= p; c++) {
             const float v = warp_sum(II[t]);
-            if (lane == t) atomicAdd(a.S + (size_t)(6 * acc_f0 + p) * n6 + 6 * acc_f0 + c, v);
+            if (lane == t) atomicAdd(a.S + (size_t)(6 * acc_f0 + p) * ld + 6 * acc_f0 + c, v);
             t++;
           }
           const float wv = warp_sum(vi[p]);
@@ -421,8 +423,8 @@ __global__ void __launch_bounds__(kGThreads) ba_global_kernel(GArgs a) {
         for (int i = 0; i < kTile; i++) {
           const int R = wb6 + tr * kTile + i;
           if (R >= n6) break;
-          float* grow = a.S + (size_t)R * n6 + wb6 + tc * kTile;
-          if (tr != tc && ((wb6 + tc * kTile) & 3) == 0 && (n6 & 3) == 0) {  // 16-B aligned rows: two vector REDs
+          float* grow = a.S + (size_t)R * ld + wb6 + tc * kTile;
+          if (tr != tc && ((wb6 + tc * kTile) & 3) == 0 && (ld & 3) == 0) {  // 16-B aligned rows: two vector REDs
             if (accT[i][0] != 0.f || accT[i][1] != 0.f || accT[i][2] != 0.f || accT[i][3] != 0.f)
               atomicAdd(reinterpret_cast<float4*>(grow), make_float4(accT[i][0], accT[i][1], accT[i][2], accT[i][3]));
             if (accT[i][4] != 0.f || accT[i][5] != 0.f || accT[i][6] != 0.f || accT[i][7] != 0.f)
@@ -475,6 +477,9 @@ __global__ void ba_global_retract_kernel(GArgs a) {
 
 // ---------------------------------------------------------------------------------------------------
 int plan_grid();  // ba_plan.cu
+// ba_band.cu: band layout of the reduced system for a half-width of `bs` frames
+int band_ld(int bs);
+size_t band_floats(int n6, int bs);
 
 size_t ba_global_workspace_bytes(int64_t E, int64_t n_patches) { return plan_bytes(E, n_patches, plan_grid()) + 1024; }
 
@@ -498,22 +503,61 @@ static int global_grid(int64_t n_patches_guess) {
 int ba_global_build(float* poses, float* patches, const float* intr, const float* target, const float* weight, const float* lmbda,
                     const int64_t* ii, const int64_t* jj, const int64_t* kk, int64_t E, int64_t n_poses, int64_t n_patches, int P,
                     int t0, int t1, const float* patches_est, float mu, int shard, int nshards, int build_plan, float* S, float* y,
-                    void* ws, size_t ws_bytes, int* status, cudaStream_t st) {
+                    void* ws, size_t ws_bytes, int* status, cudaStream_t st, int band_bs) {
   if (ws_bytes < ba_global_workspace_bytes(E, n_patches)) return WV_EWORKSPACE;
   GArgs a = make_gargs(poses, patches, intr, target, weight, lmbda, ii, jj, E, n_poses, n_patches, P, t0, t1, patches_est, mu, ws,
                        shard, nshards, status);
   const size_t n6 = 6 * (size_t)a.N;
+  // band_bs > 0: S is the band buffer of ba_band.cu: element (r, c), 0 <= r - c < ld, lives at S[r * ld + c]
+  const size_t s_floats = band_bs > 0 ? band_floats((int)n6, band_bs) : n6 * n6;
+  a.ld = band_bs > 0 ? band_ld(band_bs) : (int)n6;
   a.S = S; a.y = y;
   if (build_plan) {
     const int rc = plan_build(a.p, kk, jj, ii, n_poses, nullptr, nullptr, status, st);
     if (rc != WV_OK) return rc;
   }
   if (n6) {
-    WV_CUDA_TRY(cudaMemsetAsync(S, 0, n6 * n6 * sizeof(float), st));
+    WV_CUDA_TRY(cudaMemsetAsync(S, 0, s_floats * sizeof(float), st));
     WV_CUDA_TRY(cudaMemsetAsync(y, 0, n6 * sizeof(float), st));
   }
   WV_CUDA_TRY(cudaFuncSetAttribute(ba_global_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBuildSmem));
   ba_global_kernel<true><<<global_grid(std::min(E, n_patches)), kGThreads, kBuildSmem, st>>>(a);
+  WV_LAUNCH_CHECK();
+  return WV_OK;
+}
+
+// widest frame span of any patch's observations among the free poses (source frame included): the reduced system couples two
+// free poses only if some patch sees both, so S is block-banded with a half-width of `span` pose blocks.  One warp per patch.
+__global__ void __launch_bounds__(kGThreads) ba_global_span_kernel(GArgs a, int* out) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int Mp = a.p.hdr->Mp, N = a.N;
+  int worst = 0;
+  for (int r = blockIdx.x * kGWarps + warp; r < Mp; r += gridDim.x * kGWarps) {
+    const int off = a.p.seg_off[r], n = a.p.seg_off[r + 1] - off;
+    int lo = 1 << 30, hi = -1;
+    for (int t = lane; t < n; t += 32) {
+      const int e = a.p.eperm[off + t];
+      const long long fi = a.ii[e] - a.t0, fj = a.jj[e] - a.t0;
+      if (fi >= 0 && fi < N) { lo = min(lo, (int)fi); hi = max(hi, (int)fi); }
+      if (fj >= 0 && fj < N) { lo = min(lo, (int)fj); hi = max(hi, (int)fj); }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o)); hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o)); }
+    if (hi >= lo) worst = max(worst, hi - lo);
+  }
+  if (lane == 0 && worst > 0) atomicMax(out, worst);
+}
+
+int ba_global_span(const int64_t* ii, const int64_t* jj, const int64_t* kk, int64_t E, int64_t n_poses, int64_t n_patches, int t0, int t1,
+                   int build_plan, int* span_out, void* ws, size_t ws_bytes, int* status, cudaStream_t st) {
+  if (ws_bytes < ba_global_workspace_bytes(E, n_patches)) return WV_EWORKSPACE;
+  GArgs a = make_gargs(nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, ii, jj, E, n_poses, n_patches, 3, t0, t1, nullptr, 0.f, ws, 0, 1, status);
+  if (build_plan) {
+    const int rc = plan_build(a.p, kk, jj, ii, n_poses, nullptr, nullptr, status, st);
+    if (rc != WV_OK) return rc;
+  }
+  WV_CUDA_TRY(cudaMemsetAsync(span_out, 0, sizeof(int), st));
+  ba_global_span_kernel<<<global_grid(std::min(E, n_patches) / 4 + 1), kGThreads, 0, st>>>(a, span_out);
   WV_LAUNCH_CHECK();
   return WV_OK;
 }

@@ -101,6 +101,68 @@ torch::Tensor global_build(torch::Tensor poses, torch::Tensor patches, torch::Te
   return Sy;
 }
 
+// widest frame span of a patch's observations among the free poses (one host sync): decides band vs dense.  Builds the edge plan.
+int64_t global_span(torch::Tensor poses, torch::Tensor patches, torch::Tensor ii, torch::Tensor jj, torch::Tensor kk, int t0, int t1,
+                    bool build_plan) {
+  check_f32c(poses, "poses"); check_f32c(patches, "patches");
+  c10::cuda::CUDAGuard guard(poses.device());
+  torch::Tensor iic = idx(ii, "ii"), jjc = idx(jj, "jj"), kkc = idx(kk, "kk");
+  const int64_t E = iic.numel();
+  if (E == 0) return 0;
+  const int P = patches.size(-1);
+  const int64_t n_poses = poses.numel() / 7, n_patches = patches.numel() / (3 * P * P);
+  if (build_plan) plan_note(poses.device().index()) = PlanNote();  // the shared workspace now holds this call's plan
+  torch::Tensor ws = workspace(poses.device(), wv_ba_global_workspace_bytes(E, n_patches));
+  torch::Tensor out = torch::zeros({1}, torch::dtype(torch::kInt32).device(poses.device()));
+  check_rc(wv_ba_global_span(iic.data_ptr<int64_t>(), jjc.data_ptr<int64_t>(), kkc.data_ptr<int64_t>(), E, n_poses, n_patches, t0, t1,
+                             build_plan ? 1 : 0, out.data_ptr<int>(), ws.data_ptr(), (size_t)ws.numel(),
+                             status_word(poses.device()).data_ptr<int>(), current_stream()),
+           "cuda_ba.global_span");
+  return out.item<int>();
+}
+
+// half-width (frames) of the band path for a given span, or 0 when the dense path must be taken
+int64_t band_block(int64_t span) {
+  const int64_t bs = std::max<int64_t>(span, 2);
+  return bs <= wv_ba_band_max_bs() && !env_flag("WVB200_GLOBAL_DENSE") ? bs : 0;
+}
+
+// this shard's partial band buffer [band | y] (csrc/ba_band.cu); the edge plan must be in the workspace (global_span built it)
+torch::Tensor global_build_band(torch::Tensor poses, torch::Tensor patches, torch::Tensor intrinsics, torch::Tensor target,
+                                torch::Tensor weight, torch::Tensor lmbda, torch::Tensor ii, torch::Tensor jj, torch::Tensor kk, int t0,
+                                int t1, int shard, int nshards, int64_t bs, c10::optional<torch::Tensor> patches_est, double mu) {
+  c10::cuda::CUDAGuard guard(poses.device());
+  BAIn in = ba_inputs(poses, patches, intrinsics, target, weight, lmbda, ii, jj, kk, t0, t1, patches_est);
+  const int64_t n6 = 6 * (int64_t)(t1 - t0);
+  const int64_t nb = ((int64_t)wv_ba_band_floats((int)n6, (int)bs) + 3) / 4 * 4;   // y starts 16-byte aligned
+  torch::Tensor Sy = torch::empty({nb + n6}, poses.options());
+  if (in.E == 0) return Sy.zero_();
+  torch::Tensor ws = workspace(poses.device(), wv_ba_global_workspace_bytes(in.E, in.n_patches));
+  check_rc(wv_ba_global_build_band(poses.data_ptr<float>(), patches.data_ptr<float>(), intrinsics.data_ptr<float>(), in.tg.data_ptr<float>(),
+                                   in.wt.data_ptr<float>(), in.lm.data_ptr<float>(), in.ii.data_ptr<int64_t>(), in.jj.data_ptr<int64_t>(),
+                                   in.kk.data_ptr<int64_t>(), in.E, in.n_poses, in.n_patches, in.P, t0, t1, in.estp, (float)mu, shard,
+                                   nshards, 0, (int)bs, Sy.data_ptr<float>(), Sy.data_ptr<float>() + nb, ws.data_ptr(), (size_t)ws.numel(),
+                                   status_word(poses.device()).data_ptr<int>(), current_stream()),
+           "cuda_ba.global_build_band");
+  return Sy;
+}
+
+// damping + band Cholesky solve of the band buffer: dX [N, 6]
+torch::Tensor global_solve_band(torch::Tensor Sy, int n_free, int64_t bs) {
+  c10::cuda::CUDAGuard guard(Sy.device());
+  const int64_t n6 = 6 * (int64_t)n_free;
+  const int64_t nb = ((int64_t)wv_ba_band_floats((int)n6, (int)bs) + 3) / 4 * 4;
+  TORCH_CHECK(Sy.is_cuda() && Sy.scalar_type() == torch::kFloat && Sy.is_contiguous() && Sy.numel() == nb + n6,
+              "cuda_ba.global_solve_band: expected the flat [band | y] buffer of global_build_band");
+  torch::Tensor dX = torch::empty({n_free, 6}, Sy.options());
+  if (n6 == 0) return dX;
+  torch::Tensor F = torch::empty({(int64_t)wv_ba_band_factor_floats((int)n6, (int)bs)}, Sy.options());
+  check_rc(wv_ba_band_solve(Sy.data_ptr<float>(), Sy.data_ptr<float>() + nb, (int)n6, (int)bs, 1, F.data_ptr<float>(), dX.data_ptr<float>(),
+                            status_word(Sy.device()).data_ptr<int>(), current_stream()),
+           "cuda_ba.global_solve_band");
+  return dX;
+}
+
 // damping + the reference's own dense solve (ba_cuda.cu:517-523): returns dX [N, 6]
 torch::Tensor global_solve(torch::Tensor Sy, int n_free) {
   c10::cuda::CUDAGuard guard(Sy.device());
@@ -174,11 +236,13 @@ std::vector<torch::Tensor> ba_forward(torch::Tensor poses, torch::Tensor patches
     est = estc.data_ptr<float>();
   }
   if (E == 0 || iterations <= 0) return {};
-  if (t1 - t0 > 16) {  // global BA: dense reduced system in HBM, the reference's own dense solver
+  if (t1 - t0 > 16) {  // global BA: reduced system in HBM -- banded (band Cholesky, csrc/ba_band.cu) when the edge list allows, else dense
+    const int64_t bs = band_block(global_span(poses, patches, iic, jjc, kkc, t0, t1, true));
     for (int it = 0; it < iterations; it++) {
-      torch::Tensor Sy = global_build(poses, patches, intrinsics, tg, wt, lm, iic, jjc, kkc, t0, t1, 0, 1, it == 0, patches_est, mu);
+      torch::Tensor Sy = bs ? global_build_band(poses, patches, intrinsics, tg, wt, lm, iic, jjc, kkc, t0, t1, 0, 1, bs, patches_est, mu)
+                            : global_build(poses, patches, intrinsics, tg, wt, lm, iic, jjc, kkc, t0, t1, 0, 1, false, patches_est, mu);
       raise_on_status(poses.device(), "cuda_ba.forward");  // bad index / over-dense patch: say so before the solve trips over it
-      torch::Tensor dX = global_solve(Sy, t1 - t0);
+      torch::Tensor dX = bs ? global_solve_band(Sy, t1 - t0, bs) : global_solve(Sy, t1 - t0);
       Sy = torch::Tensor();
       torch::Tensor dZ = global_dz(poses, patches, intrinsics, tg, wt, lm, iic, jjc, kkc, t0, t1, 0, 1, dX, patches_est, mu);
       global_retract(poses, patches, E, t0, t1, dX, dZ);
@@ -379,6 +443,14 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
         py::arg("intrinsics"), py::arg("target"), py::arg("weight"), py::arg("lmbda"), py::arg("ii"), py::arg("jj"), py::arg("kk"),
         py::arg("t0"), py::arg("t1"), py::arg("shard") = 0, py::arg("nshards") = 1, py::arg("build_plan") = true,
         py::arg("patches_est") = py::none(), py::arg("mu") = 2.0);
+  m.def("global_span", &global_span, "global BA: widest frame span of a patch's observations among the free poses (builds the plan)",
+        py::arg("poses"), py::arg("patches"), py::arg("ii"), py::arg("jj"), py::arg("kk"), py::arg("t0"), py::arg("t1"), py::arg("build_plan") = true);
+  m.def("band_block", &band_block, "half-width (frames) of the band path for a span, 0 = dense path");
+  m.def("global_build_band", &global_build_band, "global BA: this shard's partial band buffer [band | y]", py::arg("poses"),
+        py::arg("patches"), py::arg("intrinsics"), py::arg("target"), py::arg("weight"), py::arg("lmbda"), py::arg("ii"), py::arg("jj"),
+        py::arg("kk"), py::arg("t0"), py::arg("t1"), py::arg("shard"), py::arg("nshards"), py::arg("bs"),
+        py::arg("patches_est") = py::none(), py::arg("mu") = 2.0);
+  m.def("global_solve_band", &global_solve_band, "global BA: damping + band Cholesky solve -> dX");
   m.def("global_solve", &global_solve, "global BA: damping + dense Cholesky solve -> dX");
   m.def("global_dz", &global_dz, "global BA: this shard's depth updates", py::arg("poses"), py::arg("patches"), py::arg("intrinsics"),
         py::arg("target"), py::arg("weight"), py::arg("lmbda"), py::arg("ii"), py::arg("jj"), py::arg("kk"), py::arg("t0"),
