@@ -11,283 +11,346 @@
 //
 // ba_band_factor_kernel: ONE CTA walks the chain, one step per pose p ("panel" = its 6 columns).  The live part of the matrix is
 // the lower triangle of a (bs + 1) x (bs + 1) window of 6x6 pose blocks; every block lives in the REGISTERS of one thread for its
-// whole life: warp w owns the block columns C == w (mod T), T = bs + 2, lane d owns block (C + d, C), lane 31 the right-hand
-// side of row C.  A step is
-//     (1) issue the global loads of the block row that enters the window (row p + bs + 1; damping applied to its diagonal block),
-//     (2) trailing update   A(R, C) -= Y(R, p) Y(C, p)^T   for the live blocks, Y(., p) read from shared memory,
-//     (3) the warp of column p + 1 -- whose blocks just got their last update -- factors its diagonal block in lane 0
-//         (6x6 Cholesky in registers), hands L to its other lanes through shared memory, which solve their sub-diagonal
-//         blocks Y(R, p + 1) L^T = A(R, p + 1), forward-substitutes its right-hand side, and publishes Y(., p + 1) (shared
-//         memory, double buffered) and the factor (global memory),
+// whole life: warp w < T owns the block columns C == w (mod T), T = bs + 2, and its lane d owns block (C + d, C); one more warp
+// (w == T) owns the right-hand side, lane l the rows R == l (mod T).  A step is
+//     (1) issue the global loads of the blocks that enter the window (one or two steps before their first use; the damping
+//         S_dd <- S_dd (1 + 1e-4) + 1 of ba_cuda.cu:517-518 is applied a step later, when the load has landed),
+//     (2) trailing update   A(R, C) -= Y(R, p) Y(C, p)^T   of the live blocks as packed fp32 FMAs (fma.rn.f32x2: the same two IEEE
+//         FMAs per instruction, half the issue slots -- the update phase is issue-bound), Y(., p) read from shared memory where it
+//         is kept twice: negated with every element doubled (the row operand, one 16-byte load = two ready pairs) and plain (the
+//         column operand, one address per warp: a broadcast),
+//     (3) the warp of column p + 1 -- whose blocks just got their last update -- factors its diagonal block (6x6 Cholesky in
+//         registers, rsqrt; every lane does it, interleaved with the solve of its own sub-diagonal block
+//         Y(R, p + 1) L^T = A(R, p + 1)) and publishes Y(., p + 1) (shared memory, double buffered); the warp that idles in the
+//         next step copies the panel from shared memory to the factor record in global memory,
+//     (r) the right-hand-side warp: z_p = L_pp^-1 y_p in the lane of row p, then y_R -= Y(R, p) z_p in the others,
 //     (4) ONE __syncthreads.
 // (3) overlaps the other warps' (2), so the factorisation of the diagonal block is off the critical path.
-// ba_band_backsolve_kernel: one warp, L^T x = z backwards, lane d reduces block (p + d, p); the next step's blocks are
-// prefetched.  The damping S_dd <- S_dd (1 + 1e-4) + 1 (ba_cuda.cu:517-518) is applied when a diagonal block is loaded.
+// ba_band_backsolve_kernel: one warp, L^T x = z backwards; see there.
+#include <cstdlib>
+
 #include "wv_common.cuh"
 
 namespace wv {
 
-static constexpr int kBandMaxBs = 26;   // T = 28 warps = 896 threads, 73 registers per thread
-static constexpr int kTileStride = 38;  // floats between transposed 6x6 tiles in shared memory (8-byte aligned, bank spread)
+static constexpr int kBandMaxBs = 25;   // T + 1 = 28 warps = 896 threads, 72 registers per thread
+static constexpr int kYStride = 36;     // floats between the transposed Y tiles in shared memory (9 float4: odd, so the lanes' 16-byte loads spread over the banks)
+static constexpr int kBackPrefetch = 6; // records in flight ahead of the back substitution
 
 int band_max_bs() { return kBandMaxBs; }
 int band_ld(int bs) { return (6 * (bs + 2) + 3) & ~3; }                       // > 6 bs + 5 + 3, multiple of 4 (vector REDs)
 size_t band_floats(int n6, int bs) { return (size_t)n6 * (size_t)(band_ld(bs) + 1) + 64; }
-// factor storage: per pose (bs + 2) tiles of 36 floats: [0] L_pp, [1..bs] Y(p + d, p), [bs + 1] the reciprocals of diag(L_pp); then z [n6]
-size_t band_factor_floats(int n6, int bs) { return (size_t)(n6 / 6) * (size_t)(bs + 2) * 36 + (size_t)n6 + 64; }
+// factor storage: per pose ONE record of (bs + 2) tiles of 36 floats: [0] L_pp, [1..bs] Y(p + d, p)^T, [bs + 1] = the reciprocals
+// of diag(L_pp) in floats 0..5 and z_p in floats 8..13
+size_t band_factor_floats(int n6, int bs) { return (size_t)(n6 / 6) * (size_t)(bs + 2) * 36 + 64; }
 
 struct BandArgs {
   const float* S;   // band buffer
   const float* y;   // [6N]
-  float* F;         // factor tiles
-  float* z;         // [6N] forward-substituted right-hand side
+  float* F;         // factor records
   float* dX;        // [6N]
   int N, bs, ld, damp;
   int* status;
+  int prio;         // 1: the publishing warp updates first, alone (named barrier 1).  WVB200_BAND_PRIO; measured slower, off
 };
 
-// in-place 6x6 Cholesky of the lower triangle of a (upper part ignored, zeroed on exit); rd = reciprocals of the diagonal of L.
-// rsqrtf (2 ulp) instead of sqrtf + division: this runs in ONE lane on the critical path of every step.  false on a bad pivot.
-__device__ __forceinline__ bool chol6(float (&a)[6][6], float (&rd)[6]) {
-  bool ok = true;
-#pragma unroll
-  for (int j = 0; j < 6; j++) {
-    float d = a[j][j];
-    if (!(d > 0.f)) { ok = false; d = 1.f; }
-    const float r = rsqrtf(d);
-    a[j][j] = d * r;
-    rd[j] = r;
-#pragma unroll
-    for (int i = j + 1; i < 6; i++) a[i][j] *= r;
-#pragma unroll
-    for (int k = j + 1; k < 6; k++)
-#pragma unroll
-      for (int i = k; i < 6; i++) a[i][k] = fmaf(-a[i][j], a[k][j], a[i][k]);
-  }
+
+// WV_BAND_TRACE (tools/band_trace.cu only): clock() stamps of the publishing warp's phases, one row of 8 per step
+#ifdef WV_BAND_TRACE
+__device__ unsigned g_band_trace[4096][8];
+#define WV_TR(step, slot, cond)                                                              \
+  do {                                                                                       \
+    if ((cond) && (step) >= 0 && (step) < 4096) g_band_trace[step][slot] = (unsigned)clock(); \
+  } while (0)
+#else
+#define WV_TR(step, slot, cond) do { } while (0)
+#endif
+
+// element (i, j) of a block held as float2 a[6][3]; i, j are compile-time under full unrolling
+#define WV_E(a, i, j) (((j) & 1) ? (a)[i][(j) >> 1].y : (a)[i][(j) >> 1].x)
+
+__device__ __forceinline__ float rsqrt_raw(float x) {   // one MUFU.RSQ: no denormal rescue (a pivot is >= 1 after the damping)
+  float r;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
+__global__ void __launch_bounds__(32 * (kBandMaxBs + 3), 1) ba_band_factor_kernel(BandArgs g) {
+  extern __shared__ __align__(16) float smem[];
+  const int bs = g.bs, T = bs + 2, N = g.N, ld = g.ld;
+  float* sY = smem;                               // [2][T][kYStride]: Y(R, p) transposed ([k][i]), slot R % T, double buffered over p
+  float* sL = sY + 2 * T * kYStride;              // [2][44]: L_qq (36) and the reciprocals of its diagonal (6)
+  float* sz = sL + 88;                            // [8]: z_p
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const size_t FP = (size_t)(bs + 2) * 36;
+  const int p0 = -1;                              // step -1 publishes column 0
+  int m = (w + 1) % T;                            // tile warps: (w - p) mod T, kept incrementally; column C = p + m
+  int ml = (lane + 1) % T;                        // rhs warp: the same for lane l
+  const int d = lane;
+  // every block column a tile warp owns is == w (mod T), so the shared-memory slots of a thread's two operands never change
+  const int slotC = w, slotR = (w + d >= T) ? w + d - T : w + d;
+  float2 a[6][3];                                 // tile warps: the block; rhs warp: row 0 holds the six right-hand-side values
+#define WV_Y(i) WV_E(a, 0, i)
 #pragma unroll
   for (int i = 0; i < 6; i++)
 #pragma unroll
-    for (int j = 0; j < 6; j++)
-      if (j > i) a[i][j] = 0.f;
-  return ok;
-}
-
-__global__ void __launch_bounds__(32 * (kBandMaxBs + 2), 1) ba_band_factor_kernel(BandArgs g) {
-  extern __shared__ float smem[];
-  const int bs = g.bs, T = bs + 2, N = g.N, ld = g.ld;
-  float* sYt = smem;                              // [2][T][kTileStride]: Y(R, p) transposed ([k][i]), slot R % T
-  float* sz = smem + 2 * T * kTileStride;         // [2][8]: z_p
-  float* sL = sz + 16;                            // [36 + 6]: L_qq and the reciprocals of its diagonal, for the lanes of the publishing warp
-  const int lane = threadIdx.x & 31, cm = threadIdx.x >> 5;
-  const int d = lane;
-  const bool is_tile = d <= bs, is_rhs = lane == 31;
-  const size_t FP = (size_t)(bs + 2) * 36;
-  // every block column this warp owns is == cm (mod T), so the shared-memory slots of this thread's rows never change
-  const int slotC = cm, slotR = (cm + d >= T) ? cm + d - T : cm + d;
-  float a[6][6];
-  float yv[6];
+    for (int j = 0; j < 3; j++) a[i][j] = make_float2(0.f, 0.f);
+  auto load_tile = [&](int C) {                   // block (C + d, C) of the band buffer.  A diagonal block's upper triangle gets whatever
+    const float* src = g.S + (size_t)(6 * (C + d)) * ld + 6 * C;   // lies next to the diagonal: the updates write it, nothing reads it
 #pragma unroll
-  for (int i = 0; i < 6; i++) {
-    yv[i] = 0.f;
+    for (int i = 0; i < 6; i++) {
+      const float2* row = reinterpret_cast<const float2*>(src + (size_t)i * ld);
+      a[i][0] = row[0]; a[i][1] = row[1]; a[i][2] = row[2];
+    }
+  };
+  auto damp_diag = [&]() {
 #pragma unroll
-    for (int j = 0; j < 6; j++) a[i][j] = 0.f;
+    for (int i = 0; i < 6; i++) WV_E(a, i, i) = WV_E(a, i, i) + (WV_E(a, i, i) * 1e-4f + 1.0f);
+  };
+  if (w < T) {                                    // tile warp w starts with column w
+    if (d <= bs && w + d < N) load_tile(w);
+    if (d == 0 && g.damp) damp_diag();
+  } else if (lane < T && lane < N) {              // rhs warp: rows 0..T-1
+#pragma unroll
+    for (int i = 0; i < 6; i++) WV_Y(i) = g.y[6 * lane + i];
   }
-  const int p0 = -(bs + 1);
-  int m = ((cm - p0) % T + T) % T;                // (cm - p) mod T, kept incrementally
 
   for (int p = p0; p < N; p++) {
-    // ---- (1) loads of the entering blocks: the diagonal block of row p + bs + 1, the other blocks of row p + bs + 2 (one step
-    //          before their first use, so that the load latency never meets the publishing warp) ---------------------------------
-    {
-      const int R = p + bs + 1 + (d > 0 ? 1 : 0);
-      if (is_tile && m == bs + 1 - d + (d > 0 ? 1 : 0) && R < N) {
-        const int C = R - d;
-        if (C >= 0) {
+    if (w < T) {
+      // ---- (1) the warp whose column was panel p - 1 is free: it loads its next column, p + T, whole -- a warp-uniform branch (a
+      //          load in SOME lane would put its destination registers on the scoreboard of the whole warp and stall the update),
+      //          two steps before the column's first use, which is the damping of its diagonal block --------------------------------
+      if (m == 0 && p >= 0) {
+        // ... after it has written its factor record to global memory for the back substitution -- from shared memory, where panel p
+        // stays valid through this step: the TRANSPOSED blocks Y(p + d, p)^T, and L_pp with the reciprocals of its diagonal
+        float* Fp = g.F + (size_t)p * FP;
+        if (d >= 1 && d <= bs && p + d < N) {
+          const float4* src = reinterpret_cast<const float4*>(sY + (size_t)((p & 1) * T + slotR) * kYStride);
+          float4* dst = reinterpret_cast<float4*>(Fp + (size_t)d * 36);
 #pragma unroll
-          for (int i = 0; i < 6; i++) {
-            const float2* row = reinterpret_cast<const float2*>(g.S + (size_t)(6 * R + i) * ld + 6 * C);
-            const float2 v0 = row[0], v1 = row[1], v2 = row[2];
-            a[i][0] = v0.x; a[i][1] = v0.y; a[i][2] = v1.x; a[i][3] = v1.y; a[i][4] = v2.x; a[i][5] = v2.y;
-          }
+          for (int t = 0; t < 9; t++) dst[t] = src[t];
+        } else if (d == 0 || d == 31) {
+          const float4* src = reinterpret_cast<const float4*>(sL + (p & 1) * 44);
+          float4* dst = reinterpret_cast<float4*>(Fp + (d == 0 ? 0 : (size_t)(bs + 1) * 36));
           if (d == 0) {
 #pragma unroll
-            for (int i = 0; i < 6; i++) {
-              if (g.damp) a[i][i] = a[i][i] + (a[i][i] * 1e-4f + 1.0f);
-#pragma unroll
-              for (int j = 0; j < 6; j++) if (j > i) a[i][j] = 0.f;
-            }
+            for (int t = 0; t < 9; t++) dst[t] = src[t];
+          } else {
+            const float4 r0 = src[9], r1 = src[10];
+            dst[0] = r0; dst[1] = make_float4(r1.x, r1.y, 0.f, 0.f);
           }
         }
+        if (d <= bs && p + T + d < N) load_tile(p + T);
       }
-      if (is_rhs && m == bs + 1) {
-        const int Ry = p + bs + 1;
+      if (d == 0 && m == bs && g.damp && p + m >= T) damp_diag();
+      // ---- (2) trailing update with panel p.  The warp that publishes in this step is the critical path (update -> factor + solve
+      //          -> publish -> barrier).  g.prio lets it update first, alone (named barrier 1 over the tile warps), with the others'
+      //          update hidden behind its factor + solve; measured (tools/band_trace.cu) that loses: 2.66 vs 2.21 us per step -----------
+      WV_TR(p, 0, m == 1 && lane == 0);
+      WV_TR(p, 6, m == 5 && lane == 0);
+      if (g.prio && m != 1) asm volatile("bar.sync 1, %0;" ::"r"(32 * T) : "memory");
+      if (p >= 0 && m >= 1 && d <= bs - m && p + m + d < N) {
+        const float4* YR = reinterpret_cast<const float4*>(sY + (size_t)((p & 1) * T + slotR) * kYStride);   // this lane's row
+        const float4* YC = reinterpret_cast<const float4*>(sY + (size_t)((p & 1) * T + slotC) * kYStride);   // the warp's column: a broadcast
 #pragma unroll
-        for (int i = 0; i < 6; i++) yv[i] = Ry < N ? g.y[6 * Ry + i] : 0.f;
-      }
-    }
-    // ---- (2) trailing update with panel p --------------------------------------------------------------------------------------
-    if (p >= 0) {
-      const float* Yb = sYt + (size_t)(p & 1) * T * kTileStride;
-      if (is_tile && m >= 1 && m <= bs - d) {
-        const int C = p + m, R = C + d;
-        if (R < N) {
-          const float* YR = Yb + slotR * kTileStride;
-          const float* YC = Yb + slotC * kTileStride;
+        for (int h = 0; h < 3; h++) {   // two k per round: 12 floats = 3 float4 of each operand
+          const float4 r0 = YR[3 * h], r1 = YR[3 * h + 1], r2 = YR[3 * h + 2];
+          const float4 c0 = YC[3 * h], c1 = YC[3 * h + 1], c2 = YC[3 * h + 2];
+          const float ra[6] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y}, rb[6] = {r1.z, r1.w, r2.x, r2.y, r2.z, r2.w};
+          const float2 ca[3] = {make_float2(c0.x, c0.y), make_float2(c0.z, c0.w), make_float2(c1.x, c1.y)};
+          const float2 cb[3] = {make_float2(c1.z, c1.w), make_float2(c2.x, c2.y), make_float2(c2.z, c2.w)};
 #pragma unroll
-          for (int k = 0; k < 6; k++) {
-            const float2 r0 = *reinterpret_cast<const float2*>(YR + 6 * k), r1 = *reinterpret_cast<const float2*>(YR + 6 * k + 2),
-                         r2 = *reinterpret_cast<const float2*>(YR + 6 * k + 4);
-            const float2 c0 = *reinterpret_cast<const float2*>(YC + 6 * k), c1 = *reinterpret_cast<const float2*>(YC + 6 * k + 2),
-                         c2 = *reinterpret_cast<const float2*>(YC + 6 * k + 4);
-            const float yr[6] = {r0.x, r0.y, r1.x, r1.y, r2.x, r2.y};
-            const float yc[6] = {c0.x, c0.y, c1.x, c1.y, c2.x, c2.y};
+          for (int i = 0; i < 6; i++)   // make_float2(-x, -x): FFMA2 takes a negated scalar operand (-R.F32), no extra instruction
 #pragma unroll
-            for (int i = 0; i < 6; i++)
+            for (int j = 0; j < 3; j++) a[i][j] = __ffma2_rn(make_float2(-ra[i], -ra[i]), ca[j], a[i][j]);
 #pragma unroll
-              for (int j = 0; j < 6; j++) a[i][j] = fmaf(-yr[i], yc[j], a[i][j]);
-          }
+          for (int i = 0; i < 6; i++)
+#pragma unroll
+            for (int j = 0; j < 3; j++) a[i][j] = __ffma2_rn(make_float2(-rb[i], -rb[i]), cb[j], a[i][j]);
         }
       }
-      if (is_rhs && m >= 1 && m <= bs) {
-        const int R = p + m;
-        if (R < N) {
-          const float* YR = Yb + slotC * kTileStride;
-          const float* zp = sz + (p & 1) * 8;
+      WV_TR(p, 1, m == 1 && lane == 0);
+      WV_TR(p, 7, m == 5 && lane == 0);
+      if (g.prio && m == 1) asm volatile("bar.arrive 1, %0;" ::"r"(32 * T) : "memory");
+      // ---- (3) the warp of column q = p + 1: factor, solve, publish ----------------------------------------------------------------
+      if (m == 1 && p + 1 >= 0 && p + 1 < N) {
+        const int q = p + 1;
+        float* L = sL + (q & 1) * 44;
+        // lane 0 hands its diagonal block to the whole warp, and EVERY lane factors it: in lockstep that costs what lane 0 alone
+        // would, and each lane's own forward substitution  Y L^T = A  (column j needs row j of L, final after factor step j) fills
+        // the latency bubbles of the factorisation's serial chain -- instead of waiting for it to end.
+        if (d == 0) {
 #pragma unroll
-          for (int k = 0; k < 6; k++) {
-            const float zk = zp[k];
+          for (int i = 0; i < 6; i++)
 #pragma unroll
-            for (int i = 0; i < 6; i++) yv[i] = fmaf(-YR[6 * k + i], zk, yv[i]);
+            for (int j = 0; j < 3; j++) *reinterpret_cast<float2*>(L + 6 * i + 2 * j) = a[i][j];
+        }
+        __syncwarp();
+        float2 gd[6][3];
+        {
+          const float4* L4 = reinterpret_cast<const float4*>(L);
+#pragma unroll
+          for (int t = 0; t < 9; t++) {
+            const float4 v = L4[t];
+            gd[(2 * t) / 3][(2 * t) % 3] = make_float2(v.x, v.y);
+            gd[(2 * t + 1) / 3][(2 * t + 1) % 3] = make_float2(v.z, v.w);
           }
         }
-      }
-    }
-    // ---- (3) the warp of column q = p + 1: factor, scale, publish -----------------------------------------------------------------
-    if (m == 1 && p + 1 >= 0 && p + 1 < N) {
-      const int q = p + 1;
-      if (d == 0) {
+        __syncwarp();   // lane 0 overwrites the buffer with L below
+        float dmin = WV_E(gd, 0, 0);
         float rd[6];
-        if (!chol6(a, rd)) set_status(g.status, WV_STATUS_NOT_SPD);
 #pragma unroll
-        for (int i = 0; i < 6; i++) {
-          sL[36 + i] = rd[i];
+        for (int j = 0; j < 6; j++) {
+          const float dj = WV_E(gd, j, j);
+          dmin = fminf(dmin, dj);
+          const float r = rsqrt_raw(dj);
+          rd[j] = r;
+          WV_E(gd, j, j) = dj * r;
 #pragma unroll
-          for (int j = 0; j < 6; j++) sL[6 * i + j] = a[i][j];
+          for (int i = j + 1; i < 6; i++) WV_E(gd, i, j) *= r;
+#pragma unroll
+          for (int k = j + 1; k < 6; k++)
+#pragma unroll
+            for (int i = k; i < 6; i++) WV_E(gd, i, k) = fmaf(-WV_E(gd, i, j), WV_E(gd, k, j), WV_E(gd, i, k));
+          // column j of this lane's block:  Y[i][j] = (A[i][j] - sum_{k < j} Y[i][k] L[j][k]) / L[j][j]   (lane 0's result is not used)
+#pragma unroll
+          for (int k = 0; k < j; k++)
+#pragma unroll
+            for (int i = 0; i < 6; i++) WV_E(a, i, j) = fmaf(-WV_E(a, i, k), WV_E(gd, j, k), WV_E(a, i, j));
+#pragma unroll
+          for (int i = 0; i < 6; i++) WV_E(a, i, j) *= r;
+        }
+        WV_TR(p, 2, lane == 0);
+        if (d == 0) {   // L_qq and the reciprocals of its diagonal: for the right-hand-side warp and the factor record (next step)
+          if (!(dmin > 0.f)) set_status(g.status, WV_STATUS_NOT_SPD);   // a non-positive pivot (or NaN)
+#define WV_LZ(f) ((f) % 6 <= (f) / 6 ? WV_E(gd, (f) / 6, (f) % 6) : 0.f)   /* flat element f of L, zero above the diagonal */
+          float4* L4 = reinterpret_cast<float4*>(L);
+#pragma unroll
+          for (int t = 0; t < 9; t++) L4[t] = make_float4(WV_LZ(4 * t), WV_LZ(4 * t + 1), WV_LZ(4 * t + 2), WV_LZ(4 * t + 3));
+          L4[9] = make_float4(rd[0], rd[1], rd[2], rd[3]);
+          L4[10] = make_float4(rd[4], rd[5], 0.f, 0.f);
+#undef WV_LZ
+        }
+        WV_TR(p, 3, lane == 1);
+        if (d >= 1 && d <= bs && q + d < N) {
+          float4* Yt = reinterpret_cast<float4*>(sY + (size_t)((q & 1) * T + slotR) * kYStride);   // transposed: [k][i] = Y[i][k]
+#pragma unroll
+          for (int t = 0; t < 9; t++)
+            Yt[t] = make_float4(WV_E(a, (4 * t) % 6, (4 * t) / 6), WV_E(a, (4 * t + 1) % 6, (4 * t + 1) / 6),
+                                WV_E(a, (4 * t + 2) % 6, (4 * t + 2) / 6), WV_E(a, (4 * t + 3) % 6, (4 * t + 3) / 6));
         }
       }
-      __syncwarp();
-      const int R = q + d;
-      float* Fq = g.F + (size_t)q * FP;
-      if (is_tile && R < N) {
-        if (d > 0) {   // Y L^T = A by forward substitution along each row:  Y[i][j] = (A[i][j] - sum_{k < j} Y[i][k] L[j][k]) / L[j][j]
-#pragma unroll
-          for (int j = 0; j < 6; j++) {
-#pragma unroll
-            for (int k = 0; k < j; k++) {
-              const float c = sL[6 * j + k];
-#pragma unroll
-              for (int i = 0; i < 6; i++) a[i][j] = fmaf(-a[i][k], c, a[i][j]);
-            }
-            const float r = sL[36 + j];
-#pragma unroll
-            for (int i = 0; i < 6; i++) a[i][j] *= r;
-          }
-          float* Yt = sYt + (size_t)(q & 1) * T * kTileStride + slotR * kTileStride;
-#pragma unroll
-          for (int k = 0; k < 6; k++)
-#pragma unroll
-            for (int i = 0; i < 6; i++) Yt[6 * k + i] = a[i][k];
-        }
-        float4* dst = reinterpret_cast<float4*>(Fq + (size_t)d * 36);
-#pragma unroll
-        for (int t = 0; t < 9; t++) {
-          const int e = 4 * t;
-          dst[t] = make_float4(a[e / 6][e % 6], a[(e + 1) / 6][(e + 1) % 6], a[(e + 2) / 6][(e + 2) % 6], a[(e + 3) / 6][(e + 3) % 6]);
-        }
-        if (d == 0) {   // reciprocals of the diagonal, for the back substitution
-          float4* di = reinterpret_cast<float4*>(Fq + (size_t)(bs + 1) * 36);
-          di[0] = make_float4(sL[36], sL[37], sL[38], sL[39]);
-          di[1] = make_float4(sL[40], sL[41], 0.f, 0.f);
-        }
-      }
-      if (is_rhs) {   // L z_q = y_q
-        float* zq = sz + (q & 1) * 8;
+      WV_TR(p, 4, m == 1 && lane == 1);
+      m = (m == 0) ? T - 1 : m - 1;
+    } else if (p >= 0) {
+      // ---- (r) right-hand side: lane l holds y of the rows == l (mod T) ------------------------------------------------------------
+      if (lane < T && ml == 0) {   // row p: every update is in; L z_p = y_p
+        const float* L = sL + (p & 1) * 44;
+        float* zg = g.F + (size_t)p * FP + (size_t)(bs + 1) * 36 + 8;
         float zz[6];
 #pragma unroll
         for (int i = 0; i < 6; i++) {
-          float s = yv[i];
+          float s = WV_Y(i);
 #pragma unroll
-          for (int k = 0; k < i; k++) s = fmaf(-sL[6 * i + k], zz[k], s);
-          zz[i] = s * sL[36 + i];
-          zq[i] = zz[i];
-          g.z[6 * q + i] = zz[i];
+          for (int k = 0; k < i; k++) s = fmaf(-L[6 * i + k], zz[k], s);
+          zz[i] = s * L[36 + i];
+          sz[i] = zz[i];
+          zg[i] = zz[i];
+        }
+        const int Rn = p + T;      // this lane's next row
+#pragma unroll
+        for (int i = 0; i < 6; i++) WV_Y(i) = Rn < N ? g.y[6 * Rn + i] : 0.f;
+      }
+      __syncwarp();
+      if (lane < T && ml >= 1 && ml <= bs && p + ml < N) {
+        const float4* YC = reinterpret_cast<const float4*>(sY + (size_t)((p & 1) * T + lane) * kYStride);
+        float yt[36];
+#pragma unroll
+        for (int t = 0; t < 9; t++) { const float4 v = YC[t]; yt[4 * t] = v.x; yt[4 * t + 1] = v.y; yt[4 * t + 2] = v.z; yt[4 * t + 3] = v.w; }
+#pragma unroll
+        for (int k = 0; k < 6; k++) {
+          const float zk = sz[k];
+#pragma unroll
+          for (int i = 0; i < 6; i++) WV_Y(i) = fmaf(-yt[6 * k + i], zk, WV_Y(i));
         }
       }
     }
+    if (w == T) ml = (ml == 0) ? T - 1 : ml - 1;
+    WV_TR(p, 5, w == T && lane == 0);
     __syncthreads();
-    m = (m == 0) ? T - 1 : m - 1;
   }
 }
 
-// L^T x = z, backwards, by one warp: lane d = 1..bs holds block Y(p + d, p), lane 0 holds L_pp and (next) the reciprocals of its diagonal; the blocks of step p - 1
-// are loaded while step p is reduced.
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// L^T x = z, backwards, by one warp, "push" style: when x_R is known (lane 0: six-step substitution with L_RR), every lane d adds
+// Y(R, R - d)^T x_R to the running sum of pose R - d that it carries, and the sums move down one lane -- so that lane 0 holds the
+// complete sum of pose R - 1 when the next step begins.  The chain of a step is substitution -> 6 shuffles -> 36 FMAs -> 6 shuffles;
+// no reduction tree.  The factor records (one contiguous run of (bs + 2) * 36 floats per pose) stream through a cp.async ring in
+// shared memory that holds the bs + 1 records a step reads plus kBackPrefetch in flight.
 __global__ void __launch_bounds__(32, 1) ba_band_backsolve_kernel(BandArgs g) {
-  __shared__ float sx[kBandMaxBs + 2][8];
-  const int bs = g.bs, T = bs + 2, N = g.N, d = threadIdx.x;
-  const size_t FP = (size_t)(bs + 2) * 36;
-  float cur[36], nxt[36], zc[6], zn[6], rc[6], rn[6];
-  auto fetch = [&](int p, float* t, float* zz, float* rr) {
-    if (d <= bs && (d == 0 || p + d < N)) {
-      const float4* src = reinterpret_cast<const float4*>(g.F + (size_t)p * FP + (size_t)d * 36);
-#pragma unroll
-      for (int q = 0; q < 9; q++) { const float4 v = src[q]; t[4 * q] = v.x; t[4 * q + 1] = v.y; t[4 * q + 2] = v.z; t[4 * q + 3] = v.w; }
+  extern __shared__ __align__(16) float smem[];
+  const int bs = g.bs, N = g.N, d = threadIdx.x;
+  const int FP = (bs + 2) * 36, FP4 = FP / 4, RING = bs + 2 + kBackPrefetch;
+  float* ring = smem;                                   // [RING][FP], record of pose q in slot q % RING
+  auto issue = [&](int pose) {
+    if (pose >= 0) {
+      const float4* src = reinterpret_cast<const float4*>(g.F + (size_t)pose * FP);
+      float4* dst = reinterpret_cast<float4*>(ring + (size_t)(pose % RING) * FP);
+      for (int t = d; t < FP4; t += 32) cp_async16(dst + t, src + t);
     }
-    if (d == 0) {
-      const float4* rs = reinterpret_cast<const float4*>(g.F + (size_t)p * FP + (size_t)(bs + 1) * 36);
-      const float4 r0 = rs[0], r1 = rs[1];
-      rr[0] = r0.x; rr[1] = r0.y; rr[2] = r0.z; rr[3] = r0.w; rr[4] = r1.x; rr[5] = r1.y;
-#pragma unroll
-      for (int i = 0; i < 6; i++) zz[i] = g.z[6 * p + i];
-    }
+    cp_async_commit();                                  // an empty group keeps the count uniform
   };
+  for (int s = 0; s <= bs + kBackPrefetch; s++) issue(N - 1 - s);
+  float acc[6];
 #pragma unroll
-  for (int i = 0; i < 36; i++) { cur[i] = 0.f; nxt[i] = 0.f; }
+  for (int j = 0; j < 6; j++) acc[j] = 0.f;
+  const bool tile_lane = d >= 1 && d <= bs;
+  int slot0 = (N - 1) % RING;                           // R % RING
+  int slotd = ((N - 1 - d) % RING + RING) % RING;       // (R - d) % RING
+  for (int R = N - 1; R >= 0; R--) {
+    cp_async_wait<kBackPrefetch>();                     // record R - bs (and every later one) has landed
+    __syncwarp();
+    issue(R - bs - kBackPrefetch - 1);                  // into the slot of pose R + 1, which nobody reads any more
+    const bool act = tile_lane && R - d >= 0;
+    float yt[36];                                       // Y(R, R - d)^T: [j][i]
+    if (act) {
+      const float4* t4 = reinterpret_cast<const float4*>(ring + (size_t)slotd * FP + d * 36);
 #pragma unroll
-  for (int i = 0; i < 6; i++) { zc[i] = 0.f; zn[i] = 0.f; rc[i] = 0.f; rn[i] = 0.f; }
-  if (N > 0) fetch(N - 1, cur, zc, rc);
-  for (int p = N - 1; p >= 0; p--) {
-    if (p > 0) fetch(p - 1, nxt, zn, rn);
-    float part[6];
-#pragma unroll
-    for (int j = 0; j < 6; j++) part[j] = 0.f;
-    if (d >= 1 && d <= bs && p + d < N) {
-      const float* xR = sx[(p + d) % T];
-#pragma unroll
-      for (int i = 0; i < 6; i++) {
-        const float xi = xR[i];
-#pragma unroll
-        for (int j = 0; j < 6; j++) part[j] = fmaf(cur[6 * i + j], xi, part[j]);
-      }
+      for (int q = 0; q < 9; q++) { const float4 v = t4[q]; yt[4 * q] = v.x; yt[4 * q + 1] = v.y; yt[4 * q + 2] = v.z; yt[4 * q + 3] = v.w; }
     }
+    float x[6];
 #pragma unroll
-    for (int j = 0; j < 6; j++) part[j] = warp_sum(part[j]);
-    if (d == 0) {   // L_pp^T x_p = z_p - sum:  x[k] = (rhs[k] - sum_{j > k} L[j][k] x[j]) / L[k][k], k descending
-      float x[6];
+    for (int k = 0; k < 6; k++) x[k] = 0.f;
+    if (d == 0) {   // L_RR^T x_R = z_R - sum:  x[k] = (rhs[k] - sum_{j > k} L[j][k] x[j]) / L[k][k], k descending
+      const float* L = ring + (size_t)slot0 * FP;
+      const float* rz = L + (bs + 1) * 36;              // [0..5] reciprocals of the diagonal, [8..13] z_R
 #pragma unroll
       for (int k = 5; k >= 0; k--) {
-        float s = zc[k] - part[k];
+        float s = rz[8 + k] - acc[k];
 #pragma unroll
-        for (int j = k + 1; j < 6; j++) s = fmaf(-cur[6 * j + k], x[j], s);
-        x[k] = s * rc[k];
-        sx[p % T][k] = x[k];
-        g.dX[6 * p + k] = x[k];
+        for (int j = k + 1; j < 6; j++) s = fmaf(-L[6 * j + k], x[j], s);
+        x[k] = s * rz[k];
+        g.dX[6 * R + k] = x[k];
       }
     }
-    __syncwarp();
 #pragma unroll
-    for (int i = 0; i < 36; i++) cur[i] = nxt[i];
+    for (int k = 0; k < 6; k++) x[k] = __shfl_sync(0xffffffffu, x[k], 0);
+    if (act) {
 #pragma unroll
-    for (int i = 0; i < 6; i++) { zc[i] = zn[i]; rc[i] = rn[i]; }
+      for (int j = 0; j < 6; j++)
+#pragma unroll
+        for (int i = 0; i < 6; i++) acc[j] = fmaf(yt[6 * j + i], x[i], acc[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < 6; j++) acc[j] = __shfl_down_sync(0xffffffffu, acc[j], 1);   // lanes > bs carry zeros
+    slot0 = slot0 == 0 ? RING - 1 : slot0 - 1;
+    slotd = slotd == 0 ? RING - 1 : slotd - 1;
   }
 }
 
@@ -297,11 +360,14 @@ int ba_band_solve(const float* S, const float* y, int n6, int bs, int damp, floa
   if (n6 <= 0) return WV_OK;
   if (bs < 2 || bs > kBandMaxBs || n6 % 6 != 0) return WV_EINVAL;
   const int N = n6 / 6, T = bs + 2;
-  BandArgs a{S, y, F, F + (size_t)N * (size_t)(bs + 2) * 36, dX, N, bs, band_ld(bs), damp, status};
-  const size_t smem = sizeof(float) * (size_t)(2 * T * kTileStride + 16 + 44);
-  ba_band_factor_kernel<<<1, 32 * T, smem, st>>>(a);
+  static const int prio = [] { const char* e = getenv("WVB200_BAND_PRIO"); return e ? atoi(e) : 0; }();
+  BandArgs a{S, y, F, dX, N, bs, band_ld(bs), damp, status, prio};
+  const size_t smem = sizeof(float) * (size_t)(2 * T * kYStride + 88 + 8);
+  ba_band_factor_kernel<<<1, 32 * (T + 1), smem, st>>>(a);
   WV_LAUNCH_CHECK();
-  ba_band_backsolve_kernel<<<1, 32, 0, st>>>(a);
+  const size_t smem_b = sizeof(float) * (size_t)(bs + 2 + kBackPrefetch) * T * 36;   // 128 KB at bs = 25
+  WV_CUDA_TRY(cudaFuncSetAttribute(ba_band_backsolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_b));
+  ba_band_backsolve_kernel<<<1, 32, smem_b, st>>>(a);
   WV_LAUNCH_CHECK();
   return WV_OK;
 }
