@@ -25,7 +25,7 @@ def syn():
 def golden():
     import numpy as np
     d = os.path.join(ROOT, "tests", "golden")
-    return {k: np.load(os.path.join(d, k + ".npz")) for k in ("corr_ref", "ba_ref", "pyba_ref", "pops_ref")}
+    return {k: np.load(os.path.join(d, k + ".npz")) for k in ("corr_ref", "ba_ref", "pyba_ref", "pops_ref", "ba_loop_ref")}
 
 
 @pytest.fixture(scope="session")

@@ -131,6 +131,24 @@ def test_ba_matches_reference(golden, name, tag):
     assert np.array_equal(patches[:, 2], np.broadcast_to(patches[:, 2, :1, :1], patches[:, 2].shape))
 
 
+@pytest.mark.parametrize("name", ["lc257", "lc40", "lc1"])
+def test_ba_loop_closure_call_shape_matches_reference(golden, name):
+    """fastba.BA as dpvo/loop_closure/long_term.py:104-127 calls it (3 fixed poses, t0 = t1 = 3, 6 iterations, lmbda 1e-3, two edges
+    per keypoint with kk = arange(n).repeat(2) -- NOT grouped by patch --, ii == 1, jj in {0, 2}, full-resolution intrinsics):
+    goldens from the reference's own ba_cuda.cu (oracle/make_golden_loop.py).  Structure only: poses must come back bit for bit."""
+    g = golden["ba_loop_ref"]
+    s = {k: g[f"{name}_in_{k}"] for k in ("poses", "patches", "intrinsics", "target", "weight", "lmbda", "ii", "jj", "kk")}
+    poses, patches = run_ba(s, 3, 3, 6)
+    assert np.array_equal(poses, s["poses"])
+    rd = g[f"{name}_patches"]
+    # six Gauss-Newton steps on a 1-D problem per point: fp32 round-off only (stated: 1e-4 relative inverse depth)
+    assert np.abs(patches[:, 2] - rd[:, 2]).max() < 1e-4 * max(1.0, np.abs(rd[:, 2]).max())
+    assert np.array_equal(patches[:, :2], rd[:, :2])
+    assert np.array_equal(patches[:, 2], np.broadcast_to(patches[:, 2, :1, :1], patches[:, 2].shape))
+    poses2, patches2 = run_ba(s, 3, 3, 6)
+    assert np.array_equal(patches, patches2)                              # deterministic
+
+
 @pytest.mark.parametrize("M,edges", [(96, "tracker"), (32, "all")])
 def test_ba_full_size_vs_oracle_and_deterministic(syn, M, edges):
     n = 40 if edges == "tracker" else 10

@@ -57,6 +57,25 @@ def test_ba_matches_reference(golden, name, tag, mode):
     assert np.array_equal(o["patches"][:, :2], g[f"{name}_{tag}_patches"][:, :2])
 
 
+LOOP_KEYS = ("poses", "patches", "intrinsics", "target", "weight", "lmbda", "ii", "jj", "kk")
+
+
+@pytest.mark.parametrize("name", ["lc257", "lc40", "lc1"])
+@pytest.mark.parametrize("mode", [oracle.F32, oracle.F64])
+def test_ba_loop_closure_call_shape_matches_reference(golden, name, mode):
+    """fastba.BA as dpvo/loop_closure/long_term.py:104-127 calls it: 3 fixed poses (t0 = t1 = 3: structure only), kk = arange(n).repeat(2)
+    (not grouped by patch), ii == 1, jj in {0, 2}, lmbda 1e-3, 6 iterations; goldens = the reference's own ba_cuda.cu (oracle/make_golden_loop.py)"""
+    g = golden["ba_loop_ref"]
+    i = {k: g[f"{name}_in_{k}"] for k in LOOP_KEYS}
+    assert np.array_equal(i["kk"], np.tile(np.arange(len(i["kk"]) // 2), 2)) and set(i["ii"]) == {1} and set(i["jj"]) <= {0, 2}
+    o = oracle.ba_forward(**i, t0=3, t1=3, iterations=6, mode=mode)
+    assert o["status"] == 0
+    assert np.array_equal(o["poses"], i["poses"])                         # no free pose
+    ref_d = g[f"{name}_patches"][:, 2, 0, 0]
+    assert np.abs(o["patches"][:, 2, 0, 0] - ref_d).max() < 1e-4 * max(1.0, np.abs(ref_d).max())
+    assert np.array_equal(o["patches"][:, :2], g[f"{name}_patches"][:, :2])
+
+
 @pytest.mark.parametrize("name", ["win", "trk", "off"])
 def test_reproject_and_neighbors_match_reference(golden, name):
     g = golden["ba_ref"]

@@ -39,7 +39,7 @@ static constexpr int kBackPrefetch = 6; // records in flight ahead of the back s
 
 int band_max_bs() { return kBandMaxBs; }
 int band_ld(int bs) { return (6 * (bs + 2) + 3) & ~3; }                       // > 6 bs + 5 + 3, multiple of 4 (vector REDs)
-size_t band_floats(int n6, int bs) { return (size_t)n6 * (size_t)(band_ld(bs) + 1) + 64; }
+size_t band_floats(int n6, int bs) { return ((size_t)n6 * (size_t)(band_ld(bs) + 1) + 64 + 3) & ~(size_t)3; }   // multiple of 4: y behind it stays 16-byte aligned
 // factor storage: per pose ONE record of (bs + 2) tiles of 36 floats: [0] L_pp, [1..bs] Y(p + d, p)^T, [bs + 1] = the reciprocals
 // of diag(L_pp) in floats 0..5 and z_p in floats 8..13
 size_t band_factor_floats(int n6, int bs) { return (size_t)(n6 / 6) * (size_t)(bs + 2) * 36 + 64; }
