@@ -262,6 +262,55 @@ def test_ba_sharded_host_logic_gloo_two_ranks(band):
         assert [c[1:] for c in res[3] if c[0] == "dz"] == [(rank, 2), (rank, 2)]
 
 
+@pytest.mark.parametrize("n,loops,freen", [(2048, 24, -1), (700, 5, 500), (40, 0, -1)])
+def test_solve_system_at_pose_graph_scale_vs_sparse_fp64(n, loops, freen, ref_modules):
+    """a pose graph of n frames: the chain plus `loops` long-range edges (one of them 0 <-> n - 1), the size at which the dense
+    (7n)^2 matrix of round 1 would have been 1.6 GB.  The entry point keeps the system in skyline storage; checked against scipy's sparse
+    fp64 solve of the same normal equations and -- where oracle/_ref exists -- against the reference's own Eigen-based solve_system"""
+    import scipy.sparse as sp
+    import scipy.sparse.linalg as spl
+    rng = np.random.default_rng(n)
+    ii = np.arange(n - 1, dtype=np.int64); jj = ii + 1
+    if loops:
+        li = rng.integers(0, n // 2, loops); lj = li + rng.integers(n // 4, n // 2, loops)
+        li[0], lj[0] = 0, n - 1
+        ii, jj = np.concatenate([ii, li]), np.concatenate([jj, lj])
+        flip = rng.random(len(ii)) < 0.3                      # edge direction is arbitrary in the reference
+        ii, jj = np.where(flip, jj, ii).astype(np.int64), np.where(flip, ii, jj).astype(np.int64)
+    r = len(ii)
+    Ji = (np.eye(7)[None] + 0.1 * rng.standard_normal((r, 7, 7))).astype(np.float32)
+    Jj = (-np.eye(7)[None] + 0.1 * rng.standard_normal((r, 7, 7))).astype(np.float32)
+    res = rng.standard_normal((r, 7)).astype(np.float32)
+    ep, lm = 1e-4, 1e-4
+    lib = _pkg().capi()
+    vp = lambda a: a.ctypes.data_as(ctypes.c_void_p)  # noqa: E731
+    f = lib.wv_solve_system_host
+    f.argtypes = [ctypes.c_void_p] * 5 + [ctypes.c_int64, ctypes.c_float, ctypes.c_float, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
+    nn = ctypes.c_int64(0)
+    delta = np.zeros((n, 7), np.float32)
+    assert f(vp(Ji), vp(Jj), vp(ii), vp(jj), vp(res), r, ep, lm, freen, vp(delta), ctypes.byref(nn)) == 0 and nn.value == n
+    # the same normal equations in scipy: J is [7r x 7n] with two 7x7 blocks per edge row (ba.cpp:174-234)
+    rows = (np.arange(r)[:, None, None] * 7 + np.arange(7)[None, :, None]) + np.zeros((1, 1, 7), np.int64)
+    cols_i = ii[:, None, None] * 7 + np.arange(7)[None, None, :] + np.zeros((1, 7, 1), np.int64)
+    cols_j = jj[:, None, None] * 7 + np.arange(7)[None, None, :] + np.zeros((1, 7, 1), np.int64)
+    J = sp.coo_matrix((np.concatenate([Ji.astype(np.float64).ravel(), Jj.astype(np.float64).ravel()]),
+                       (np.concatenate([rows.ravel(), rows.ravel()]), np.concatenate([cols_i.ravel(), cols_j.ravel()]))), shape=(7 * r, 7 * n)).tocsr()
+    A = (J.T @ J).tolil()
+    d = A.diagonal()
+    A.setdiag(d + d * np.float64(np.float32(lm)) + np.float64(np.float32(ep)))
+    b = -(J.T @ res.astype(np.float64).ravel())
+    m = 7 * n if freen < 0 else 7 * freen
+    x = np.zeros(7 * n)
+    x[:m] = spl.spsolve(A.tocsc()[:m, :m], b[:m])
+    assert np.abs(delta.ravel() - x).max() < 2e-5 * max(1.0, np.abs(x).max())
+    assert np.all(delta.ravel()[m:] == 0)
+    ref = ref_modules.get("ref_cuda_ba") if hasattr(ref_modules, "get") else None
+    if ref is not None and n <= 700:                          # the reference itself (Eigen SimplicialLLT), where it was built
+        import torch
+        dr, = ref.solve_system(torch.from_numpy(Ji), torch.from_numpy(Jj), torch.from_numpy(ii), torch.from_numpy(jj), torch.from_numpy(res), ep, lm, freen)
+        assert np.abs(delta.ravel() - dr.numpy().ravel()).max() < 2e-5 * max(1.0, np.abs(x).max())
+
+
 # ------------------------------------------------------------------------------------------------- COLMAP text export (SURVEY 8f N3)
 def test_float_formatter_is_cpython_repr():
     """every number of the export goes through wv_format_f64; the reference formats with f-strings / str(): CPython's float repr"""

@@ -11,39 +11,53 @@
 
 namespace {
 
-// Banded-aware dense LL^T in double on the lower triangle (row-major n x n); returns false if not SPD.
-// PGO systems here are <= a few thousand unknowns with a chain + a few loop edges, so the profile
-// (first non-zero column of every row) stays short and the factorisation is O(n * profile^2).
-bool profile_cholesky_solve(std::vector<double>& A, std::vector<double>& b, int64_t n) {
-  std::vector<int64_t> first(n);
-  for (int64_t i = 0; i < n; i++) {
-    int64_t f = i;
-    for (int64_t k = 0; k < i; k++)
-      if (A[i * n + k] != 0.0) { f = k; break; }
-    first[i] = f;
+// The lower triangle of a symmetric matrix in SKYLINE (envelope) storage: row i holds its entries from its first non-zero column
+// first[i] to the diagonal, contiguously.  Cholesky fill-in stays inside the envelope, so nothing else is ever stored: a pose
+// graph of n frames with a chain and a few loop edges costs O(n * band + loops * n) doubles -- not the (7n)^2 of a dense matrix
+// (1.6 GB at n = 2 048) -- where the reference hands the same system to Eigen's sparse SimplicialLLT (dpvo/fastba/ba.cpp:156-172).
+struct Skyline {
+  std::vector<int64_t> first, off;
+  std::vector<double> v;
+  void shape(const std::vector<int64_t>& first_col) {
+    first = first_col;
+    off.resize(first.size() + 1);
+    off[0] = 0;
+    for (size_t i = 0; i < first.size(); i++) off[i + 1] = off[i] + ((int64_t)i - first[i] + 1);
+    v.assign((size_t)off.back(), 0.0);
   }
-  for (int64_t i = 0; i < n; i++) {  // fill-in can only lower a row's first column to that of rows it touches
-    for (int64_t j = first[i]; j <= i; j++) {
-      double s = A[i * n + j];
-      const int64_t k0 = std::max(first[i], first[j]);
-      for (int64_t k = k0; k < j; k++) s -= A[i * n + k] * A[j * n + k];
+  double& at(int64_t i, int64_t j) { return v[(size_t)(off[i] + j - first[i])]; }   // first[i] <= j <= i
+  const double* row(int64_t i) const { return v.data() + off[i] - first[i]; }      // row(i)[j], first[i] <= j <= i
+  double* row(int64_t i) { return v.data() + off[i] - first[i]; }
+};
+
+// LL^T in double inside the envelope, then the two substitutions; false if not SPD
+bool skyline_cholesky_solve(Skyline& A, std::vector<double>& b) {
+  const int64_t n = (int64_t)A.first.size();
+  for (int64_t i = 0; i < n; i++) {
+    double* ri = A.row(i);
+    for (int64_t j = A.first[i]; j <= i; j++) {
+      const double* rj = A.row(j);
+      double s = ri[j];
+      for (int64_t k = std::max(A.first[i], A.first[j]); k < j; k++) s -= ri[k] * rj[k];
       if (j < i) {
-        A[i * n + j] = s / A[j * n + j];
+        ri[j] = s / rj[j];
       } else {
         if (!(s > 0.0)) return false;
-        A[i * n + i] = sqrt(s);
+        ri[i] = sqrt(s);
       }
     }
   }
   for (int64_t i = 0; i < n; i++) {
+    const double* ri = A.row(i);
     double s = b[i];
-    for (int64_t k = first[i]; k < i; k++) s -= A[i * n + k] * b[k];
-    b[i] = s / A[i * n + i];
+    for (int64_t k = A.first[i]; k < i; k++) s -= ri[k] * b[k];
+    b[i] = s / ri[i];
   }
   for (int64_t i = n - 1; i >= 0; i--) {
-    b[i] /= A[i * n + i];
+    const double* ri = A.row(i);
+    b[i] /= ri[i];
     const double x = b[i];
-    for (int64_t k = first[i]; k < i; k++) b[k] -= A[i * n + k] * x;
+    for (int64_t k = A.first[i]; k < i; k++) b[k] -= ri[k] * x;
   }
   return true;
 }
@@ -67,19 +81,30 @@ int wv_solve_system_host(const float* J_i, const float* J_j, const int64_t* ii, 
   int64_t m = freen < 0 ? n7 : std::min<int64_t>(n7, (int64_t)freen * 7);  // solve(A, b, freen*7), ba.cpp:156-172
   for (int64_t a = 0; a < n7; a++) delta[a] = 0.f;
   if (m == 0) return WV_OK;
-  std::vector<double> A((size_t)m * m, 0.0), b((size_t)m, 0.0);
+  // envelope: a row block starts at the lowest block an edge connects it to
+  std::vector<int64_t> first((size_t)m);
+  for (int64_t a = 0; a < m; a++) first[a] = a / 7 * 7;
+  for (int64_t x = 0; x < r; x++) {
+    const int64_t lo = std::min(ii[x], jj[x]) * 7, hi = std::max(ii[x], jj[x]) * 7;
+    if (hi >= m) continue;
+    for (int l = 0; l < 7; l++) first[hi + l] = std::min(first[hi + l], lo);
+  }
+  Skyline A;
+  A.shape(first);
+  std::vector<double> b((size_t)m, 0.0);
   for (int64_t x = 0; x < r; x++) {
     const int64_t cb[2] = {ii[x] * 7, jj[x] * 7};
     const float* Jb[2] = {J_i + x * 49, J_j + x * 49};
     for (int p = 0; p < 2; p++) {
       if (cb[p] >= m) continue;
       for (int q = 0; q < 2; q++) {
-        if (cb[q] >= m) continue;
+        if (cb[q] >= m || cb[q] > cb[p]) continue;   // lower triangle only
         for (int l = 0; l < 7; l++)
           for (int c = 0; c < 7; c++) {
+            if (cb[q] + c > cb[p] + l) continue;
             double s = 0;
             for (int k = 0; k < 7; k++) s += (double)Jb[p][k * 7 + l] * (double)Jb[q][k * 7 + c];
-            A[(size_t)(cb[p] + l) * m + cb[q] + c] += s;
+            A.at(cb[p] + l, cb[q] + c) += s;
           }
       }
       for (int l = 0; l < 7; l++) {
@@ -89,8 +114,8 @@ int wv_solve_system_host(const float* J_i, const float* J_j, const int64_t* ii, 
       }
     }
   }
-  for (int64_t d = 0; d < m; d++) { A[(size_t)d * m + d] += A[(size_t)d * m + d] * (double)lm; A[(size_t)d * m + d] += (double)ep; }
-  if (!profile_cholesky_solve(A, b, m)) return 1;
+  for (int64_t d = 0; d < m; d++) { A.at(d, d) += A.at(d, d) * (double)lm; A.at(d, d) += (double)ep; }
+  if (!skyline_cholesky_solve(A, b)) return 1;
   for (int64_t a = 0; a < m; a++) delta[a] = (float)b[a];
   return WV_OK;
 }
