@@ -3,7 +3,8 @@ block-banded Cholesky instead of the reference's dense torch::linalg::cholesky +
 
 Checked here, on the GPU, through the C ABI (wv_ba_band_solve) and through cuda_ba:
   * the solve against scipy's fp64 banded Cholesky on random SPD band systems, N = 1 ... 2047 poses, half-widths 2 ... 25, with and
-    without the reference's damping; tolerance: fp32 backward error (stated at the assert);
+    without the reference's damping, single-sided (short chains) and two-sided (long chains: both ends at once, a middle system
+    in between); tolerance: fp32 backward error (stated at the assert);
   * a non-positive pivot raises the status flag; sizes beyond the maximum half-width are refused;
   * the band buffer built by ba_global_kernel holds the same numbers as the dense build, and nothing of S lies outside the band;
   * whole BA calls through the band path and through the dense path (WVB200_GLOBAL_DENSE=1) against the fp64 oracle of the
@@ -81,7 +82,9 @@ def _solve(lib, S, y, n6, bs, damp):
 
 
 @pytest.mark.parametrize("N,bs,damp", [(1, 2, 1), (2, 2, 1), (3, 5, 0), (7, 25, 1), (26, 24, 1), (27, 25, 0), (40, 5, 1), (300, 19, 1),
-                                       (301, 2, 0), (1024, 24, 1), (2047, 24, 1), (2047, 19, 0), (2047, 25, 1)])
+                                       (301, 2, 0), (1024, 24, 1), (2047, 24, 1), (2047, 19, 0), (2047, 25, 1),
+                                       # around the switch to the two-sided factorisation (N >= 2 bs + 16) and uneven halves
+                                       (65, 25, 1), (66, 25, 1), (67, 25, 0), (20, 2, 1), (21, 2, 1), (101, 24, 1), (64, 24, 1)])
 def test_band_solve_vs_scipy_banded_cholesky(N, bs, damp):
     from scipy.linalg import solveh_banded
     lib = _lib()
@@ -104,12 +107,13 @@ def test_band_solve_vs_scipy_banded_cholesky(N, bs, damp):
 
 def test_band_solve_flags_a_non_positive_pivot_and_refuses_bad_sizes():
     lib = _lib()
-    N, bs = 40, 5
-    n6, ld = 6 * N, (6 * (bs + 2) + 3) // 4 * 4
-    ab, y = _band_system(N, bs, seed=3)
-    ab[0, 6 * 17 + 2] = -50.0                                    # one negative diagonal entry (stays negative after the damping)
-    rc, x, status = _solve(lib, _to_band_layout(ab, ld, lib.wv_ba_band_floats(n6, bs)), y, n6, bs, 1)
-    assert rc == 0 and status & WV_STATUS_NOT_SPD
+    # the bad pivot in the forward half, in the reverse half, in the middle system of the two-sided form, and in a single-sided solve
+    for N, bs, where in ((40, 5, 3), (40, 5, 33), (40, 5, 19), (12, 5, 7)):
+        n6, ld = 6 * N, (6 * (bs + 2) + 3) // 4 * 4
+        ab, y = _band_system(N, bs, seed=3)
+        ab[0, 6 * where + 2] = -50.0                             # one negative diagonal entry (stays negative after the damping)
+        rc, x, status = _solve(lib, _to_band_layout(ab, ld, lib.wv_ba_band_floats(n6, bs)), y, n6, bs, 1)
+        assert rc == 0 and status & WV_STATUS_NOT_SPD, (N, bs, where)
     mx = lib.wv_ba_band_max_bs()
     assert mx >= 25                                              # the tracker's PATCH_LIFETIME window (span 24) and the global pattern (19) fit
     S = _to_band_layout(*(_band_system(4, 2, 1)[0], (6 * 4 + 3) // 4 * 4, lib.wv_ba_band_floats(24, 2)))

@@ -42,7 +42,11 @@ int band_ld(int bs) { return (6 * (bs + 2) + 3) & ~3; }                       //
 size_t band_floats(int n6, int bs) { return ((size_t)n6 * (size_t)(band_ld(bs) + 1) + 64 + 3) & ~(size_t)3; }   // multiple of 4: y behind it stays 16-byte aligned
 // factor storage: per pose ONE record of (bs + 2) tiles of 36 floats: [0] L_pp, [1..bs] Y(p + d, p)^T, [bs + 1] = the reciprocals
 // of diag(L_pp) in floats 0..5 and z_p in floats 8..13
-size_t band_factor_floats(int n6, int bs) { return (size_t)(n6 / 6) * (size_t)(bs + 2) * 36 + 64; }
+// ... followed by the scratch of the two-sided form: the middle system of bs poses (band buffer, right-hand side, its own factor)
+size_t band_factor_floats(int n6, int bs) {
+  const int bsm = bs - 1 < 2 ? 2 : bs - 1;
+  return (size_t)(n6 / 6) * (size_t)(bs + 2) * 36 + band_floats(6 * bs, bsm) + (size_t)(6 * bs + 4) + (size_t)bs * (size_t)(bsm + 2) * 36 + 64;
+}
 
 struct BandArgs {
   const float* S;   // band buffer
@@ -52,6 +56,14 @@ struct BandArgs {
   int N, bs, ld, damp;
   int* status;
   int prio;         // 1: the publishing warp updates first, alone (named barrier 1).  WVB200_BAND_PRIO; measured slower, off
+  // Two-sided ("twisted") factorisation, grid = 2: CTA 0 eliminates poses 0 .. mf-1 forwards, CTA 1 poses N-1 .. N-mb downwards (the
+  // same code on the block-reversed matrix); the g = N - mf - mb = bs poses in between form the MIDDLE system, which both CTAs
+  // accumulate into Smid / ymid (band layout, leading dimension ldm) and a single-sided solve finishes.  Single-sided: mf = N,
+  // mb = 0, Smid = nullptr, grid = 1.
+  int mf, mb;
+  float* Smid;
+  float* ymid;
+  int ldm;
 };
 
 
@@ -77,7 +89,14 @@ __device__ __forceinline__ float rsqrt_raw(float x) {   // one MUFU.RSQ: no deno
 
 __global__ void __launch_bounds__(32 * (kBandMaxBs + 3), 1) ba_band_factor_kernel(BandArgs g) {
   extern __shared__ __align__(16) float smem[];
-  const int bs = g.bs, T = bs + 2, N = g.N, ld = g.ld;
+  const int bs = g.bs, T = bs + 2, ld = g.ld;
+  // this CTA's side: it eliminates `me` poses of a local chain of N poses -- its own plus, two-sided, the middle ones; local pose R
+  // is global pose R (forward) or g.N - 1 - R (reverse)
+  const bool rev = blockIdx.x == 1;
+  const int me = rev ? g.mb : g.mf;
+  const int gsz = g.N - g.mf - g.mb;
+  const int N = me + gsz;
+  float* const F = g.F + (rev ? (size_t)g.mf * (size_t)(bs + 2) * 36 : 0);
   float* sY = smem;                               // [2][T][kYStride]: Y(R, p) transposed ([k][i]), slot R % T, double buffered over p
   float* sL = sY + 2 * T * kYStride;              // [2][44]: L_qq (36) and the reciprocals of its diagonal (6)
   float* sz = sL + 88;                            // [8]: z_p
@@ -95,27 +114,41 @@ __global__ void __launch_bounds__(32 * (kBandMaxBs + 3), 1) ba_band_factor_kerne
   for (int i = 0; i < 6; i++)
 #pragma unroll
     for (int j = 0; j < 3; j++) a[i][j] = make_float2(0.f, 0.f);
-  auto load_tile = [&](int C) {                   // block (C + d, C) of the band buffer.  A diagonal block's upper triangle gets whatever
-    const float* src = g.S + (size_t)(6 * (C + d)) * ld + 6 * C;   // lies next to the diagonal: the updates write it, nothing reads it
+  // block (C + d, C) of the local chain into t.  Forward: as stored.  Reverse: local (R, C) is global (N-1-R, N-1-C), which lies
+  // in the upper triangle: the stored block (N-1-C, N-1-R) transposed -- except on the diagonal, where the stored lower triangle
+  // is what is wanted.  (A diagonal block's upper triangle gets whatever lies next to the diagonal in the band buffer: the
+  // updates write it, nothing reads it.)
+  auto fetch_tile = [&](int C, float2 (&t)[6][3]) {
+    const int gr = rev ? g.N - 1 - C : C + d, gc = rev ? g.N - 1 - (C + d) : C;
+    const float* src = g.S + (size_t)(6 * gr) * ld + 6 * gc;
+    if (rev && d > 0) {
 #pragma unroll
-    for (int i = 0; i < 6; i++) {
-      const float2* row = reinterpret_cast<const float2*>(src + (size_t)i * ld);
-      a[i][0] = row[0]; a[i][1] = row[1]; a[i][2] = row[2];
+      for (int i = 0; i < 6; i++)
+#pragma unroll
+        for (int j = 0; j < 6; j++) WV_E(t, i, j) = src[(size_t)j * ld + i];
+    } else {
+#pragma unroll
+      for (int i = 0; i < 6; i++) {
+        const float2* row = reinterpret_cast<const float2*>(src + (size_t)i * ld);
+        t[i][0] = row[0]; t[i][1] = row[1]; t[i][2] = row[2];
+      }
     }
   };
-  auto damp_diag = [&]() {
+  auto load_tile = [&](int C) { fetch_tile(C, a); };
+  auto damp_diag = [&](float2 (&t)[6][3]) {
 #pragma unroll
-    for (int i = 0; i < 6; i++) WV_E(a, i, i) = WV_E(a, i, i) + (WV_E(a, i, i) * 1e-4f + 1.0f);
+    for (int i = 0; i < 6; i++) WV_E(t, i, i) = WV_E(t, i, i) + (WV_E(t, i, i) * 1e-4f + 1.0f);
   };
+  auto y_row = [&](int R) { return g.y + 6 * (rev ? g.N - 1 - R : R); };
   if (w < T) {                                    // tile warp w starts with column w
     if (d <= bs && w + d < N) load_tile(w);
-    if (d == 0 && g.damp) damp_diag();
+    if (d == 0 && g.damp) damp_diag(a);
   } else if (lane < T && lane < N) {              // rhs warp: rows 0..T-1
 #pragma unroll
-    for (int i = 0; i < 6; i++) WV_Y(i) = g.y[6 * lane + i];
+    for (int i = 0; i < 6; i++) WV_Y(i) = y_row(lane)[i];
   }
 
-  for (int p = p0; p < N; p++) {
+  for (int p = p0; p < me; p++) {
     if (w < T) {
       // ---- (1) the warp whose column was panel p - 1 is free: it loads its next column, p + T, whole -- a warp-uniform branch (a
       //          load in SOME lane would put its destination registers on the scoreboard of the whole warp and stall the update),
@@ -123,7 +156,7 @@ __global__ void __launch_bounds__(32 * (kBandMaxBs + 3), 1) ba_band_factor_kerne
       if (m == 0 && p >= 0) {
         // ... after it has written its factor record to global memory for the back substitution -- from shared memory, where panel p
         // stays valid through this step: the TRANSPOSED blocks Y(p + d, p)^T, and L_pp with the reciprocals of its diagonal
-        float* Fp = g.F + (size_t)p * FP;
+        float* Fp = F + (size_t)p * FP;
         if (d >= 1 && d <= bs && p + d < N) {
           const float4* src = reinterpret_cast<const float4*>(sY + (size_t)((p & 1) * T + slotR) * kYStride);
           float4* dst = reinterpret_cast<float4*>(Fp + (size_t)d * 36);
@@ -142,7 +175,7 @@ __global__ void __launch_bounds__(32 * (kBandMaxBs + 3), 1) ba_band_factor_kerne
         }
         if (d <= bs && p + T + d < N) load_tile(p + T);
       }
-      if (d == 0 && m == bs && g.damp && p + m >= T) damp_diag();
+      if (d == 0 && m == bs && g.damp && p + m >= T) damp_diag(a);
       // ---- (2) trailing update with panel p.  The warp that publishes in this step is the critical path (update -> factor + solve
       //          -> publish -> barrier).  g.prio lets it update first, alone (named barrier 1 over the tile warps), with the others'
       //          update hidden behind its factor + solve; measured (tools/band_trace.cu) that loses: 2.66 vs 2.21 us per step -----------
@@ -173,7 +206,7 @@ __global__ void __launch_bounds__(32 * (kBandMaxBs + 3), 1) ba_band_factor_kerne
       WV_TR(p, 7, m == 5 && lane == 0);
       if (g.prio && m == 1) asm volatile("bar.arrive 1, %0;" ::"r"(32 * T) : "memory");
       // ---- (3) the warp of column q = p + 1: factor, solve, publish ----------------------------------------------------------------
-      if (m == 1 && p + 1 >= 0 && p + 1 < N) {
+      if (m == 1 && p + 1 >= 0 && p + 1 < me) {
         const int q = p + 1;
         float* L = sL + (q & 1) * 44;
         // lane 0 hands its diagonal block to the whole warp, and EVERY lane factors it: in lockstep that costs what lane 0 alone
@@ -246,7 +279,7 @@ __global__ void __launch_bounds__(32 * (kBandMaxBs + 3), 1) ba_band_factor_kerne
       // ---- (r) right-hand side: lane l holds y of the rows == l (mod T) ------------------------------------------------------------
       if (lane < T && ml == 0) {   // row p: every update is in; L z_p = y_p
         const float* L = sL + (p & 1) * 44;
-        float* zg = g.F + (size_t)p * FP + (size_t)(bs + 1) * 36 + 8;
+        float* zg = F + (size_t)p * FP + (size_t)(bs + 1) * 36 + 8;
         float zz[6];
 #pragma unroll
         for (int i = 0; i < 6; i++) {
@@ -259,7 +292,7 @@ __global__ void __launch_bounds__(32 * (kBandMaxBs + 3), 1) ba_band_factor_kerne
         }
         const int Rn = p + T;      // this lane's next row
 #pragma unroll
-        for (int i = 0; i < 6; i++) WV_Y(i) = Rn < N ? g.y[6 * Rn + i] : 0.f;
+        for (int i = 0; i < 6; i++) WV_Y(i) = Rn < N ? y_row(Rn)[i] : 0.f;
       }
       __syncwarp();
       if (lane < T && ml >= 1 && ml <= bs && p + ml < N) {
@@ -279,6 +312,41 @@ __global__ void __launch_bounds__(32 * (kBandMaxBs + 3), 1) ba_band_factor_kerne
     WV_TR(p, 5, w == T && lane == 0);
     __syncthreads();
   }
+  // ---- two-sided: what is left in the window is this side's Schur complement on the middle poses (local me .. me + gsz - 1): block
+  //      (me + m + d, me + m) in the thread of phase m (the phases now belong to p = me).  Middle = W_forward + W_reverse - A (the
+  //      original block is in both windows, damped in both): the forward side subtracts it.  The reverse side's blocks land
+  //      block-reversed and transposed.
+  if (g.Smid) {
+    const int ldm = g.ldm;
+    if (w < T) {
+      const int cM = m, rM = m + d;
+      if (m < gsz && d <= bs && rM < gsz) {
+        if (!rev) {
+          float2 o[6][3];
+          fetch_tile(me + m, o);
+          if (d == 0 && g.damp) damp_diag(o);
+#pragma unroll
+          for (int i = 0; i < 6; i++)
+#pragma unroll
+            for (int j = 0; j < 3; j++) { a[i][j].x -= o[i][j].x; a[i][j].y -= o[i][j].y; }
+        }
+        const int rb = rev ? gsz - 1 - cM : rM, cb = rev ? gsz - 1 - rM : cM;
+        float* dst = g.Smid + (size_t)(6 * rb) * ldm + 6 * cb;
+#pragma unroll
+        for (int i = 0; i < 6; i++)
+#pragma unroll
+          for (int j = 0; j < 6; j++) {
+            if (d == 0) { if (j <= i) atomicAdd(dst + (size_t)i * ldm + j, WV_E(a, i, j)); }
+            else if (!rev) atomicAdd(dst + (size_t)i * ldm + j, WV_E(a, i, j));
+            else atomicAdd(dst + (size_t)j * ldm + i, WV_E(a, i, j));
+          }
+      }
+    } else if (lane < T && ml < gsz) {
+      const int R = me + ml, rb = rev ? gsz - 1 - ml : ml;
+#pragma unroll
+      for (int i = 0; i < 6; i++) atomicAdd(g.ymid + 6 * rb + i, WV_Y(i) - (rev ? 0.f : y_row(R)[i]));
+    }
+  }
 }
 
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
@@ -295,12 +363,19 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 // shared memory that holds the bs + 1 records a step reads plus kBackPrefetch in flight.
 __global__ void __launch_bounds__(32, 1) ba_band_backsolve_kernel(BandArgs g) {
   extern __shared__ __align__(16) float smem[];
-  const int bs = g.bs, N = g.N, d = threadIdx.x;
+  const int bs = g.bs, d = threadIdx.x;
+  // this CTA's side (see ba_band_factor_kernel): `me` eliminated poses with factor records, then gsz middle poses whose x is
+  // already in dX (the middle solve ran before this kernel)
+  const bool rev = blockIdx.x == 1;
+  const int me = rev ? g.mb : g.mf;
+  const int gsz = g.N - g.mf - g.mb;
+  const int N = me + gsz;
   const int FP = (bs + 2) * 36, FP4 = FP / 4, RING = bs + 2 + kBackPrefetch;
+  const float* const F = g.F + (rev ? (size_t)g.mf * FP : 0);
   float* ring = smem;                                   // [RING][FP], record of pose q in slot q % RING
   auto issue = [&](int pose) {
-    if (pose >= 0) {
-      const float4* src = reinterpret_cast<const float4*>(g.F + (size_t)pose * FP);
+    if (pose >= 0 && pose < me) {
+      const float4* src = reinterpret_cast<const float4*>(F + (size_t)pose * FP);
       float4* dst = reinterpret_cast<float4*>(ring + (size_t)(pose % RING) * FP);
       for (int t = d; t < FP4; t += 32) cp_async16(dst + t, src + t);
     }
@@ -317,7 +392,7 @@ __global__ void __launch_bounds__(32, 1) ba_band_backsolve_kernel(BandArgs g) {
     cp_async_wait<kBackPrefetch>();                     // record R - bs (and every later one) has landed
     __syncwarp();
     issue(R - bs - kBackPrefetch - 1);                  // into the slot of pose R + 1, which nobody reads any more
-    const bool act = tile_lane && R - d >= 0;
+    const bool act = tile_lane && R - d >= 0 && R - d < me;
     float yt[36];                                       // Y(R, R - d)^T: [j][i]
     if (act) {
       const float4* t4 = reinterpret_cast<const float4*>(ring + (size_t)slotd * FP + d * 36);
@@ -327,16 +402,22 @@ __global__ void __launch_bounds__(32, 1) ba_band_backsolve_kernel(BandArgs g) {
     float x[6];
 #pragma unroll
     for (int k = 0; k < 6; k++) x[k] = 0.f;
-    if (d == 0) {   // L_RR^T x_R = z_R - sum:  x[k] = (rhs[k] - sum_{j > k} L[j][k] x[j]) / L[k][k], k descending
-      const float* L = ring + (size_t)slot0 * FP;
-      const float* rz = L + (bs + 1) * 36;              // [0..5] reciprocals of the diagonal, [8..13] z_R
+    if (d == 0) {
+      float* xg = g.dX + 6 * (rev ? g.N - 1 - R : R);
+      if (R >= me) {   // a middle pose: solved already
 #pragma unroll
-      for (int k = 5; k >= 0; k--) {
-        float s = rz[8 + k] - acc[k];
+        for (int k = 0; k < 6; k++) x[k] = xg[k];
+      } else {         // L_RR^T x_R = z_R - sum:  x[k] = (rhs[k] - sum_{j > k} L[j][k] x[j]) / L[k][k], k descending
+        const float* L = ring + (size_t)slot0 * FP;
+        const float* rz = L + (bs + 1) * 36;            // [0..5] reciprocals of the diagonal, [8..13] z_R
 #pragma unroll
-        for (int j = k + 1; j < 6; j++) s = fmaf(-L[6 * j + k], x[j], s);
-        x[k] = s * rz[k];
-        g.dX[6 * R + k] = x[k];
+        for (int k = 5; k >= 0; k--) {
+          float s = rz[8 + k] - acc[k];
+#pragma unroll
+          for (int j = k + 1; j < 6; j++) s = fmaf(-L[6 * j + k], x[j], s);
+          x[k] = s * rz[k];
+          xg[k] = x[k];
+        }
       }
     }
 #pragma unroll
@@ -354,22 +435,58 @@ __global__ void __launch_bounds__(32, 1) ba_band_backsolve_kernel(BandArgs g) {
   }
 }
 
+static int band_mid_bs(int bs) { return bs - 1 < 2 ? 2 : bs - 1; }   // half-width of the middle system of bs poses
+static bool band_two_sided(int N, int bs) {
+  static const int on = [] { const char* e = getenv("WVB200_BAND_TWISTED"); return e ? atoi(e) : 1; }();
+  return on && N >= 2 * bs + 16;
+}
+
+static int band_launch(const BandArgs& a, int grid, cudaStream_t st) {
+  const int T = a.bs + 2;
+  const size_t smem = sizeof(float) * (size_t)(2 * T * kYStride + 88 + 8);
+  ba_band_factor_kernel<<<grid, 32 * (T + 1), smem, st>>>(a);
+  WV_LAUNCH_CHECK();
+  return WV_OK;
+}
+static int band_back_launch(const BandArgs& a, int grid, cudaStream_t st) {
+  const int T = a.bs + 2;
+  const size_t smem_b = sizeof(float) * (size_t)(a.bs + 2 + kBackPrefetch) * T * 36;   // 128 KB at bs = 25
+  WV_CUDA_TRY(cudaFuncSetAttribute(ba_band_backsolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_b));
+  ba_band_backsolve_kernel<<<grid, 32, smem_b, st>>>(a);
+  WV_LAUNCH_CHECK();
+  return WV_OK;
+}
+
 // S: band buffer (band_floats(n6, bs) floats, lower triangle, not yet damped); y [n6]; F: band_factor_floats(n6, bs) floats of
-// scratch; dX [n6].  Two launches on `st`, no host synchronisation; a non-positive pivot sets WV_STATUS_NOT_SPD.
+// scratch; dX [n6].  Launches on `st` only, no host synchronisation; a non-positive pivot sets WV_STATUS_NOT_SPD.
+// Long chains are factored from BOTH ends at once (two CTAs, N / 2 dependent steps each instead of N): see BandArgs.
 int ba_band_solve(const float* S, const float* y, int n6, int bs, int damp, float* F, float* dX, int* status, cudaStream_t st) {
   if (n6 <= 0) return WV_OK;
   if (bs < 2 || bs > kBandMaxBs || n6 % 6 != 0) return WV_EINVAL;
-  const int N = n6 / 6, T = bs + 2;
+  const int N = n6 / 6;
   static const int prio = [] { const char* e = getenv("WVB200_BAND_PRIO"); return e ? atoi(e) : 0; }();
-  BandArgs a{S, y, F, dX, N, bs, band_ld(bs), damp, status, prio};
-  const size_t smem = sizeof(float) * (size_t)(2 * T * kYStride + 88 + 8);
-  ba_band_factor_kernel<<<1, 32 * (T + 1), smem, st>>>(a);
-  WV_LAUNCH_CHECK();
-  const size_t smem_b = sizeof(float) * (size_t)(bs + 2 + kBackPrefetch) * T * 36;   // 128 KB at bs = 25
-  WV_CUDA_TRY(cudaFuncSetAttribute(ba_band_backsolve_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_b));
-  ba_band_backsolve_kernel<<<1, 32, smem_b, st>>>(a);
-  WV_LAUNCH_CHECK();
-  return WV_OK;
+  BandArgs a{S, y, F, dX, N, bs, band_ld(bs), damp, status, prio, N, 0, nullptr, nullptr, 0};
+  if (!band_two_sided(N, bs)) {
+    int rc = band_launch(a, 1, st);
+    return rc != WV_OK ? rc : band_back_launch(a, 1, st);
+  }
+  const int g = bs, bsm = band_mid_bs(bs);
+  a.mf = (N - g + 1) / 2;
+  a.mb = N - g - a.mf;
+  a.ldm = band_ld(bsm);
+  float* mid = F + (size_t)N * (size_t)(bs + 2) * 36;
+  const size_t smid = band_floats(6 * g, bsm), ymid = (size_t)(6 * g + 3) & ~(size_t)3;
+  a.Smid = mid;
+  a.ymid = mid + smid;
+  float* Fmid = a.ymid + ymid;
+  WV_CUDA_TRY(cudaMemsetAsync(mid, 0, (smid + ymid) * sizeof(float), st));
+  int rc = band_launch(a, 2, st);
+  if (rc != WV_OK) return rc;
+  // the middle system: bs poses, already damped, solved single-sided straight into its place in dX
+  BandArgs am{a.Smid, a.ymid, Fmid, dX + 6 * a.mf, g, bsm, a.ldm, 0, status, prio, g, 0, nullptr, nullptr, 0};
+  if ((rc = band_launch(am, 1, st)) != WV_OK) return rc;
+  if ((rc = band_back_launch(am, 1, st)) != WV_OK) return rc;
+  return band_back_launch(a, 2, st);
 }
 
 }  // namespace wv
