@@ -46,7 +46,7 @@ enum {
 enum {
   WV_STATUS_BAD_INDEX = 1, /* an ii/jj/kk entry was outside its tensor; that edge was skipped */
   WV_STATUS_NOT_SPD = 2,   /* Cholesky met a non-positive pivot (reference: torch::linalg::cholesky throws, ba_cuda.cu:521) */
-  WV_STATUS_TOO_DENSE = 4, /* global BA: one patch had more than 384 free-pose observations; the excess was dropped */
+  WV_STATUS_TOO_DENSE = 4, /* global BA: one patch had more than 8 256 entries (two per pose of a 4 096-frame buffer) in its column of E; the excess was dropped */
   WV_STATUS_STALE_PLAN = 8 /* wv_ba_forward_planned: the plan in the workspace was not built for this kk; the result is invalid */
 };
 

@@ -829,17 +829,28 @@ def test_pops_full_size_vs_oracle_and_bad_index(syn):
         del os.environ["WVB200_CHECK_INDICES"]
 
 
-def test_global_ba_dense_patches_and_entry_limit(syn):
-    """every patch observed by every frame: 60 observations per patch go through the per-warp entry list (2 lane chunks per patch);
-    more than 384 observations per patch is refused loudly, not silently truncated"""
+def test_global_ba_dense_patches_and_heavy_patches(syn):
+    """every patch observed by every frame.  60 observations per patch go through the per-warp entry list in shared memory (2 lane
+    chunks per patch); 399 observations per patch (more than the 384-entry list holds: round 1 refused that) go through the heavy
+    pass with the entry lists in global memory -- the reference has no limit (a camera turning on the spot under distance-based
+    edges sees a patch from every frame).  Both against the fp64 oracle; a mixed scene (heavy and light patches side by side) too."""
     s = syn.make_ba_scene(seed=16, n=60, M=2, edges="all", pose_noise=0.005)
     o, *tols = _global_tol(s, 1, 60, 1)
     poses, patches = run_ba(s, 1, 60, 1)
     _check_global(poses, patches, o, *tols)
     big = syn.make_ba_scene(seed=17, n=400, M=1, edges="all", pose_noise=0.002)
-    with pytest.raises(RuntimeError, match="more than 384"):
-        run_ba(big, 1, 400, 1)
-    run_ba(s, 1, 60, 1)  # and the extension keeps working
+    o, *tols = _global_tol(big, 1, 400, 1)
+    poses, patches = run_ba(big, 1, 400, 1)
+    _check_global(poses, patches, o, *tols)
+    assert np.abs(patches[:, 2, 0, 0] - big["patches"][:, 2, 0, 0]).max() > 1e-4     # the depths did move
+    # mixed: the global pattern plus three patches that every frame observes (the edge list stays in the generator's order: the
+    # heavy patches' edges come last, not grouped with their neighbours')
+    n = 420
+    mix = syn.make_ba_scene(seed=18, n=n, M=2, edges="global", pose_noise=0.003, heavy_patches=(7, 401, 838))
+    assert np.bincount(mix["kk"]).max() == n - 1
+    o, *tols = _global_tol(mix, 1, n, 1)
+    poses, patches = run_ba(mix, 1, n, 1)
+    _check_global(poses, patches, o, *tols)
 
 
 # ------------------------------------------------------------------------------------------------- SoftAgg (group plan + fused scatter softmax / sum)

@@ -28,6 +28,14 @@ static constexpr int kGThreads = 256;
 static constexpr int kGWarps = kGThreads / 32;
 static constexpr int kMaxEntries = 384;  // (frame, 6-vector) entries of one patch's column of E (per-warp list in shared memory)
 static constexpr size_t kEntryBytes = (size_t)kGWarps * kMaxEntries * (6 * sizeof(float) + sizeof(int));
+// A patch with more than kMaxEntries / 2 edges ("heavy": a camera turning on the spot under distance-based edges can see one
+// patch from every frame; the reference has no limit) may not fit the shared-memory list.  The main pass skips it and appends its
+// rank to a list; a second, small launch of the SAME kernel body (HEAVY) walks that list with the entry lists in global memory
+// (kHeavyCap entries per warp: two per pose of a 4 096-frame buffer).  Slower per patch, but nothing is dropped.
+static constexpr int kHeavyCtas = 16;
+static constexpr int kHeavyCap = 2 * 4096 + 64;
+static constexpr size_t kHeavySpillBytes = (size_t)kHeavyCtas * kGWarps * kHeavyCap * (6 * sizeof(float) + sizeof(int));
+static size_t heavy_list_ints(int64_t E) { return (size_t)(E / (kMaxEntries / 2 + 1) + 2 + 3) & ~(size_t)3; }
 
 struct GArgs {
   float* poses; float* patches; const float* intr; const float* target; const float* weight; const float* lmbda;
@@ -42,6 +50,8 @@ struct GArgs {
   float* dZ;        // [Mp_cap], indexed by the plan's patch rank
   int shard, nshards;
   int* status;
+  int* heavy;       // [0] count, [4 ...] ranks of the heavy patches of this pass (workspace, behind the plan)
+  float* spill;     // HEAVY: entry lists in global memory, [kHeavyCtas * kGWarps][kHeavyCap] x (6 floats), then the frames
 };
 
 // A CTA works on a chunk of kChunk consecutive patches (consecutive ids = the same or neighbouring source frames, which observe
@@ -135,12 +145,13 @@ __device__ __forceinline__ void lane_acc_flush(const LaneAcc& A, float* S, float
   }
 }
 
-template <bool BUILD>
+template <bool BUILD, bool HEAVY>
 __global__ void __launch_bounds__(kGThreads) ba_global_kernel(GArgs a) {
   extern __shared__ float smem_all[];  // entry lists [kGWarps][kMaxEntries] x (6 floats + frame); BUILD: + Ecol, q, qu
   float(*ent_v)[kMaxEntries][6] = reinterpret_cast<float(*)[kMaxEntries][6]>(smem_all);
   int(*ent_f)[kMaxEntries] = reinterpret_cast<int(*)[kMaxEntries]>(smem_all + kGWarps * kMaxEntries * 6);
   float* dyn_mem = smem_all + kEntryBytes / sizeof(float);  // BUILD: Ecol [kChunk][kWinDim], q [kChunk], qu [kChunk]
+  constexpr int kCap = HEAVY ? kHeavyCap : kMaxEntries;
   __shared__ int s_wb;
   __shared__ int perm[kGWarps][32];
   const int N = a.N, n6 = 6 * N;
@@ -150,10 +161,13 @@ __global__ void __launch_bounds__(kGThreads) ba_global_kernel(GArgs a) {
   const float fx = a.intr[0], fy = a.intr[1], cx = a.intr[2], cy = a.intr[3];  // row 0 only (ba_cuda.cu:232-238)
   const float lambda = a.lmbda[0];
   const int Mp = a.p.hdr->Mp;
-  const int r_lo = (int)((long long)Mp * a.shard / a.nshards), r_hi = (int)((long long)Mp * (a.shard + 1) / a.nshards);
+  // the main pass walks this shard's contiguous run of patch ranks; the heavy pass walks the list the main pass left behind
+  const int r_lo = HEAVY ? 0 : (int)((long long)Mp * a.shard / a.nshards);
+  const int r_hi = HEAVY ? a.heavy[0] : (int)((long long)Mp * (a.shard + 1) / a.nshards);
   const unsigned FULL = 0xffffffffu;
-  float(*ev)[6] = ent_v[warp];
-  int* ef = ent_f[warp];
+  const size_t gw = (size_t)blockIdx.x * kGWarps + warp;
+  float(*ev)[6] = HEAVY ? reinterpret_cast<float(*)[6]>(a.spill + gw * kHeavyCap * 6) : ent_v[warp];
+  int* ef = HEAVY ? reinterpret_cast<int*>(a.spill + (size_t)kHeavyCtas * kGWarps * kHeavyCap * 6) + gw * kHeavyCap : ent_f[warp];
   float* Ecol = dyn_mem;
   float* qs = dyn_mem + kChunk * kWinDim;
   float* qus = qs + kChunk;
@@ -165,7 +179,7 @@ __global__ void __launch_bounds__(kGThreads) ba_global_kernel(GArgs a) {
     if (BUILD) {
       // window base: the lowest free frame the chunk's first patch touches (its segment is ordered by target frame)
       if (threadIdx.x == 0) {
-        const int e0 = a.p.eperm[a.p.seg_off[c_lo]];
+        const int e0 = a.p.eperm[a.p.seg_off[HEAVY ? a.heavy[4 + c_lo] : c_lo]];
         long long f = min(a.jj[e0], a.ii[e0]) - a.t0;
         s_wb = (int)max(0ll, min(f, (long long)max(N - kWinFrames, 0)));
       }
@@ -184,9 +198,14 @@ __global__ void __launch_bounds__(kGThreads) ba_global_kernel(GArgs a) {
       for (int t = 0; t < 6; t++) vi[t] = 0.f;
     }
     for (int pi = 0; pi < kPerWarp; pi++) {
-      const int r = c_lo + warp * kPerWarp + pi;
-      if (r >= c_hi) break;
+      const int slot = c_lo + warp * kPerWarp + pi;     // position in the chunk's run (column slot - c_lo of Ecol)
+      if (slot >= c_hi) break;
+      const int r = HEAVY ? a.heavy[4 + slot] : slot;   // rank of the patch in the plan
       const int id = a.p.kx[r], off = a.p.seg_off[r], n = a.p.seg_off[r + 1] - off;
+      if (!HEAVY && 2 * n > kMaxEntries) {              // may not fit the shared-memory list: leave it to the heavy pass
+        if (lane == 0) a.heavy[4 + atomicAdd(a.heavy, 1)] = r;
+        continue;
+      }
       const float* pc = a.patches + (size_t)id * 3 * PP;
       const float px = pc[ctr], py = pc[PP + ctr], pd = pc[2 * PP + ctr];
       float Csum = 0.f, usum = 0.f;
@@ -293,7 +312,7 @@ __global__ void __launch_bounds__(kGThreads) ba_global_kernel(GArgs a) {
         {
           const unsigned mj = __ballot_sync(FULL, free_j);
           const int nj = __popc(mj);
-          if (L + nj <= kMaxEntries) {
+          if (L + nj <= kCap) {
             if (free_j) {
               const int s = L + __popc(mj & ((1u << lane) - 1u));
               ef[s] = fj;
@@ -307,7 +326,7 @@ __global__ void __launch_bounds__(kGThreads) ba_global_kernel(GArgs a) {
 #pragma unroll
             for (int c = 0; c < 6; c++) Es[c] = warp_sum(Ei[c]);
             if (free0) {
-              if (L + 1 <= kMaxEntries) {
+              if (L + 1 <= kCap) {
                 if (lane == 0) {
                   ef[L] = f0;
 #pragma unroll
@@ -319,7 +338,7 @@ __global__ void __launch_bounds__(kGThreads) ba_global_kernel(GArgs a) {
           } else {
             const unsigned mi = __ballot_sync(FULL, free_i);
             const int ni = __popc(mi);
-            if (L + ni <= kMaxEntries) {
+            if (L + ni <= kCap) {
               if (free_i) {
                 const int s = L + __popc(mi & ((1u << lane) - 1u));
                 ef[s] = fi;
@@ -342,7 +361,7 @@ __global__ void __launch_bounds__(kGThreads) ba_global_kernel(GArgs a) {
       if (BUILD) {
         if (N > 0) {
           // window part of the column -> Ecol (entries of one patch may repeat a frame: add), the rest -> HBM atomics
-          const int col = r - c_lo;
+          const int col = slot - c_lo;
           float* mycol = Ecol + col * kWinDim;
           for (int t = lane; t < L * 6; t += 32) {
             const int en = t / 6, c = t - 6 * en, f = ef[en];
@@ -481,7 +500,10 @@ int plan_grid();  // ba_plan.cu
 int band_ld(int bs);
 size_t band_floats(int n6, int bs);
 
-size_t ba_global_workspace_bytes(int64_t E, int64_t n_patches) { return plan_bytes(E, n_patches, plan_grid()) + 1024; }
+static size_t heavy_offset(int64_t E, int64_t n_patches) { return (plan_bytes(E, n_patches, plan_grid()) + 1024 + 255) & ~(size_t)255; }
+size_t ba_global_workspace_bytes(int64_t E, int64_t n_patches) {
+  return heavy_offset(E, n_patches) + heavy_list_ints(E) * sizeof(int) + 256 + kHeavySpillBytes;
+}
 
 static GArgs make_gargs(float* poses, float* patches, const float* intr, const float* target, const float* weight, const float* lmbda,
                         const int64_t* ii, const int64_t* jj, int64_t E, int64_t n_poses, int64_t n_patches, int P, int t0, int t1,
@@ -491,6 +513,8 @@ static GArgs make_gargs(float* poses, float* patches, const float* intr, const f
   a.poses = poses; a.patches = patches; a.intr = intr; a.target = target; a.weight = weight; a.lmbda = lmbda; a.ii = ii; a.jj = jj;
   a.patches_est = patches_est; a.mu = mu; a.P = P; a.t0 = t0; a.N = t1 - t0; a.n_poses = (int)n_poses;
   a.shard = shard; a.nshards = nshards; a.status = status;
+  a.heavy = reinterpret_cast<int*>(static_cast<char*>(ws) + heavy_offset(E, n_patches));
+  a.spill = reinterpret_cast<float*>(static_cast<char*>(ws) + ((heavy_offset(E, n_patches) + heavy_list_ints(E) * sizeof(int) + 255) & ~(size_t)255));
   return a;
 }
 
@@ -498,6 +522,19 @@ static int global_grid(int64_t n_patches_guess) {
   const int64_t want = (n_patches_guess + kChunk - 1) / kChunk;
   const int64_t cap = (int64_t)sm_count() * 2;
   return (int)std::max<int64_t>(1, std::min(want, cap));
+}
+
+// the main pass over this shard's patches, then the heavy pass over the patches it skipped (an empty list costs one idle launch)
+template <bool BUILD>
+static int launch_global_passes(const GArgs& a, int64_t n_patches_guess, size_t smem, cudaStream_t st) {
+  WV_CUDA_TRY(cudaMemsetAsync(a.heavy, 0, 4 * sizeof(int), st));
+  WV_CUDA_TRY(cudaFuncSetAttribute(ba_global_kernel<BUILD, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  ba_global_kernel<BUILD, false><<<global_grid(n_patches_guess), kGThreads, smem, st>>>(a);
+  WV_LAUNCH_CHECK();
+  WV_CUDA_TRY(cudaFuncSetAttribute(ba_global_kernel<BUILD, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  ba_global_kernel<BUILD, true><<<kHeavyCtas, kGThreads, smem, st>>>(a);
+  WV_LAUNCH_CHECK();
+  return WV_OK;
 }
 
 int ba_global_build(float* poses, float* patches, const float* intr, const float* target, const float* weight, const float* lmbda,
@@ -520,10 +557,7 @@ int ba_global_build(float* poses, float* patches, const float* intr, const float
     WV_CUDA_TRY(cudaMemsetAsync(S, 0, s_floats * sizeof(float), st));
     WV_CUDA_TRY(cudaMemsetAsync(y, 0, n6 * sizeof(float), st));
   }
-  WV_CUDA_TRY(cudaFuncSetAttribute(ba_global_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBuildSmem));
-  ba_global_kernel<true><<<global_grid(std::min(E, n_patches)), kGThreads, kBuildSmem, st>>>(a);
-  WV_LAUNCH_CHECK();
-  return WV_OK;
+  return launch_global_passes<true>(a, std::min(E, n_patches), kBuildSmem, st);
 }
 
 // widest frame span of any patch's observations among the free poses (source frame included): the reduced system couples two
@@ -578,10 +612,7 @@ int ba_global_dz(float* poses, float* patches, const float* intr, const float* t
                        shard, nshards, status);
   a.dX = dX; a.dZ = dZ;
   WV_CUDA_TRY(cudaMemsetAsync(dZ, 0, sizeof(float) * (size_t)std::min(E, n_patches), st));
-  WV_CUDA_TRY(cudaFuncSetAttribute(ba_global_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kEntryBytes));
-  ba_global_kernel<false><<<global_grid(std::min(E, n_patches)), kGThreads, kEntryBytes, st>>>(a);
-  WV_LAUNCH_CHECK();
-  return WV_OK;
+  return launch_global_passes<false>(a, std::min(E, n_patches), kEntryBytes, st);
 }
 
 int ba_global_retract(float* poses, float* patches, int64_t E, int64_t n_poses, int64_t n_patches, int P, int t0, int t1,

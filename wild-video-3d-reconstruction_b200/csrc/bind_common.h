@@ -52,7 +52,7 @@ inline void raise_on_status(const torch::Device& dev, const char* what) {
   TORCH_CHECK_INDEX(!(s & WV_STATUS_BAD_INDEX), what, ": index out of range in the edge list");
   TORCH_CHECK(!(s & WV_STATUS_STALE_PLAN), what, ": the cached edge plan did not match kk (poses / patches of this call are invalid); "
               "set WVB200_NO_PLAN_CACHE=1 and report this");
-  TORCH_CHECK(!(s & WV_STATUS_TOO_DENSE), what, ": a patch is observed by more than 384 free poses (global BA entry list)");
+  TORCH_CHECK(!(s & WV_STATUS_TOO_DENSE), what, ": a patch has more than 8256 pose entries (global BA entry list: duplicate edges?)");
   TORCH_CHECK(!(s & WV_STATUS_NOT_SPD), what,
               ": linalg.cholesky: the reduced camera system is not positive-definite");
 }

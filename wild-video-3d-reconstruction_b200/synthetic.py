@@ -114,13 +114,15 @@ def config4_edges(n, M, span=12, loop_frac=0.02, seed=3):
 
 # ----------------------------------------------------------------------------- BA scene
 def make_ba_scene(seed=0, n=10, M=96, edges="all", ht=96, wd=128, fx=110.0, n_buffer=None,
-                  pose_noise=0.02, depth_noise=0.1, pix_noise=0.5, first_frame=0, lifetime=13, removal=22, loop_frac=0.02):
+                  pose_noise=0.02, depth_noise=0.1, pix_noise=0.5, first_frame=0, lifetime=13, removal=22, loop_frac=0.02,
+                  heavy_patches=()):
     """Synthetic window: forward motion 0.1 m/frame + 1 deg/frame yaw, points at depth U(2,8) m.
 
     Returns a dict of float32/int64 numpy arrays with the layouts cuda_ba.forward takes:
     poses [Nbuf,7] (world->camera), patches [Nbuf*M,3,3,3], intrinsics [Nbuf,4], target/weight [E,2],
     ii/jj/kk [E], plus poses_gt / patches_gt / patches_est (prior with 20 % invalid = 0).
-    Frames live at buffer rows first_frame .. first_frame+n-1.
+    Frames live at buffer rows first_frame .. first_frame+n-1.  `heavy_patches`: patch ids (0-based, before `first_frame`) that
+    EVERY other frame observes, whatever the edge pattern says (a camera turning on the spot under distance-based edges).
     """
     rng = np.random.default_rng(seed)
     P = 3
@@ -150,6 +152,10 @@ def make_ba_scene(seed=0, n=10, M=96, edges="all", ht=96, wd=128, fx=110.0, n_bu
         ii, jj, kk = config4_edges(n, M, loop_frac=loop_frac)
     else:
         ii, jj, kk = tracker_edges(n, M, lifetime, removal)
+    for k in heavy_patches:
+        keep = kk != k
+        oth = np.setdiff1d(np.arange(n), [k // M])
+        ii = np.concatenate([ii[keep], np.full(len(oth), k // M)]); jj = np.concatenate([jj[keep], oth]); kk = np.concatenate([kk[keep], np.full(len(oth), k)])
     # true projections of the patch centres
     src = kk // M
     Xc = np.stack([(ctr[kk, 0] - cx) / fx, (ctr[kk, 1] - cy) / fx, np.ones(len(kk))], -1) * depth[kk, None]
