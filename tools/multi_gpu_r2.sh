@@ -15,4 +15,18 @@ import json
 d = json.loads(open("$O/bench.json").read().strip().splitlines()[-1])
 print({k: d[k] for k in ("metric", "value", "n_gpus", "ms_per_step", "scaling")}, d.get("e2e"), d.get("sharded", {}).get("ms_2_iterations"), d.get("ref_cuda", {}).get("value"))
 PY
-tail -3 $O/*.err | cut -c1-300
+tail -n 3 $O/bench.err | cut -c1-300
+# configs[4]: a clip batch over the N GPUs (8 clips per GPU), then one clip of every rank's shard again in ONE process: the COLMAP
+# export must not depend on the sharding (trees stay on the box; the JSON lines come back)
+C=$((8 * N)); FR=${CLIP_FRAMES:-80}
+$TR --master-port 29516 tools/run_clips.py --clips $C --frames $FR --out /tmp/clips_n$N > $O/clips.json 2> $O/clips.err
+ONLY=$(python -c "print(','.join(str(8 * r + (r % 8)) for r in range($N)))")
+python tools/run_clips.py --only $ONLY --frames $FR --out /tmp/clips_one > $O/clips_one_process.json 2>> $O/clips.err
+python tools/run_clips.py --compare /tmp/clips_n$N /tmp/clips_one --subset > $O/clips_compare.json 2>> $O/clips.err
+python - <<PY
+import json
+d = json.loads(open("$O/clips.json").read().strip().splitlines()[-1])
+print({k: d[k] for k in ("metric", "value", "n_gpus", "clips", "frames_per_clip", "seconds", "ate_rmse_m")})
+print(open("$O/clips_compare.json").read())
+PY
+tail -n 3 $O/clips.err | cut -c1-300

@@ -57,10 +57,14 @@ def read_images_txt(path):
     return rows
 
 
-def compare_trees(a, b, tol=1e-4):
-    """-> dict(clips, max_pose_diff, max_point_diff); raises AssertionError on the first violation"""
-    clips = sorted(d for d in os.listdir(a) if d.startswith("clip_"))
-    assert clips and clips == sorted(d for d in os.listdir(b) if d.startswith("clip_")), "different clip sets"
+def compare_trees(a, b, tol=1e-4, subset=False):
+    """-> dict(clips, max_pose_diff, max_point_diff); raises AssertionError on the first violation.  subset: compare the clips
+    of tree b only (b = a re-run of some clips of a under another sharding)"""
+    clips = sorted(d for d in os.listdir(b if subset else a) if d.startswith("clip_"))
+    if subset:
+        assert clips and all(os.path.isdir(os.path.join(a, c)) for c in clips), "clips of the second tree missing from the first"
+    else:
+        assert clips and clips == sorted(d for d in os.listdir(b) if d.startswith("clip_")), "different clip sets"
     worst_pose = worst_pt = 0.0
     for c in clips:
         ia, ib = read_images_txt(os.path.join(a, c, "colmap", "images.txt")), read_images_txt(os.path.join(b, c, "colmap", "images.txt"))
@@ -91,9 +95,11 @@ def main():
     ap.add_argument("--wd", type=int, default=512)
     ap.add_argument("--out", default="gpurun_out/clips")
     ap.add_argument("--compare", nargs=2, default=None)
+    ap.add_argument("--subset", action="store_true", help="--compare: the second tree holds a subset of the first tree's clips")
+    ap.add_argument("--only", default=None, help="comma-separated clip ids to track instead of 0 .. clips-1 (sharded the same way)")
     args = ap.parse_args()
     if args.compare:
-        print(json.dumps(compare_trees(*args.compare)))
+        print(json.dumps(compare_trees(*args.compare, subset=args.subset)))
         return 0
     real_stdout = os.fdopen(os.dup(1), "w")
     os.dup2(2, 1)
@@ -106,7 +112,9 @@ def main():
     from harness.world import World
     H.load_tracker("b200")
     colmap = importlib.import_module(PKG + ".colmap_export")
-    mine = dist_mod.clip_shard(args.clips, rank, world)
+    ids = [int(c) for c in args.only.split(",")] if args.only else list(range(args.clips))
+    mine = [ids[i] for i in dist_mod.clip_shard(len(ids), rank, world)]
+    args.clips = len(ids)
     os.makedirs(args.out, exist_ok=True)
     dist_mod.barrier()
     torch.cuda.synchronize()
