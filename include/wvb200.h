@@ -47,7 +47,7 @@ enum {
   WV_STATUS_BAD_INDEX = 1, /* an ii/jj/kk entry was outside its tensor; that edge was skipped */
   WV_STATUS_NOT_SPD = 2,   /* Cholesky met a non-positive pivot (reference: torch::linalg::cholesky throws, ba_cuda.cu:521) */
   WV_STATUS_TOO_DENSE = 4, /* global BA: one patch had more than 8 256 entries (two per pose of a 4 096-frame buffer) in its column of E; the excess was dropped */
-  WV_STATUS_STALE_PLAN = 8 /* wv_ba_forward_planned: the plan in the workspace was not built for this kk; the result is invalid */
+  WV_STATUS_STALE_PLAN = 8 /* wv_ba_forward_planned: the plan in the workspace was not built for this kk; NOTHING was applied (poses / patches untouched): call wv_ba_forward */
 };
 
 const char* wv_strerror(int code);
@@ -150,7 +150,7 @@ int wv_ba_forward(float* poses, float* patches, const float* intrinsics, const f
  * built for the SAME kk / jj (the tracker calls neighbors and BA on one edge list per update(), dpvo/net.py:81 then
  * dpvo/dpvo.py:733): skips the second plan build.  workspace_bytes >= wv_ba_workspace_bytes(E, plan_groups, t1 - t0);
  * kk values must be < plan_groups.  ii / jj are range-checked by the BA kernel itself, every edge's kk is verified against the
- * plan (mismatch -> WV_STATUS_STALE_PLAN: the call's result is invalid), and patch ids >= n_patches are flagged
+ * plan (mismatch -> WV_STATUS_STALE_PLAN: the kernel stops before it applies anything, the caller repeats with wv_ba_forward), and patch ids >= n_patches are flagged
  * (WV_STATUS_BAD_INDEX) and skipped. */
 int wv_ba_forward_planned(float* poses, float* patches, const float* intrinsics, const float* target,
                           const float* weight, const float* lmbda, const int64_t* ii, const int64_t* jj,

@@ -748,11 +748,35 @@ def test_planned_ba_detects_a_plan_built_for_other_edges(syn):
     st, poses, _ = planned(D["kk"], D["kk"], n_patches)
     assert st == 0 and not torch.equal(poses, D["poses"])
     other = D["kk"].clone(); other[::7] = (other[::7] + 3) % n_patches
-    st, _, _ = planned(D["kk"], other, n_patches)
-    assert st & 8                      # WV_STATUS_STALE_PLAN
+    st, poses, patches = planned(D["kk"], other, n_patches)
+    assert st & 8                      # WV_STATUS_STALE_PLAN ...
+    assert torch.equal(poses, D["poses"]) and torch.equal(patches, D["patches"])   # ... and nothing was applied
     st, _, patches = planned(D["kk"], D["kk"], n_patches // 2)   # half the patch buffer: ids beyond it are flagged ...
     assert st & 1                      # WV_STATUS_BAD_INDEX
     assert torch.equal(patches[n_patches // 2:], D["patches"][n_patches // 2:])  # ... and never touched
+
+
+def test_forward_repeats_with_its_own_plan_when_the_cached_plan_is_stale(syn):
+    """cuda_ba.neighbors(kk, jj) leaves an edge plan behind for the BA that follows on the same tensors (one update() of the tracker).
+    If the tensor at that address holds OTHER ids by the time forward() runs -- same pointer, same _version: what a caching allocator
+    can produce after the first tensor died -- the plan is stale: the call must come back with the right answer, not a corrupted state
+    and an exception (the kernel verifies every edge against the plan, stops before applying, the binding repeats)."""
+    _, cb = pkg().native_modules()
+    s = syn.make_ba_scene(seed=2, n=20, M=16, edges="tracker")
+    t1 = int(s["t1"]); t0 = t1 - 10
+    D = {k: dev(s[k]) for k in ("intrinsics", "target", "weight", "lmbda", "ii", "jj")}
+    kk_true = dev(s["kk"])
+    n_patches = s["patches"].shape[0]
+    wrong = kk_true.clone(); wrong[::7] = (wrong[::7] + 3) % n_patches
+    kk = wrong.clone()
+    cb.neighbors(kk, D["jj"])                                  # the plan left behind is for the WRONG ids ...
+    v = kk._version
+    kk.data.copy_(kk_true)                                     # ... same storage, same version counter, other contents (`.data` writes
+    assert kk._version == v and torch.equal(kk, kk_true)       # do not bump the version): the cache key still matches
+    poses, patches = dev(s["poses"].copy()), dev(s["patches"].copy())
+    cb.forward(poses, patches, D["intrinsics"], D["target"], D["weight"], D["lmbda"], D["ii"], D["jj"], kk, t0, t1, 2)
+    wp, wq = run_ba(s, t0, t1, 2)                              # the same call without any cached plan
+    assert np.array_equal(poses.cpu().numpy(), wp) and np.array_equal(patches.cpu().numpy(), wq)
 
 
 # ------------------------------------------------------------------------------------------------- fused projective ops (N1 / N4)

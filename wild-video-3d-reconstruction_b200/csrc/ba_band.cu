@@ -373,15 +373,21 @@ __global__ void __launch_bounds__(32, 1) ba_band_backsolve_kernel(BandArgs g) {
   const int FP = (bs + 2) * 36, FP4 = FP / 4, RING = bs + 2 + kBackPrefetch;
   const float* const F = g.F + (rev ? (size_t)g.mf * FP : 0);
   float* ring = smem;                                   // [RING][FP], record of pose q in slot q % RING
-  auto issue = [&](int pose) {
+  // record `pose` into ring slot `slot` (= pose % RING, kept incrementally by the callers: no division in the loop)
+  auto issue = [&](int pose, int slot) {
     if (pose >= 0 && pose < me) {
-      const float4* src = reinterpret_cast<const float4*>(F + (size_t)pose * FP);
-      float4* dst = reinterpret_cast<float4*>(ring + (size_t)(pose % RING) * FP);
-      for (int t = d; t < FP4; t += 32) cp_async16(dst + t, src + t);
+      const float4* src = reinterpret_cast<const float4*>(F) + (size_t)pose * FP4 + d;
+      float4* dst = reinterpret_cast<float4*>(ring) + (size_t)slot * FP4 + d;
+#pragma unroll
+      for (int t = 0; t < (kBandMaxBs + 2) * 9; t += 32)
+        if (t + d < FP4) cp_async16(dst + t, src + t);
     }
     cp_async_commit();                                  // an empty group keeps the count uniform
   };
-  for (int s = 0; s <= bs + kBackPrefetch; s++) issue(N - 1 - s);
+  {
+    int sl = (N - 1) % RING;
+    for (int s = 0; s <= bs + kBackPrefetch; s++) { issue(N - 1 - s, sl); sl = sl == 0 ? RING - 1 : sl - 1; }
+  }
   float acc[6];
 #pragma unroll
   for (int j = 0; j < 6; j++) acc[j] = 0.f;
@@ -391,7 +397,7 @@ __global__ void __launch_bounds__(32, 1) ba_band_backsolve_kernel(BandArgs g) {
   for (int R = N - 1; R >= 0; R--) {
     cp_async_wait<kBackPrefetch>();                     // record R - bs (and every later one) has landed
     __syncwarp();
-    issue(R - bs - kBackPrefetch - 1);                  // into the slot of pose R + 1, which nobody reads any more
+    issue(R - bs - kBackPrefetch - 1, slot0 + 1 == RING ? 0 : slot0 + 1);   // the slot of pose R + 1, which nobody reads any more
     const bool act = tile_lane && R - d >= 0 && R - d < me;
     float yt[36];                                       // Y(R, R - d)^T: [j][i]
     if (act) {

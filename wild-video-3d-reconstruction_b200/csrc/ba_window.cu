@@ -270,6 +270,9 @@ __global__ void __launch_bounds__(kBaThreads, 1) ba_window_kernel(BAArgs a) {
         }
       }
       grid.sync();
+      // a reused plan that does not belong to this kk (flagged by some CTA in phase A, visible to all after the grid syncs): stop
+      // BEFORE anything is applied -- poses and patches are still the caller's, who rebuilds the plan and calls again
+      if (a.kk_check && (*reinterpret_cast<volatile int*>(a.status) & WV_STATUS_STALE_PLAN)) break;
       // ---------------------------------------------------------------- phase C: damped Cholesky (every CTA)
       // Blocked right-looking LL^T on the (n6+1) x n6 trapezoid [S ; y^T] in shared memory, one 6-column pose block per step
       // (N steps of 2 barriers instead of 6N column steps): carrying the right-hand side as an extra row makes the forward
@@ -397,6 +400,10 @@ __global__ void __launch_bounds__(kBaThreads, 1) ba_window_kernel(BAArgs a) {
       }
       grid.sync();
     } else {  // structure-only (ba_cuda.cu:494-506): dZ = Q u
+      if (a.kk_check) {   // reused plan: agree on its validity before applying anything (see above)
+        grid.sync();
+        if (*reinterpret_cast<volatile int*>(a.status) & WV_STATUS_STALE_PLAN) break;
+      }
       for (int r = r_lo + threadIdx.x; r < r_hi; r += blockDim.x) {
         if (a.p.kx[r] >= a.n_patches) continue;
         float* pdz = a.patches + (size_t)a.p.kx[r] * 3 * PP + 2 * PP;

@@ -43,19 +43,26 @@ inline torch::Tensor& status_word(const torch::Device& dev) {
   return it->second;
 }
 
-// read + clear the status word (host sync); raises like the reference would
-inline void raise_on_status(const torch::Device& dev, const char* what) {
+// read + clear the status word (host sync)
+inline int read_status(const torch::Device& dev, const char* what) {
   torch::Tensor& w = status_word(dev);
   int s = 0;
   check_rc(wv_status_read(w.data_ptr<int>(), &s, current_stream()), what);  // async copy to a pinned word + event spin; clears when set
+  return s;
+}
+
+// raise like the reference would
+inline void raise_for_status(int s, const char* what) {
   if (s == 0) return;
   TORCH_CHECK_INDEX(!(s & WV_STATUS_BAD_INDEX), what, ": index out of range in the edge list");
-  TORCH_CHECK(!(s & WV_STATUS_STALE_PLAN), what, ": the cached edge plan did not match kk (poses / patches of this call are invalid); "
-              "set WVB200_NO_PLAN_CACHE=1 and report this");
+  TORCH_CHECK(!(s & WV_STATUS_STALE_PLAN), what, ": the cached edge plan did not match kk and the call ran with WVB200_ASYNC=1, so it could "
+              "not be repeated with a fresh plan (poses / patches were left untouched); set WVB200_NO_PLAN_CACHE=1");
   TORCH_CHECK(!(s & WV_STATUS_TOO_DENSE), what, ": a patch has more than 8256 pose entries (global BA entry list: duplicate edges?)");
   TORCH_CHECK(!(s & WV_STATUS_NOT_SPD), what,
               ": linalg.cholesky: the reduced camera system is not positive-definite");
 }
+
+inline void raise_on_status(const torch::Device& dev, const char* what) { raise_for_status(read_status(dev, what), what); }
 
 inline int wv_dtype_of(const torch::Tensor& t, const char* name) {
   if (t.scalar_type() == torch::kHalf) return WV_F16;

@@ -256,6 +256,13 @@ std::vector<torch::Tensor> ba_forward(torch::Tensor poses, torch::Tensor patches
   const bool planned = !env_flag("WVB200_NO_PLAN_CACHE") && note.E == E && note.kk == kkc.data_ptr() && note.jj == jjc.data_ptr() &&
                        note.vkk == kkc._version() && note.vjj == jjc._version() && note.ws == ws.data_ptr() &&
                        note.stream == (void*)current_stream() && n_patches <= kPlanGroups && (size_t)ws.numel() >= wsb_shared;
+  auto own_plan = [&]() {
+    check_rc(wv_ba_forward(poses.data_ptr<float>(), patches.data_ptr<float>(), intrinsics.data_ptr<float>(), tg.data_ptr<float>(),
+                           wt.data_ptr<float>(), lm.data_ptr<float>(), iic.data_ptr<int64_t>(), jjc.data_ptr<int64_t>(),
+                           kkc.data_ptr<int64_t>(), E, n_poses, n_patches, P, t0, t1, iterations, est, (float)mu, ws.data_ptr(),
+                           (size_t)ws.numel(), status_word(poses.device()).data_ptr<int>(), current_stream()),
+             "cuda_ba.forward");
+  };
   if (planned) {
     check_rc(wv_ba_forward_planned(poses.data_ptr<float>(), patches.data_ptr<float>(), intrinsics.data_ptr<float>(),
                                    tg.data_ptr<float>(), wt.data_ptr<float>(), lm.data_ptr<float>(), iic.data_ptr<int64_t>(),
@@ -266,15 +273,20 @@ std::vector<torch::Tensor> ba_forward(torch::Tensor poses, torch::Tensor patches
     note = PlanNote();  // one-shot: the next BA without a neighbors() before it builds its own plan
   } else {
     note = PlanNote();  // this call rebuilds the plan with its own layout
-    check_rc(wv_ba_forward(poses.data_ptr<float>(), patches.data_ptr<float>(), intrinsics.data_ptr<float>(), tg.data_ptr<float>(),
-                           wt.data_ptr<float>(), lm.data_ptr<float>(), iic.data_ptr<int64_t>(), jjc.data_ptr<int64_t>(),
-                           kkc.data_ptr<int64_t>(), E, n_poses, n_patches, P, t0, t1, iterations, est, (float)mu, ws.data_ptr(),
-                           (size_t)ws.numel(), status_word(poses.device()).data_ptr<int>(), current_stream()),
-             "cuda_ba.forward");
+    own_plan();
   }
   // The reference raises from torch::linalg::cholesky inside this call (dpvo/dpvo.py:733 lets it propagate);
   // reading the status word costs one host sync.  WVB200_ASYNC=1 skips it (capture-safe, errors stay sticky).
-  if (!env_flag("WVB200_ASYNC")) raise_on_status(poses.device(), "cuda_ba.forward");
+  if (!env_flag("WVB200_ASYNC")) {
+    int s = read_status(poses.device(), "cuda_ba.forward");
+    if (planned && (s & WV_STATUS_STALE_PLAN)) {
+      // the plan neighbors() left behind was not for this kk (a caching-allocator address reused by another tensor): the kernel
+      // stopped before applying anything, so the call is simply repeated with its own plan
+      own_plan();
+      s = (s & ~WV_STATUS_STALE_PLAN) | read_status(poses.device(), "cuda_ba.forward");
+    }
+    raise_for_status(s, "cuda_ba.forward");
+  }
   return {};
 }
 
