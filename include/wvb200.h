@@ -60,6 +60,11 @@ unsigned long long wv_launch_count(void);
 int wv_gridsync_probe(int n_ctas, int iters, wv_stream_t stream);
 /* 1 when a device of compute capability 10.x is current, else 0 (the library has sm_100a code only) */
 int wv_device_supported(void);
+/* The library's own status word of the CURRENT device (allocated and zeroed on first use, never freed): one word shared by
+ * every module bound to this library, so that an error flagged by one (e.g. a bad index in a correlation call) is seen by
+ * whoever reads the word next.  Callers may pass their own word instead wherever a `status` argument is taken.  NULL on failure.
+ * No reference counterpart (the reference raises C++ exceptions). */
+int* wv_status_word(void);
 /* Read a device status word back to the host after everything enqueued on `stream` so far, and clear it when non-zero.
  * Blocks (a short spin on an event, then a blocking wait); *value receives the WV_STATUS_* bits.  This is the one host
  * synchronisation a caller needs to turn a data-dependent failure into an exception from the same call, as the reference's

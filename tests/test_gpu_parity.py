@@ -779,6 +779,22 @@ def test_forward_repeats_with_its_own_plan_when_the_cached_plan_is_stale(syn):
     assert np.array_equal(poses.cpu().numpy(), wp) and np.array_equal(patches.cpu().numpy(), wq)
 
 
+def test_corr_index_error_surfaces_through_the_shared_status_word(syn):
+    """a bad index in a correlation call zeroes that edge's rows and flags the library's status word -- the SAME word cuda_ba reads
+    (each extension module is its own shared object; round 1 kept one word per module, so nobody ever saw this flag)"""
+    cc, cb = pkg().native_modules()
+    w = syn.make_corr_workload(seed=1, M=8, pmem=12, n_frames=14, ht=24, wd=32, C=128, lifetime=6, removal=9)
+    g, f0 = dev(w["gmap"], torch.float16), dev(w["fmap0"], torch.float16)
+    co, ii1, jj1 = dev(w["coords"]), dev(w["ii1"]), dev(w["jj1"])
+    cb.check_status(co)                                         # start clean
+    bad = jj1.clone(); bad[3] = 10 ** 6
+    out, = cc.forward(g, f0, co, ii1, bad, 3)
+    assert out[0, 3].abs().max().item() == 0.0
+    with pytest.raises(IndexError):
+        cb.check_status(co)
+    cb.check_status(co)                                         # reading cleared it
+
+
 # ------------------------------------------------------------------------------------------------- fused projective ops (N1 / N4)
 def _pops_dev(g, name):
     return [dev(g[f"{name}_{k}"]) for k in ("poses", "patches", "intrinsics", "ii", "jj", "kk")]

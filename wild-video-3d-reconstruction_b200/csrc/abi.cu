@@ -108,6 +108,21 @@ int wv_device_supported(void) {
   return major == 10 ? 1 : 0;
 }
 
+// One status word per device, owned by the library, so that every module bound to it (cuda_corr, cuda_ba, cuda_agg,
+// lietorch_backends are separate shared objects) reports into -- and reads from -- the same word.
+int* wv_status_word(void) {
+  static int* words[64] = {nullptr};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  if (!words[dev]) {
+    int* p = nullptr;
+    if (cudaMalloc(reinterpret_cast<void**>(&p), 256) != cudaSuccess) return nullptr;
+    if (cudaMemset(p, 0, 256) != cudaSuccess) { cudaFree(p); return nullptr; }
+    words[dev] = p;
+  }
+  return words[dev];
+}
+
 static int word_read(int* status, int n, int* value, wv_stream_t stream, bool clear);
 
 int wv_status_read(int* status, int* value, wv_stream_t stream) { return word_read(status, 1, value, stream, true); }

@@ -34,12 +34,16 @@ inline void check_rc(int rc, const char* what) {
   TORCH_CHECK(false, what, ": ", wv_strerror(rc));
 }
 
-// one int32 status word per device, zero when healthy
+// the library's int32 status word of this device (wv_status_word: shared by all extension modules), zero when healthy
 inline torch::Tensor& status_word(const torch::Device& dev) {
   static std::map<int, torch::Tensor> words;
   auto it = words.find(dev.index());
-  if (it == words.end())
-    it = words.emplace(dev.index(), torch::zeros({1}, torch::dtype(torch::kInt32).device(dev))).first;
+  if (it == words.end()) {
+    c10::cuda::CUDAGuard guard(dev);
+    int* p = wv_status_word();
+    TORCH_CHECK(p != nullptr, "wv_status_word: could not allocate the status word on ", dev);
+    it = words.emplace(dev.index(), torch::from_blob(p, {1}, torch::dtype(torch::kInt32).device(dev))).first;
+  }
   return it->second;
 }
 

@@ -298,7 +298,9 @@ std::vector<torch::Tensor> neighbors(torch::Tensor ii, torch::Tensor jj) {
   torch::Tensor ix = torch::empty({E}, iic.options()), jx = torch::empty({E}, iic.options());
   if (E == 0) return {ix, jx};
   const int64_t n_groups = kPlanGroups;
-  const size_t wsb = wv_ba_workspace_bytes(E, n_groups, 16);  // room for a following BA on the same plan (<= 16 free poses)
+  // room for a following windowed BA on the same plan (<= 16 free poses) -- only at the tracker's edge counts: the global-BA list
+  // (E ~ 1e7, also sent through network.update -> neighbors) would pin gigabytes for a plan the global path cannot use anyway
+  const size_t wsb = wv_ba_workspace_bytes(E, n_groups, E <= ((int64_t)1 << 20) ? 16 : 0);
   torch::Tensor ws = workspace(iic.device(), wsb);
   PlanNote& note = plan_note(iic.device().index());
   note = PlanNote();
