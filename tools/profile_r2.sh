@@ -6,8 +6,9 @@ O=gpurun_out/prof_r2
 mkdir -p $O
 B="python bench.py --no-cpu --no-ref-cuda --no-sharded --quick --steps 10 --warmup 30 --breakdown-frames 0"
 $B > $O/bench_plain.json 2> $O/bench_plain.err || exit 1
-# every kernel of the command (torch's, cuDNN's, cuBLAS's and this library's): the library's share of a frame is the point
-ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file $O/launches_bench_all.csv $B > $O/bench_under_ncu.json 2> $O/bench_under_ncu.err
+# every kernel of the command (torch's, cuDNN's, cuBLAS's and this library's) over ~8 steady-state frames (the launches before
+# them run unprofiled): the library's share of a frame is the point
+ncu --metrics gpu__time_duration.sum --clock-control none --launch-skip ${NCU_SKIP:-40000} --launch-count ${NCU_COUNT:-12000} --csv --log-file $O/launches_bench_all.csv $B > $O/bench_under_ncu.json 2> $O/bench_under_ncu.err
 if [ -z "$SKIP_BAND" ]; then
 python tools/band_one.py > $O/band_one.log 2>&1 || exit 1
 ncu --set full --clock-control none --import-source on -k regex:'ba_band|ba_global_kernel|ba_global_span' -c 8 -o $O/band_global_r2 python tools/band_one.py > $O/ncu_band.log 2>&1
