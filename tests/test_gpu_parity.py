@@ -1138,3 +1138,39 @@ def test_global_ba_at_512_frames_vs_the_reference_cuda_build_gauge_free(syn, sol
     dd = np.abs(d_o[k] / sc - d_r1[k]) / d_r1[k]
     dd_ref = np.abs(d_r2[k] / _sim3_max_diff(c_r2, c_r1)[1] - d_r1[k]) / d_r1[k]
     assert np.median(dd) <= max(5 * np.median(dd_ref), 1e-4), (np.median(dd), np.median(dd_ref), msg)
+
+
+# ------------------------------------------------------------------------------------------------- two devices in one process
+def test_second_device_in_the_same_process(syn):
+    """per-device state (opted-in dynamic shared memory of the tile kernels, SM count, status word, workspaces)
+    used to be process-wide statics, so the first call on a SECOND device of the same process failed to launch.  Same inputs on
+    cuda:0 and cuda:1 from one process: identical results (the kernels are deterministic), no error.  Needs a box with >= 2 GPUs."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("one GPU on this box")
+    cc, cb = pkg().native_modules()
+    altcorr = importlib.import_module(PKG + ".altcorr")
+    w = syn.make_corr_workload(seed=1)
+    s = syn.make_ba_scene(seed=2, n=40, M=96, edges="tracker")
+    g = syn.make_ba_scene(seed=15, n=64, M=4, edges="global", pose_noise=0.005)
+    t1 = int(s["t1"]); t0 = t1 - 10
+    outs = []
+    for d in ("cuda:0", "cuda:1", "cuda:0"):
+        T = lambda a, dt=None: (torch.from_numpy(np.ascontiguousarray(a)).to(d) if dt is None else torch.from_numpy(np.ascontiguousarray(a)).to(d, dt))  # noqa: E731
+        with torch.cuda.device(d):
+            st = altcorr.corr_stacked(T(w["gmap"], torch.float16), (T(w["fmap0"], torch.float16), T(w["fmap1"], torch.float16)),
+                                      T(w["coords"]), T(w["ii1"]), T(w["jj1"]), 3)
+            ix, jx = cb.neighbors(T(s["kk"]), T(s["jj"]))
+            po, pa = T(s["poses"].copy()), T(s["patches"].copy())
+            cb.forward(po, pa, T(s["intrinsics"]), T(s["target"]), T(s["weight"]), T(s["lmbda"]), T(s["ii"]), T(s["jj"]), T(s["kk"]), t0, t1, 2)
+            gp, gq = T(g["poses"].copy()), T(g["patches"].copy())
+            cb.forward(gp, gq, T(g["intrinsics"]), T(g["target"]), T(g["weight"]), T(g["lmbda"]), T(g["ii"]), T(g["jj"]), T(g["kk"]), 1, 64, 2)
+            lb = importlib.import_module("lietorch_backends")
+            X = lb.expm(3, T(np.linspace(-0.3, 0.3, 60).reshape(10, 6)))
+            torch.cuda.synchronize(d)
+            assert st.device == torch.device(d) and po.device == torch.device(d)
+            outs.append([t.cpu() for t in (st, ix, jx, po, pa, X)] + [gp.cpu()])
+    for a, b in zip(outs[0][:6], outs[1][:6]):
+        assert torch.equal(a, b)                        # deterministic kernels: bit-identical across devices
+    for a, b in zip(outs[0][:6], outs[2][:6]):
+        assert torch.equal(a, b)                        # and device 0 still works after device 1 was used
+    assert (outs[0][6] - outs[1][6]).abs().max().item() < 2e-3   # global BA: atomics, reproducible to rounding only
