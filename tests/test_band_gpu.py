@@ -8,7 +8,7 @@ Checked here, on the GPU, through the C ABI (wv_ba_band_solve) and through cuda_
   * a non-positive pivot raises the status flag; sizes beyond the maximum half-width are refused;
   * the band buffer built by ba_global_kernel holds the same numbers as the dense build, and nothing of S lies outside the band;
   * whole BA calls through the band path and through the dense path (WVB200_GLOBAL_DENSE=1) against the fp64 oracle of the
-    reference's algorithm (oracle.ba_reference), same tolerances as the dense-path tests in test_gpu_parity.py."""
+    reference's algorithm (oracle.ba_forward, fp64 mode), same tolerances as the dense-path tests in test_gpu_parity.py."""
 import ctypes
 import importlib
 
