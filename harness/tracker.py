@@ -89,12 +89,24 @@ def make_cfg(yaml_name="default.yaml", **overrides):
 class TeacherNet(torch.nn.Module):
     """see the module docstring; `world` supplies the ground truth"""
 
-    def __init__(self, world, seed=1234, noise_px=0.25, weight=0.6, patches_per_frame=384):
+    def __init__(self, world, seed=1234, noise_px=0.25, weight=0.6, patches_per_frame=384, fused_softagg=False):
         super().__init__()
         net_mod = _loaded["net"]
         g = torch.random.get_rng_state()
         torch.manual_seed(seed)
-        self.base = net_mod.VONet()
+        if fused_softagg:
+            # INTEGRATION.md section 1, optional switch: the update operator's two SoftAgg modules (dpvo/net.py:17, :44-45) become this
+            # repository's blocks.SoftAgg (same parameter names and creation order, so the same seed gives the same weights): group
+            # plan + one fused scatter-softmax / scatter-sum kernel instead of torch.unique + torch_scatter (shimmed in this image)
+            import importlib
+            ours = importlib.import_module("wild-video-3d-reconstruction_b200.blocks").SoftAgg
+            ref_cls, net_mod.SoftAgg = net_mod.SoftAgg, ours
+            try:
+                self.base = net_mod.VONet()
+            finally:
+                net_mod.SoftAgg = ref_cls
+        else:
+            self.base = net_mod.VONet()
         torch.random.set_rng_state(g)
         self.P, self.DIM, self.RES = self.base.P, self.base.DIM, self.base.RES
         self.world = world
@@ -213,7 +225,7 @@ def crc(t):
 
 
 def run_clip(world, backend="b200", n_frames=None, cfg=None, use_depth=True, use_mask=True, log=False, frames_on_host=False,
-             seed=1234, noise_px=0.25, final_updates=12, hooks=None, pre_rendered=None, breakdown=False):
+             seed=1234, noise_px=0.25, final_updates=12, hooks=None, pre_rendered=None, breakdown=False, fused_softagg=False):
     """the loop of dpvo_demo.py:62-141 on the synthetic clip.  Returns a dict with the trajectory (terminate()), per-frame log
     (log=True: n, m, E and CRCs of ii/jj/kk after every frame -- one D2H sync per frame, off for timing), timings, ATE."""
     T = load_tracker(backend)
@@ -222,7 +234,7 @@ def run_clip(world, backend="b200", n_frames=None, cfg=None, use_depth=True, use
     n_frames = n_frames or world.n_frames
     dev = torch.device("cuda")
     torch.manual_seed(seed); torch.cuda.manual_seed_all(seed); np.random.seed(seed)
-    net = TeacherNet(world, seed=seed, noise_px=noise_px, patches_per_frame=cfg.PATCHES_PER_FRAME)
+    net = TeacherNet(world, seed=seed, noise_px=noise_px, patches_per_frame=cfg.PATCHES_PER_FRAME, fused_softagg=fused_softagg)
     frames = pre_rendered if pre_rendered is not None else [world.frame(t) for t in range(n_frames)]
     if frames_on_host:   # the e2e form: every frame starts in pinned host memory, dpvo_demo.py:55-60 uploads it
         frames = [(t, im.cpu().pin_memory(), dp.cpu().pin_memory(), mk.cpu().pin_memory(), K.cpu().pin_memory()) for (t, im, dp, mk, K) in frames]
@@ -281,7 +293,7 @@ def ate_rmse_safe(est, gt):
 
 
 def run_clip_windows(world, backend, warmup, steps, breakdown_frames=0, cfg=None, frames=None, frames_on_host=False, seed=1234,
-                     noise_px=0.25, barrier=None, sampler=None, net=None):
+                     noise_px=0.25, barrier=None, sampler=None, net=None, fused_softagg=False):
     """bench form of run_clip: ONE tracker instance fed `warmup` untimed frames (they cover the tracker's initialisation: 10 frames
     + 12 updates, dpvo/dpvo.py:858-863), then exactly `steps` timed frames bracketed by barrier() + torch.cuda.synchronize() and a
     pair of CUDA events, then `breakdown_frames` more frames under the PhaseTimer.  frames_on_host: every frame starts in pinned host
@@ -295,7 +307,7 @@ def run_clip_windows(world, backend, warmup, steps, breakdown_frames=0, cfg=None
     assert total <= world.n_frames
     torch.manual_seed(seed); torch.cuda.manual_seed_all(seed); np.random.seed(seed)
     if net is None:
-        net = TeacherNet(world, seed=seed, noise_px=noise_px, patches_per_frame=cfg.PATCHES_PER_FRAME)
+        net = TeacherNet(world, seed=seed, noise_px=noise_px, patches_per_frame=cfg.PATCHES_PER_FRAME, fused_softagg=fused_softagg)
     frames = frames if frames is not None else [world.frame(t) for t in range(total)]
     if frames_on_host:
         frames = [(t, im.cpu().pin_memory(), dp.cpu().pin_memory(), mk.cpu().pin_memory(), K.cpu().pin_memory()) for (t, im, dp, mk, K) in frames[:total]]

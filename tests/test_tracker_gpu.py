@@ -30,9 +30,9 @@ def _need():
         pytest.skip("not shipped with this snapshot: " + ", ".join(os.path.relpath(m, ROOT) for m in miss))
 
 
-def _run(backend, tmp, *extra):
-    out = os.path.join(tmp, f"track_{backend}.json")
-    poses = os.path.join(tmp, f"poses_{backend}.npz")
+def _run(backend, tmp, *extra, tag=""):
+    out = os.path.join(tmp, f"track_{backend}{tag}.json")
+    poses = os.path.join(tmp, f"poses_{backend}{tag}.npz")
     cmd = [sys.executable, os.path.join(ROOT, "tools", "track.py"), "--backend", backend, "--frames", str(FRAMES), "--log", "--out", out,
            "--save-poses", poses, *extra]
     p = subprocess.run(cmd, capture_output=True, text=True, timeout=1500)
@@ -130,3 +130,17 @@ def test_clip_batch_export_is_independent_of_the_sharding(tmp_path):
     import run_clips
     res = run_clips.compare_trees(a, b, tol=1e-4)
     assert res["clips"] == 4
+
+
+@pytest.mark.gpu
+def test_fused_softagg_switch_tracks_the_same(arms, tmp_path):
+    """INTEGRATION.md's optional switch: dpvo.net's two SoftAgg modules replaced by this repository's blocks.SoftAgg
+    (group plan + fused scatter-softmax / scatter-sum kernel, same weights).  The tracker's decisions must not change: per-frame logs
+    (edge lists, keyframe removals) identical to the unswitched run, trajectory equal to it within the BA's own rounding."""
+    _, _, our, our_p = arms
+    fus, fus_p = _run("b200", str(tmp_path), "--fused-softagg", tag="_fused")
+    assert fus["frame_log"] == our["frame_log"]
+    assert np.isfinite(fus["ate"]) and abs(fus["ate"] - our["ate"]) <= 0.05 * our["ate"] + 1e-4
+    sys.path.insert(0, ROOT)
+    from harness.world import ate_rmse
+    assert ate_rmse(fus_p["poses"][:, :3], our_p["poses"][:, :3]) <= 0.2 * our["ate"]

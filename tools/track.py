@@ -112,6 +112,7 @@ def main():
     ap.add_argument("--no-depth", action="store_true")
     ap.add_argument("--no-mask", action="store_true")
     ap.add_argument("--global-ba", action="store_true")
+    ap.add_argument("--fused-softagg", action="store_true", help="b200 only: dpvo.net's SoftAgg modules -> this repository's blocks.SoftAgg")
     ap.add_argument("--buffer", type=int, default=0)
     ap.add_argument("--out", default="")
     ap.add_argument("--save-poses", default="")
@@ -156,7 +157,8 @@ def main():
         type(slam).__call__ = call
 
     r = H.run_clip(world, backend=args.backend, n_frames=args.frames, cfg=cfg, log=args.log, frames_on_host=args.host_frames,
-                   use_depth=not args.no_depth, use_mask=not args.no_mask, pre_rendered=frames, hooks=hooks, breakdown=args.breakdown)
+                   use_depth=not args.no_depth, use_mask=not args.no_mask, pre_rendered=frames, hooks=hooks, breakdown=args.breakdown,
+                   fused_softagg=args.fused_softagg)
     if args.profile:
         ev = prof_state["p"].key_averages()
         rows = sorted(((e.key, e.count, e.device_time_total / 1e3) for e in ev if e.device_time_total > 0), key=lambda x: -x[2])
