@@ -481,7 +481,11 @@ def run_b200(args):
         try:
             Kf = min(K, 100)
             r3 = H.run_clip_windows(wld, "b200", W, Kf, 0, frames=frames, barrier=barrier, fused_softagg=True)
+            r4 = H.run_clip_windows(wld, "b200", W, Kf, 0, frames=frames, barrier=barrier, fused_softagg="all")
             fused = {"value": Kf / (r3["timed_ms"] * 1e-3), "unit": "frames/s", "steps": Kf, "ms_per_frame": r3["timed_ms"] / Kf,
+                     "all_three_switches": {"value": Kf / (r4["timed_ms"] * 1e-3), "ms_per_frame": r4["timed_ms"] / Kf, "ate_rmse_m": r4["ate"],
+                                            "what": "+ DPVO.corr as ONE altcorr.corr_stacked call (dpvo/dpvo.py:325-333) and dpvo.dpvo's `pops` "
+                                                    "module replaced by this repository's fused projective_ops (transform / flow_mag / point_cloud)"},
                      "ate_rmse_m": r3["ate"], "keyframes": r3["keyframes"],
                      "what": "same clip and loop; dpvo.net's two SoftAgg modules are wild-video-3d-reconstruction_b200.blocks.SoftAgg (group "
                              "plan + one fused scatter-softmax / scatter-sum kernel, same weights) instead of torch.unique + the "

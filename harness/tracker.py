@@ -78,6 +78,41 @@ def load_tracker(backend="b200"):
     return _loaded
 
 
+class host_switches:
+    """INTEGRATION.md section 1, the OPTIONAL edits of the reference's Python, applied as patches for one run (b200 backend only) and
+    undone afterwards: `corr` -- DPVO.corr (dpvo/dpvo.py:325-333) as one altcorr.corr_stacked call; `pops` -- dpvo.dpvo's `pops`
+    module (transform / flow_mag / point_cloud, dpvo/projective_ops.py) -> this repository's fused projective_ops.  (The SoftAgg
+    switch lives in TeacherNet: it changes how the network is built.)"""
+
+    def __init__(self, which):
+        self.which = set(which or ())
+        self.saved = []
+
+    def __enter__(self):
+        if not self.which:
+            return self
+        assert _loaded.get("backend") == "b200", "the optional switches replace reference code by this repository's"
+        dm = _loaded["dpvo"]
+        if "corr" in self.which:
+            altcorr = importlib.import_module(PKG + ".altcorr")
+
+            def corr(slam, coords, indicies=None):
+                ii, jj = indicies if indicies is not None else (slam.pg.kk, slam.pg.jj)
+                return altcorr.corr_stacked(slam.gmap, slam.pyramid, coords, ii % (slam.M * slam.pmem), jj % slam.pmem, 3)
+            self.saved.append((dm.DPVO, "corr", dm.DPVO.corr))
+            dm.DPVO.corr = corr
+        if "pops" in self.which:
+            self.saved.append((dm, "pops", dm.pops))
+            dm.pops = importlib.import_module(PKG + ".projective_ops")
+        return self
+
+    def __exit__(self, *exc):
+        for obj, name, old in reversed(self.saved):
+            setattr(obj, name, old)
+        self.saved = []
+        return False
+
+
 def make_cfg(yaml_name="default.yaml", **overrides):
     cfg = load_tracker(_loaded.get("backend", "b200"))["cfg"].clone()
     cfg.merge_from_file(os.path.join(REF_INSTALL, "dpvo_configs", yaml_name))
@@ -94,7 +129,7 @@ class TeacherNet(torch.nn.Module):
         net_mod = _loaded["net"]
         g = torch.random.get_rng_state()
         torch.manual_seed(seed)
-        if fused_softagg:
+        if fused_softagg:   # True or "all"
             # INTEGRATION.md section 1, optional switch: the update operator's two SoftAgg modules (dpvo/net.py:17, :44-45) become this
             # repository's blocks.SoftAgg (same parameter names and creation order, so the same seed gives the same weights): group
             # plan + one fused scatter-softmax / scatter-sum kernel instead of torch.unique + torch_scatter (shimmed in this image)
@@ -229,6 +264,8 @@ def run_clip(world, backend="b200", n_frames=None, cfg=None, use_depth=True, use
     """the loop of dpvo_demo.py:62-141 on the synthetic clip.  Returns a dict with the trajectory (terminate()), per-frame log
     (log=True: n, m, E and CRCs of ii/jj/kk after every frame -- one D2H sync per frame, off for timing), timings, ATE."""
     T = load_tracker(backend)
+    _sw = host_switches(("corr", "pops") if fused_softagg == "all" else ())
+    _sw.__enter__()
     DPVO = T["dpvo"].DPVO
     cfg = cfg if cfg is not None else make_cfg()
     n_frames = n_frames or world.n_frames
@@ -280,6 +317,7 @@ def run_clip(world, backend="b200", n_frames=None, cfg=None, use_depth=True, use
         poses, tstamps = slam.terminate()
     est = np.asarray(poses)[:, :3]
     gt = world.gt_cam_positions()[:len(est)]
+    _sw.__exit__()
     return dict(poses=np.asarray(poses), tstamps=np.asarray(tstamps), frame_log=frame_log, seconds=t_track, frames=n_frames,
                 ms_breakdown=ms_breakdown, fps=n_frames / t_track, device_ms=ev0.elapsed_time(ev1), ate=ate_rmse_safe(est, gt), keyframes=n_kf, edges=E_final,
                 h2d_bytes_per_frame=h2d / max(n_frames, 1), d2h_bytes_per_frame=d2h / max(n_frames, 1), slam=slam, net=net)
@@ -300,6 +338,8 @@ def run_clip_windows(world, backend, warmup, steps, breakdown_frames=0, cfg=None
     memory and is uploaded inside the timed region (dpvo_demo.py:55-60), and the newest pose is read back after every frame.
     -> dict(timed_ms, wall_s, h2d/d2h bytes per frame, ms_breakdown, ate, keyframes, edges, launches_per_frame)"""
     T = load_tracker(backend)
+    _sw = host_switches(("corr", "pops") if fused_softagg == "all" else ())
+    _sw.__enter__()
     DPVO = T["dpvo"].DPVO
     cfg = cfg if cfg is not None else make_cfg()
     dev = torch.device("cuda")
@@ -364,6 +404,7 @@ def run_clip_windows(world, backend, warmup, steps, breakdown_frames=0, cfg=None
             slam.update()
         poses, _ = slam.terminate()
     est = np.asarray(poses)[:, :3]
+    _sw.__exit__()
     return dict(timed_ms=ev0.elapsed_time(ev1), wall_s=wall, h2d_bytes_per_frame=h2d / max(steps, 1), d2h_bytes_per_frame=d2h / max(steps, 1),
                 ms_breakdown=ms_breakdown, ate=ate_rmse_safe(est, world.gt_cam_positions()[:len(est)]), keyframes=n_kf, edges=E_final,
                 frames_total=total, net=net)

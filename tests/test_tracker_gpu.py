@@ -144,3 +144,10 @@ def test_fused_softagg_switch_tracks_the_same(arms, tmp_path):
     sys.path.insert(0, ROOT)
     from harness.world import ate_rmse
     assert ate_rmse(fus_p["poses"][:, :3], our_p["poses"][:, :3]) <= 0.2 * our["ate"]
+    # all three optional switches: + DPVO.corr as one corr_stacked call (bit-identical to the two calls + stack) and the fused
+    # projective ops in place of dpvo.dpvo.pops (2e-4 px from the reference's, so keyframe decisions could differ in principle:
+    # on this clip they do not)
+    al, al_p = _run("b200", str(tmp_path), "--all-switches", tag="_all")
+    assert [f[:3] for f in al["frame_log"]] == [f[:3] for f in our["frame_log"]]      # n, m, E per frame
+    assert np.isfinite(al["ate"]) and abs(al["ate"] - our["ate"]) <= 0.05 * our["ate"] + 1e-4
+    assert ate_rmse(al_p["poses"][:, :3], our_p["poses"][:, :3]) <= 0.2 * our["ate"]

@@ -113,6 +113,7 @@ def main():
     ap.add_argument("--no-mask", action="store_true")
     ap.add_argument("--global-ba", action="store_true")
     ap.add_argument("--fused-softagg", action="store_true", help="b200 only: dpvo.net's SoftAgg modules -> this repository's blocks.SoftAgg")
+    ap.add_argument("--all-switches", action="store_true", help="b200 only: + DPVO.corr as one corr_stacked call, dpvo.dpvo.pops -> the fused projective_ops")
     ap.add_argument("--buffer", type=int, default=0)
     ap.add_argument("--out", default="")
     ap.add_argument("--save-poses", default="")
@@ -158,7 +159,7 @@ def main():
 
     r = H.run_clip(world, backend=args.backend, n_frames=args.frames, cfg=cfg, log=args.log, frames_on_host=args.host_frames,
                    use_depth=not args.no_depth, use_mask=not args.no_mask, pre_rendered=frames, hooks=hooks, breakdown=args.breakdown,
-                   fused_softagg=args.fused_softagg)
+                   fused_softagg="all" if args.all_switches else args.fused_softagg)
     if args.profile:
         ev = prof_state["p"].key_averages()
         rows = sorted(((e.key, e.count, e.device_time_total / 1e3) for e in ev if e.device_time_total > 0), key=lambda x: -x[2])
