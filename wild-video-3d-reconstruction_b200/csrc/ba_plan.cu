@@ -244,7 +244,7 @@ __device__ void plan_phase_order(const PlanArgs& a) {
 }
 
 // ---- launch forms ---------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kPlanThreads) plan_coop_kernel(PlanArgs a) {
+__global__ void __launch_bounds__(1024, 1) plan_coop_kernel(PlanArgs a) {   // 512 threads at tracker sizes, 1024 for > 1 M edges (see plan_build_groups)
   extern __shared__ int sh[];
   cg::grid_group grid = cg::this_grid();
   if (!a.small) {
@@ -262,12 +262,12 @@ __global__ void __launch_bounds__(kPlanThreads) plan_coop_kernel(PlanArgs a) {
   plan_phase_order(a);
 }
 
-__global__ void __launch_bounds__(kPlanThreads) plan_k_minmax(PlanArgs a) { plan_phase_minmax(a); }
-__global__ void __launch_bounds__(kPlanThreads) plan_k_zero(PlanArgs a) { plan_phase_zero(a); }
-__global__ void __launch_bounds__(kPlanThreads) plan_k_count(PlanArgs a) { plan_phase_count(a); }
-__global__ void __launch_bounds__(kPlanThreads) plan_k_scan(PlanArgs a) { extern __shared__ int sh[]; plan_phase_scan(a, sh); }
-__global__ void __launch_bounds__(kPlanThreads) plan_k_fill(PlanArgs a) { extern __shared__ int sh[]; plan_phase_fill(a, sh, sh + gridDim.x + 1); }
-__global__ void __launch_bounds__(kPlanThreads) plan_k_order(PlanArgs a) { plan_phase_order(a); }
+__global__ void __launch_bounds__(1024, 1) plan_k_minmax(PlanArgs a) { plan_phase_minmax(a); }
+__global__ void __launch_bounds__(1024, 1) plan_k_zero(PlanArgs a) { plan_phase_zero(a); }
+__global__ void __launch_bounds__(1024, 1) plan_k_count(PlanArgs a) { plan_phase_count(a); }
+__global__ void __launch_bounds__(1024, 1) plan_k_scan(PlanArgs a) { extern __shared__ int sh[]; plan_phase_scan(a, sh); }
+__global__ void __launch_bounds__(1024, 1) plan_k_fill(PlanArgs a) { extern __shared__ int sh[]; plan_phase_fill(a, sh, sh + gridDim.x + 1); }
+__global__ void __launch_bounds__(1024, 1) plan_k_order(PlanArgs a) { plan_phase_order(a); }
 
 bool use_cooperative() {  // read every call so tests can flip it; getenv is a few ns next to a launch
   const char* s = getenv("WVB200_NO_COOP");
@@ -297,21 +297,25 @@ int plan_build_groups(const Plan& p, const int64_t* g, int64_t goff, const int64
     if (want < grid) grid = want < 32 ? 32 : (int)want;
   }
   if (const char* e = getenv("WVB200_PLAN_GRID")) { const int v = atoi(e); if (v > 0 && v <= plan_grid()) grid = v; }
+  // at global-BA sizes the edge-striding phases want more threads in flight: 1024 per CTA instead of 512 took the plan of E = 9.8 M
+  // edges from 1.09 to 0.77 ms on a B200 (taking four edges per thread and iteration on top of that changed nothing: the phases are
+  // bound by the atomics' throughput in L2 by then, not by load latency)
+  const int threads = p.E > ((int64_t)1 << 20) ? 1024 : kPlanThreads;
   const size_t sh = sizeof(int) * (size_t)(2 * (grid + 1) + 72);
   if (use_cooperative()) {
     void* args[] = {&a};
-    cudaError_t e = cudaLaunchCooperativeKernel((const void*)plan_coop_kernel, dim3(grid), dim3(kPlanThreads), args, sh, st);
+    cudaError_t e = cudaLaunchCooperativeKernel((const void*)plan_coop_kernel, dim3(grid), dim3(threads), args, sh, st);
     if (e == cudaSuccess) { ++g_launches; return WV_OK; }
     (void)cudaGetLastError();  // fall through to the multi-launch form
   }
   if (!a.small) {
-    plan_k_minmax<<<grid, kPlanThreads, 0, st>>>(a);
-    plan_k_zero<<<grid, kPlanThreads, 0, st>>>(a);
+    plan_k_minmax<<<grid, threads, 0, st>>>(a);
+    plan_k_zero<<<grid, threads, 0, st>>>(a);
   }
-  plan_k_count<<<grid, kPlanThreads, 0, st>>>(a);
-  plan_k_scan<<<grid, kPlanThreads, sh, st>>>(a);
-  plan_k_fill<<<grid, kPlanThreads, sh, st>>>(a);
-  plan_k_order<<<grid, kPlanThreads, 0, st>>>(a);
+  plan_k_count<<<grid, threads, 0, st>>>(a);
+  plan_k_scan<<<grid, threads, sh, st>>>(a);
+  plan_k_fill<<<grid, threads, sh, st>>>(a);
+  plan_k_order<<<grid, threads, 0, st>>>(a);
   WV_LAUNCH_CHECK();
   return WV_OK;
 }
