@@ -37,3 +37,24 @@ two = lambda: torch.stack([cc.forward(g, f0, c0 / 1, ii, jj, 3)[0], cc.forward(g
 one = lambda: altcorr.corr_stacked(g, (f0, f1), c0, ii, jj, 3)
 assert torch.equal(two(), one())
 print("DPVO.corr: two calls + stack %.4f ms   stacked kernel %.4f ms" % (t2(two), t2(one)), flush=True)
+# the generic kernels that carry training shapes (no timing evidence): fp32 forward, backward, patchify fwd / bwd
+gf, f0f = g.float(), f0.float()
+gr = torch.randn(1, E, 7, 7, 3, 3, device=dev)
+print("generic fp32 forward L0 %.4f ms" % t2(lambda: cc.forward(gf, f0f, c0, ii, jj, 3)), flush=True)
+print("backward (fp32, L0)     %.4f ms" % t2(lambda: cc.backward(gf, f0f, c0, ii, jj, gr, 3), n=5), flush=True)
+net = torch.randn(1, 128, 96, 128, device=dev)
+pc = torch.rand(1, 96, 2, device=dev) * torch.tensor([120.0, 90.0], device=dev) + 2
+print("patchify fwd r=1        %.4f ms" % t2(lambda: cc.patchify_forward(net, pc, 1)), flush=True)
+pg = torch.randn(1, 96, 128, 3, 3, device=dev)
+print("patchify bwd r=1        %.4f ms" % t2(lambda: cc.patchify_backward(net, pc, pg, 1)), flush=True)
+# the reference's own CUDA build beside it, when oracle/_ref/refgpu_cuda_corr.so was built (oracle/build_ref_gpu.py)
+sys.path.insert(0, os.path.join(os.getcwd(), "oracle"))
+import build_ref
+rc = build_ref.load("refgpu_cuda_corr")
+if rc is not None:
+    print("REF-CUDA: fp32 forward L0 %.4f ms, backward %.4f ms, fp16 forward L0 %.4f ms" % (
+        t2(lambda: rc.forward(gf, f0f, c0, ii, jj, 3), n=5), t2(lambda: rc.backward(gf, f0f, c0, ii, jj, gr, 3), n=5),
+        t2(lambda: rc.forward(g, f0, c0, ii, jj, 3), n=5)), flush=True)
+    ours = cc.backward(gf, f0f, c0, ii, jj, gr, 3); ref = rc.backward(gf, f0f, c0, ii, jj, gr, 3)
+    for a_, b_ in zip(ours, ref):
+        print("  backward max |ours - ref| / max |ref| = %.2e" % ((a_ - b_).abs().max().item() / b_.abs().max().item()))
