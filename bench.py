@@ -46,7 +46,7 @@ CORR_BYTES_L0 = 2 * 128 * 9 + 2 * 128 * 100 + 72 + 16 + 2 * 49 * 9   # 28 874
 CORR_BYTES_L1 = 2 * 128 * 9 + 2 * 128 * 81 + 72 + 16 + 2 * 49 * 9    # 24 010
 BA_BYTES_PER_EDGE_ITER = 116
 # dram__bytes_read.sum + dram__bytes_write.sum of one DPVO.corr call at E = 45 312 (restage + corr_tc5_kernel<2>), ncu --set full
-NCU_TRAFFIC_CORR = 643.0e6
+NCU_TRAFFIC_CORR = 630.4e6
 # compulsory DRAM bytes of that call: both rings 120.3 MB + gmap 8.0 + output 80.0 + coords / indices 4.0
 CORR_COMPULSORY_BYTES = 212.3e6
 MIN_WARMUP = 30
@@ -544,7 +544,7 @@ def run_b200(args):
             "roofline": {"kernel": "DPVO.corr at configs[1]: both levels, stacked (restage_kernel x2 + corr_tc5_kernel<2>, fp16 maps)",
                          "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": NCU_TRAFFIC_CORR, "peak_source": peak_src, "algorithmic_bytes_per_launch": alg,
-                         "traffic_source": "dram__bytes_read+write of restage_kernel x2 + corr_tc5_kernel<2>, ncu --set full, profiles/r1_stacked_ncu_summary.txt",
+                         "traffic_source": "dram__bytes_read+write of restage_kernel x2 + corr_tc5_kernel<2>, ncu --set full, profiles/r2_corr_stacked_ncu_summary.txt",
                          "dram_gbs_from_traffic": NCU_TRAFFIC_CORR / (corr_ms * 1e-3) / 1e9,
                          "dram_frac_of_peak": NCU_TRAFFIC_CORR / (corr_ms * 1e-3) / 1e9 / peak,
                          "compulsory_bytes": CORR_COMPULSORY_BYTES,
