@@ -468,6 +468,51 @@ __global__ void __launch_bounds__(kGThreads) ba_global_kernel(GArgs a) {
   }
 }
 
+// dZ_k = q_k (u_k - sum_a E_a . dX[f_a])  (ba_cuda.cu:524-525) without the entry lists: the dot products are taken edge by edge
+// (E_j . dX[j] + E_i . dX[i]) as the edge's terms are recomputed.  One warp per patch of this shard, a lane per edge; no shared
+// memory, so several CTAs per SM (the build kernel's body with BUILD = false carried the 86 KB entry lists and 249 registers
+// along for a sum it does not need: 0.72 ms at configs[3]; patches of any observation count take the same path).
+__global__ void __launch_bounds__(kGThreads) ba_global_dz_kernel(GArgs a) {
+  const int N = a.N, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int PP = a.P * a.P, ctr = (a.P / 2) * a.P + a.P / 2;
+  const float fx = a.intr[0], fy = a.intr[1], cx = a.intr[2], cy = a.intr[3];  // row 0 only (ba_cuda.cu:232-238)
+  const float lambda = a.lmbda[0];
+  const int Mp = a.p.hdr->Mp;
+  const int r_lo = (int)((long long)Mp * a.shard / a.nshards), r_hi = (int)((long long)Mp * (a.shard + 1) / a.nshards);
+  for (int r = r_lo + blockIdx.x * kGWarps + warp; r < r_hi; r += gridDim.x * kGWarps) {
+    const int id = a.p.kx[r], off = a.p.seg_off[r], n = a.p.seg_off[r + 1] - off;
+    const float* pc = a.patches + (size_t)id * 3 * PP;
+    const float px = pc[ctr], py = pc[PP + ctr], pd = pc[2 * PP + ctr];
+    float Csum = 0.f, usum = 0.f, sdot = 0.f;
+    for (int base = 0; base < n; base += 32) {
+      if (base + lane >= n) continue;
+      const int e = a.p.eperm[off + base + lane];
+      const int64_t iv = a.ii[e], jv = a.jj[e];
+      if (iv < 0 || iv >= a.n_poses || jv < 0 || jv >= a.n_poses) { set_status(a.status, WV_STATUS_BAD_INDEX); continue; }
+      const int ix = (int)iv, jx = (int)jv, fi = ix - a.t0, fj = jx - a.t0;
+      EdgeTerms T;
+      edge_terms(a, e, ix, jx, px, py, pd, fx, fy, cx, cy, T);
+      Csum += T.w[0] * T.Jz[0] * T.Jz[0] + T.w[1] * T.Jz[1] * T.Jz[1];
+      usum += T.w[0] * T.r[0] * T.Jz[0] + T.w[1] * T.r[1] * T.Jz[1];
+      if (fj >= 0 && fj < N) {
+#pragma unroll
+        for (int c = 0; c < 6; c++) sdot += (T.w[0] * T.Jz[0] * T.Jj[0][c] + T.w[1] * T.Jz[1] * T.Jj[1][c]) * a.dX[6 * fj + c];
+      }
+      if (fi >= 0 && fi < N) {
+#pragma unroll
+        for (int c = 0; c < 6; c++) sdot -= (T.w[0] * T.Jz[0] * T.Ji[0][c] + T.w[1] * T.Jz[1] * T.Ji[1][c]) * a.dX[6 * fi + c];
+      }
+    }
+    float C = warp_sum(Csum), u = warp_sum(usum);
+    sdot = warp_sum(sdot);
+    if (a.patches_est) {  // depth prior (dpvo/ba.py:151-159)
+      const float dest = a.patches_est[(size_t)id * 3 * PP + 2 * PP + ctr];
+      if (dest > 0.f) { C += a.mu; u -= a.mu * (pd - dest); }
+    }
+    if (lane == 0) a.dZ[r] = (u - sdot) / (C + lambda);
+  }
+}
+
 __global__ void ba_global_damp_kernel(float* S, int n6) {
   const int d = blockIdx.x * blockDim.x + threadIdx.x;
   if (d < n6) { float* p = S + (size_t)d * n6 + d; const float s = *p; *p = s + (s * 1e-4f + 1.0f); }  // ba_cuda.cu:517-518
@@ -612,7 +657,13 @@ int ba_global_dz(float* poses, float* patches, const float* intr, const float* t
                        shard, nshards, status);
   a.dX = dX; a.dZ = dZ;
   WV_CUDA_TRY(cudaMemsetAsync(dZ, 0, sizeof(float) * (size_t)std::min(E, n_patches), st));
-  return launch_global_passes<false>(a, std::min(E, n_patches), kEntryBytes, st);
+  {
+    const int64_t want = (std::min(E, n_patches) + kGWarps - 1) / kGWarps;
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(want, (int64_t)sm_count() * 8));
+    ba_global_dz_kernel<<<grid, kGThreads, 0, st>>>(a);
+    WV_LAUNCH_CHECK();
+  }
+  return WV_OK;
 }
 
 int ba_global_retract(float* poses, float* patches, int64_t E, int64_t n_poses, int64_t n_patches, int P, int t0, int t1,
